@@ -1,0 +1,746 @@
+// qpmpc.cu -- sampling-MPC solve for sm_100a behind the C ABI of include/qpmpc.h.
+//
+// One solve = two launches on the handle's stream:
+//   k_rollout   grid (ceil(N/T), robots): thread = one rollout.  Draws its noise row with Philox into a
+//               shared-memory column (or copies a reference-supplied row), integrates the SRBD over the horizon,
+//               saturates the cost, then the block reduces {min cost, argmin, sum exp(-(c - min_b)),
+//               sum exp(-(c - min_b)) * eps[P]} from the noise still resident in shared memory.
+//   k_finalize  grid (robots): merges the per-block partials with an online-softmax rescale, applies the
+//               random-sampling / MPPI / CEM-MPPI update, evaluates the first-step GRF and the one-step
+//               prediction, and (CEM) selects the elites and their per-parameter spread.
+// Reference semantics: quadruped_pympc/controllers/sampling/centroidal_nmpc_jax.py:629-1094 and
+// centroidal_nmpc_jax_gait_adaptive.py:634-1131 (see include/qpmpc.h for the entry-point map).
+// No CPU fallback: every entry point fails with QPMPC_E_NODEVICE / QPMPC_E_CUDA when the GPU path cannot run.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "../../include/qpmpc.h"
+#include "philox.cuh"
+#include "srbd.cuh"
+
+namespace qp {
+
+constexpr int PART_HDR = 4;  // per-block partial: [min cost, sum w, argmin cost, argmin index bits] + V[P]
+constexpr int FIN_THREADS = 256;
+
+struct RolloutArgs {
+    const float *state, *reference, *contact, *best, *sigma, *timing, *nominal;
+    const int32_t *oswing;
+    const float *eps, *freqs;  // reference-supplied noise (or the parameter matrix in costs_only mode)
+    float *costs, *partials;
+    NoiseKey key;
+    int n;            // rollouts per robot in this launch
+    int costs_only;   // 1: jit_vectorized_rollout semantics (eps = parameters, no saturation, no partials)
+    int nblk;         // blocks per robot
+};
+
+struct FinalizeArgs {
+    const float *state, *reference, *contact, *best, *sigma, *nominal;
+    const int32_t *oswing;
+    const float *eps, *freqs;
+    const float *costs, *partials;
+    qpmpc_result *result;
+    float *best_out, *sigma_out;
+    NoiseKey key;
+    int nblk;
+};
+
+// ---------------------------------------------------------------- noise ------------------------------------
+// additional_random_parameters[i, 4g..4g+3] (sigma applied) for robot `robot`:
+//   random_sampling centroidal_nmpc_jax.py:647-677 (the two Gaussian thirds share ONE key upstream, hence the
+//   same normals scaled by sigma[0] and sigma[1]; the uniform block is U(-sigma[2], sigma[2]));
+//   mppi :806-812; cem_mppi :951-958 (normals * sigma vector).  Row 0 is always zero.
+__device__ __forceinline__ float4 noise_group(const DevCfg &c, const NoiseKey &nk, const float *sigma_vec, int i,
+                                              int g, uint32_t robot) {
+    if (i == 0) return make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c.method == QPMPC_METHOD_RANDOM) {
+        const int third = c.N / 3;
+        if (i < 1 + 2 * third) {
+            const bool first = i < 1 + third;
+            const float4 z = normal4(draw(nk, STREAM_NORMAL, g, first ? i - 1 : i - 1 - third, robot));
+            const float s = first ? c.sig_rs[0] : c.sig_rs[1];
+            return make_float4(__fmul_rn(s, z.x), __fmul_rn(s, z.y), __fmul_rn(s, z.z), __fmul_rn(s, z.w));
+        }
+        const uint4 u = draw(nk, STREAM_UNIFORM, g, i - 1 - 2 * third, robot);
+        const float a = c.sig_rs[2], w = __fmul_rn(2.0f, a);
+        return make_float4(__fmaf_rn(u01_half_open(u.x), w, -a), __fmaf_rn(u01_half_open(u.y), w, -a),
+                           __fmaf_rn(u01_half_open(u.z), w, -a), __fmaf_rn(u01_half_open(u.w), w, -a));
+    }
+    const float4 z = normal4(draw(nk, STREAM_NORMAL, g, i - 1, robot));
+    if (c.method == QPMPC_METHOD_MPPI) {
+        const float s = c.sig_mppi;
+        return make_float4(__fmul_rn(s, z.x), __fmul_rn(s, z.y), __fmul_rn(s, z.z), __fmul_rn(s, z.w));
+    }
+    return make_float4(__fmul_rn(z.x, sigma_vec[4 * g]), __fmul_rn(z.y, sigma_vec[4 * g + 1]),
+                       __fmul_rn(z.z, sigma_vec[4 * g + 2]), __fmul_rn(z.w, sigma_vec[4 * g + 3]));
+}
+
+// step_frequencies_vec[i]: ..._gait_adaptive.py:687-692 (random_sampling), :834-838 (mppi), :994-999 (cem)
+__device__ __forceinline__ float freq_sample(const DevCfg &c, const NoiseKey &nk, int i, uint32_t robot,
+                                             float nominal, int oswing) {
+    const uint32_t x = draw(nk, STREAM_FREQ, 0, i, robot).x;
+    if (c.method == QPMPC_METHOD_CEM) {
+        const int k = (int)(((uint64_t)x * 3ull) >> 32);
+        const float v = k == 0 ? 0.0f : (k == 1 ? 0.2f : 0.4f);
+        return __fadd_rn(__fmul_rn(v, (float)oswing), nominal);
+    }
+    const int k = (int)(((uint64_t)x * (uint64_t)c.nfreq) >> 32);
+    if (c.method == QPMPC_METHOD_RANDOM && !oswing) return nominal;
+    return c.freqs[k];
+}
+
+// ---------------------------------------------------------------- reductions -------------------------------
+__device__ __forceinline__ void argmin_combine(float &c, int &i, float oc, int oi) {
+    if (oc < c || (oc == c && oi < i)) {
+        c = oc;
+        i = oi;
+    }
+}
+
+// lexicographic (cost, index) minimum over the block; result broadcast to all threads.  s_red: >= 64 floats.
+__device__ __forceinline__ void block_argmin(float &c, int &i, float *s_red) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float oc = __shfl_xor_sync(0xffffffffu, c, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, i, o);
+        argmin_combine(c, i, oc, oi);
+    }
+    __syncthreads();
+    if (lane == 0) {
+        s_red[wid] = c;
+        s_red[32 + wid] = __int_as_float(i);
+    }
+    __syncthreads();
+    c = s_red[0];
+    i = __float_as_int(s_red[32]);
+    for (int w = 1; w < nw; ++w) argmin_combine(c, i, s_red[w], __float_as_int(s_red[32 + w]));
+}
+
+__device__ __forceinline__ float block_sum(float v, float *s_red) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if (lane == 0) s_red[wid] = v;
+    __syncthreads();
+    float s = s_red[0];
+    for (int w = 1; w < nw; ++w) s += s_red[w];
+    return s;
+}
+
+// ---------------------------------------------------------------- rollout kernel ---------------------------
+// Shared memory layout (floats): best[P] | sigma[P] | state[24] | ref[12] | stance[4H] | ref_fz[H] | q[H] |
+// index[H] (int) | mgk[8] | red[64] | w[T] | eps[P*T]  (eps column t belongs to thread t: conflict-free).
+__host__ __device__ inline int rollout_smem_floats(int P, int H, int T) {
+    return 2 * P + 24 + 12 + 4 * H + 3 * H + 8 + 64 + T + P * T;
+}
+
+template <int PARAM, bool GA>
+__global__ void k_rollout(const __grid_constant__ DevCfg c, const RolloutArgs a) {
+    extern __shared__ float smem[];
+    const int P = c.P, H = c.H, T = blockDim.x, t = threadIdx.x;
+    float *s_best = smem;
+    float *s_sigma = s_best + P;
+    float *s_state = s_sigma + P;
+    float *s_ref = s_state + 24;
+    float *s_stance = s_ref + 12;
+    float *s_reffz = s_stance + 4 * H;
+    float *s_q = s_reffz + H;
+    int *s_index = reinterpret_cast<int *>(s_q + H);
+    float *s_mgk = s_q + 2 * H;
+    float *s_red = s_mgk + 8;
+    float *s_w = s_red + 64;
+    float *s_eps = s_w + T;
+
+    const int r = blockIdx.y;
+    const int i = blockIdx.x * T + t;
+    const bool valid = i < a.n;
+
+    // ---- stage the per-robot problem
+    for (int p = t; p < P; p += T) {
+        s_best[p] = a.costs_only ? 0.f : a.best[(size_t)r * P + p];
+        s_sigma[p] = (c.method == QPMPC_METHOD_CEM && a.sigma) ? a.sigma[(size_t)r * P + p] : 0.f;
+    }
+    for (int k = t; k < 24; k += T) s_state[k] = a.state[r * 24 + k];
+    for (int k = t; k < 12; k += T) s_ref[k] = a.reference[r * 24 + k];
+    if (!GA) {
+        for (int k = t; k < 4 * H; k += T) s_stance[k] = a.contact[(size_t)r * 4 * H + k];
+        for (int n = t; n < H; n += T) {
+            const float *cs = a.contact + (size_t)r * 4 * H;
+            const float nst = ((cs[n] + cs[H + n]) + cs[2 * H + n]) + cs[3 * H + n];
+            s_reffz[n] = c.mg / nst;
+            const int idx = chunk_index(c, (float)n);
+            s_index[n] = idx;
+            s_q[n] = chunk_tau(c, (float)n, (float)H, idx);
+        }
+    } else if (t < 5) {
+        s_mgk[t] = c.mg / (float)t;
+    }
+    __syncthreads();
+
+    // ---- this thread's noise row -> shared column t
+    const uint32_t robot = (uint32_t)r;
+    if (a.eps) {
+        const float *src = a.eps + ((size_t)r * a.n + (size_t)blockIdx.x * T) * P;
+        const int rows = min(T, a.n - blockIdx.x * T);
+        for (int e = t; e < rows * P; e += T) s_eps[(e % P) * T + e / P] = src[e];
+        __syncthreads();
+    } else if (valid) {
+        for (int g = 0; g < P / 4; ++g) {
+            const float4 e = noise_group(c, a.key, s_sigma, i, g, robot);
+            s_eps[(4 * g + 0) * T + t] = e.x;
+            s_eps[(4 * g + 1) * T + t] = e.y;
+            s_eps[(4 * g + 2) * T + t] = e.z;
+            s_eps[(4 * g + 3) * T + t] = e.w;
+        }
+    }
+
+    // ---- rollout
+    float cost = INFINITY;
+    if (valid) {
+        const int np = c.np;
+        auto par = [&](int leg, int j) { return s_best[leg * np + j] + s_eps[(leg * np + j) * T + t]; };
+        if (GA) {
+            float timing[4];
+#pragma unroll
+            for (int l = 0; l < 4; ++l) timing[l] = a.timing[r * 4 + l];
+            const float freq = a.freqs ? a.freqs[(size_t)r * a.n + i]
+                                       : freq_sample(c, a.key, i, robot, a.nominal[r], a.oswing[r]);
+            cost = rollout_gait_adaptive<PARAM>(c, s_state, s_ref, s_mgk, timing, freq, par);
+        } else {
+            const StepTables tb = {s_stance, s_reffz, s_index, s_q};
+            cost = rollout_fixed<PARAM>(c, s_state, s_ref, tb, par);
+        }
+        if (!a.costs_only) {  // centroidal_nmpc_jax.py:686-687
+            cost = isnan(cost) ? 1000000.0f : cost;
+            cost = isinf(cost) ? 1000000.0f : cost;
+        }
+        a.costs[(size_t)r * a.n + i] = cost;
+    }
+    if (a.costs_only) return;
+
+    // ---- block partials
+    float bc = cost;
+    int bi = valid ? i : 0x7fffffff;
+    block_argmin(bc, bi, s_red);
+    float *part = a.partials + ((size_t)r * a.nblk + blockIdx.x) * (PART_HDR + P);
+    if (c.method == QPMPC_METHOD_RANDOM) {
+        if (t == 0) {
+            part[0] = bc;
+            part[1] = 0.f;
+            part[2] = bc;
+            part[3] = __int_as_float(bi);
+        }
+        return;
+    }
+    // softmin numerators relative to the block minimum (merged exactly in k_finalize), :828-836
+    const float w = valid ? expf(-(cost - bc)) : 0.f;
+    s_w[t] = w;
+    const float sw = block_sum(w, s_red);  // contains the __syncthreads that publishes s_w
+    if (t == 0) {
+        part[0] = bc;
+        part[1] = sw;
+        part[2] = bc;
+        part[3] = __int_as_float(bi);
+    }
+    for (int p = t; p < P; p += T) {
+        const float *row = s_eps + p * T;
+        float acc = 0.f;
+        for (int k = 0; k < T; ++k) {
+            const int tt = (k + t) & (T - 1);  // skew: lanes of a warp hit distinct banks (T is a power of two)
+            const float wt = s_w[tt];
+            acc += (wt == 0.f) ? 0.f : wt * row[tt];  // rows of invalid threads are never initialised
+        }
+        part[PART_HDR + p] = acc;
+    }
+}
+
+// ---------------------------------------------------------------- finalize kernel --------------------------
+// Shared: best_out[P] | sel (elite indices) [cem_elite] | red[64] | misc
+template <int PARAM>
+__device__ void grf_and_prediction(const DevCfg &c, const float *s_best, const float *state, const float *contact,
+                                   qpmpc_result *out) {
+    // centroidal_nmpc_jax.py:707-784: spline at (step = 0.0, horizon_leg = 1), passed-in contact_sequence[:, 0]
+    float f[4][3], st[4];
+    const int index = chunk_index(c, 0.0f);
+    const float q = chunk_tau(c, 0.0f, 1.0f, index);
+    const CubicBasis B = cubic_basis(q);
+#pragma unroll
+    for (int l = 0; l < 4; ++l) {
+        st[l] = contact[l * c.H];
+        const float *pl = s_best + l * c.np;
+        spline_eval<PARAM>(c, [&](int j) { return pl[j]; }, 0, index, q, B, f[l]);
+    }
+    const float nst = ((st[0] + st[1]) + st[2]) + st[3];
+    shape_forces(c, f, st, c.mg / nst);
+    float x[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) x[k] = state[k];
+    srbd_step(c, x, state + 12, f, st, c.dts[0]);
+#pragma unroll
+    for (int l = 0; l < 4; ++l)
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            out->grf[3 * l + k] = f[l][k];
+            out->footholds[3 * l + k] = 0.f;
+        }
+#pragma unroll
+    for (int k = 0; k < 12; ++k) {
+        out->predicted_state[k] = x[k];
+        out->predicted_state[12 + k] = state[12 + k];
+    }
+}
+
+__global__ void __launch_bounds__(FIN_THREADS) k_finalize(const __grid_constant__ DevCfg c, const FinalizeArgs a) {
+    extern __shared__ float smem[];
+    const int P = c.P, N = c.N, t = threadIdx.x, r = blockIdx.x;
+    float *s_best = smem;
+    float *s_red = s_best + P;
+    int *s_sel = reinterpret_cast<int *>(s_red + 64);
+    const float *part = a.partials + (size_t)r * a.nblk * (PART_HDR + P);
+    const int stride = PART_HDR + P;
+    const uint32_t robot = (uint32_t)r;
+
+    // global minimum / first argmin over the block partials (nanargmin: lowest index among equal minima)
+    float bc = INFINITY;
+    int bi = 0x7fffffff;
+    for (int b = t; b < a.nblk; b += blockDim.x)
+        argmin_combine(bc, bi, part[(size_t)b * stride + 2], __float_as_int(part[(size_t)b * stride + 3]));
+    block_argmin(bc, bi, s_red);
+
+    if (c.method == QPMPC_METHOD_RANDOM) {  // best = control_parameters_vec[best_index], :692
+        for (int p = t; p < P; p += blockDim.x) {
+            float e;
+            if (a.eps) {
+                e = a.eps[((size_t)r * N + bi) * P + p];
+            } else {
+                const float4 v = noise_group(c, a.key, nullptr, bi, p >> 2, robot);
+                const int k = p & 3;
+                e = k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w));
+            }
+            s_best[p] = __fadd_rn(a.best[(size_t)r * P + p], e);
+        }
+    } else {  // best += sum_i w_i eps_i, w = softmin(costs), :828-836
+        float den = 0.f;
+        for (int b = 0; b < a.nblk; ++b) den += part[(size_t)b * stride + 1] * expf(-(part[(size_t)b * stride] - bc));
+        for (int p = t; p < P; p += blockDim.x) {
+            float num = 0.f;
+            for (int b = 0; b < a.nblk; ++b) {
+                const float sc = expf(-(part[(size_t)b * stride] - bc));
+                num += (sc == 0.f) ? 0.f : sc * part[(size_t)b * stride + PART_HDR + p];
+            }
+            s_best[p] = a.best[(size_t)r * P + p] + num / den;
+        }
+    }
+    __syncthreads();
+    for (int p = t; p < P; p += blockDim.x) a.best_out[(size_t)r * P + p] = s_best[p];
+
+    qpmpc_result *out = a.result + r;
+    if (t == 0) {
+        out->best_cost = bc;
+        out->best_index = bi;
+        out->reserved = 0;
+        float bf;
+        if (c.ga)
+            bf = a.freqs ? a.freqs[(size_t)r * N + bi] : freq_sample(c, a.key, bi, robot, a.nominal[r], a.oswing[r]);
+        else
+            bf = (c.method == QPMPC_METHOD_CEM) ? 1.65f : 1.4f;  // centroidal_nmpc_jax.py:786,930,1083
+        out->best_freq = bf;
+        const float *state = a.state + r * 24;
+        const float *contact = a.contact + (size_t)r * 4 * c.H;
+        if (c.param == QPMPC_PARAM_ZERO_ORDER)
+            grf_and_prediction<QPMPC_PARAM_ZERO_ORDER>(c, s_best, state, contact, out);
+        else if (c.param == QPMPC_PARAM_LINEAR)
+            grf_and_prediction<QPMPC_PARAM_LINEAR>(c, s_best, state, contact, out);
+        else
+            grf_and_prediction<QPMPC_PARAM_CUBIC>(c, s_best, state, contact, out);
+    }
+
+    if (c.method != QPMPC_METHOD_CEM || a.sigma_out == nullptr) return;
+    // ---- CEM: elites = argsort(costs)[:K] (stable: ties by index), new sigma from their noise rows,
+    // centroidal_nmpc_jax.py:1075-1081 (K=10, sqrt, clip [0.2,5]) / ..._gait_adaptive.py:1115-1121 (K=200, no sqrt, [0.5,3])
+    const int K = min(c.cem_elite, N);
+    const float *costs = a.costs + (size_t)r * N;
+    float lc = -INFINITY;
+    int li = -1;
+    for (int k = 0; k < K; ++k) {
+        float mc = INFINITY;
+        int mi = 0x7fffffff;
+        for (int i = t; i < N; i += blockDim.x) {
+            const float ci = costs[i];
+            if (ci > lc || (ci == lc && i > li)) argmin_combine(mc, mi, ci, i);
+        }
+        block_argmin(mc, mi, s_red);
+        if (t == 0) s_sel[k] = mi;
+        lc = mc;
+        li = mi;
+    }
+    __syncthreads();
+    for (int p = t; p < P; p += blockDim.x) {
+        float mean = 0.f;
+        for (int pass = 0; pass < 2; ++pass) {
+            float acc = 0.f;
+            for (int k = 0; k < K; ++k) {
+                const int i = s_sel[k];
+                float e;
+                if (a.eps) {
+                    e = a.eps[((size_t)r * N + i) * P + p];
+                } else {
+                    const float4 v = noise_group(c, a.key, a.sigma + (size_t)r * P, i, p >> 2, robot);
+                    const int kk = p & 3;
+                    e = kk == 0 ? v.x : (kk == 1 ? v.y : (kk == 2 ? v.z : v.w));
+                }
+                acc += pass == 0 ? e : (e - mean) * (e - mean);
+            }
+            if (pass == 0) mean = acc / (float)K;
+            else {
+                float v = acc / (float)(K - 1) + 1e-8f;
+                if (c.cem_sqrt) v = sqrtf(v);
+                v = v > c.cem_hi ? c.cem_hi : v;
+                v = v < c.cem_lo ? c.cem_lo : v;
+                a.sigma_out[(size_t)r * P + p] = v;
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------- noise dump -------------------------------
+__global__ void k_dump_noise(const __grid_constant__ DevCfg c, NoiseKey key, uint32_t robot, const float *sigma,
+                             float nominal, int oswing, float *eps_out, float *freqs_out) {
+    const int G = c.P / 4;
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx < (long long)c.N * G) {
+        const int i = (int)(idx / G), g = (int)(idx % G);
+        const float4 e = noise_group(c, key, sigma, i, g, robot);
+        reinterpret_cast<float4 *>(eps_out)[idx] = e;
+    }
+    if (freqs_out && c.ga && idx < c.N) freqs_out[idx] = freq_sample(c, key, (int)idx, robot, nominal, oswing);
+}
+
+}  // namespace qp
+
+// ================================================================ host side ================================
+using namespace qp;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string &msg) {
+    g_err = msg;
+    return code;
+}
+#define CU(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess)                                                                           \
+            return fail(QPMPC_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));               \
+    } while (0)
+
+struct qpmpc_handle {
+    qpmpc_config cfg;
+    DevCfg dc;
+    int device;
+    cudaStream_t stream;
+    int T_single, T_batch;
+    size_t max_smem;
+    // single-robot staging: one pinned input block, one pinned output block
+    float *h_in, *d_in;
+    float *h_out, *d_out;
+    size_t in_floats, out_floats;
+    float *d_costs;     // [max_robots * N]
+    float *d_partials;  // [max_robots * nblk_max * (4 + P)]
+    size_t partial_floats;
+    int64_t launches;
+};
+
+static int num_params_of(const qpmpc_config &c) {
+    if (c.parametrization == QPMPC_PARAM_LINEAR) return (c.num_splines + 1) * 3 * 4;
+    if (c.parametrization == QPMPC_PARAM_CUBIC) return 4 * 3 * c.num_splines * 4;
+    return c.horizon * 3 * 4;
+}
+
+// centroidal_model_jax.py:67-91 evaluated in float32 (same cofactor order as the reference's inertia inverse)
+static void inverse3(const float A[9], float out[9]) {
+    const float a11 = A[0], a12 = A[1], a13 = A[2], a21 = A[3], a22 = A[4], a23 = A[5], a31 = A[6], a32 = A[7],
+                a33 = A[8];
+    const float det = a11 * (a33 * a22 - a32 * a23) - a21 * (a33 * a12 - a32 * a13) + a31 * (a23 * a12 - a22 * a13);
+    out[0] = (a33 * a22 - a32 * a23) / det;
+    out[1] = -(a33 * a12 - a32 * a13) / det;
+    out[2] = (a23 * a12 - a22 * a13) / det;
+    out[3] = -(a33 * a21 - a31 * a23) / det;
+    out[4] = (a33 * a11 - a31 * a13) / det;
+    out[5] = -(a23 * a11 - a21 * a13) / det;
+    out[6] = (a32 * a21 - a31 * a22) / det;
+    out[7] = -(a32 * a11 - a31 * a12) / det;
+    out[8] = (a22 * a11 - a21 * a12) / det;
+}
+
+typedef void (*rollout_fn)(const DevCfg, const RolloutArgs);
+static rollout_fn pick_rollout(int param, int ga) {
+    switch (param * 2 + (ga ? 1 : 0)) {
+        case 0: return k_rollout<QPMPC_PARAM_ZERO_ORDER, false>;
+        case 1: return k_rollout<QPMPC_PARAM_ZERO_ORDER, true>;
+        case 2: return k_rollout<QPMPC_PARAM_LINEAR, false>;
+        case 3: return k_rollout<QPMPC_PARAM_LINEAR, true>;
+        case 4: return k_rollout<QPMPC_PARAM_CUBIC, false>;
+        default: return k_rollout<QPMPC_PARAM_CUBIC, true>;
+    }
+}
+
+static int pick_threads(const qpmpc_handle *h, long long total_rollouts) {
+    // enough blocks to cover the 148 SMs several times -> 128-thread blocks; otherwise 64 (latency regime)
+    int T = total_rollouts >= 148LL * 128 * 8 ? 128 : 64;
+    while (T > 32 && (size_t)rollout_smem_floats(h->dc.P, h->dc.H, T) * 4 > h->max_smem) T >>= 1;
+    return T;
+}
+
+extern "C" const char *qpmpc_last_error(void) { return g_err.c_str(); }
+#define QPMPC_STR2(x) #x
+#define QPMPC_STR(x) QPMPC_STR2(x)
+extern "C" const char *qpmpc_version(void) { return "qpmpc-b200 0.1 (sm_100a, cudart " QPMPC_STR(CUDART_VERSION) ")"; }
+
+extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
+    if (!cfg || !out) return fail(QPMPC_E_ARG, "null argument");
+    *out = nullptr;
+    const qpmpc_config &c = *cfg;
+    if (c.horizon < 1 || c.horizon > QPMPC_MAX_H) return fail(QPMPC_E_ARG, "horizon out of range [1, 32]");
+    if (c.parametrization < 0 || c.parametrization > 2) return fail(QPMPC_E_ARG, "unknown control_parametrization");
+    if (c.sampling_method < 0 || c.sampling_method > 2) return fail(QPMPC_E_ARG, "unknown sampling_method");
+    if (c.num_splines < 1 || c.num_splines > MAX_SPLINES) return fail(QPMPC_E_ARG, "num_splines out of range [1, 16]");
+    if (c.num_parallel_computations < 1) return fail(QPMPC_E_ARG, "num_parallel_computations must be >= 1");
+    if (c.max_robots < 1) return fail(QPMPC_E_ARG, "max_robots must be >= 1");
+    const int P = num_params_of(c);
+    if (P > QPMPC_MAX_P) return fail(QPMPC_E_ARG, "too many control parameters");
+    if (c.gait_adaptive && (c.num_step_freq < 1 || c.num_step_freq > QPMPC_MAX_FREQ))
+        return fail(QPMPC_E_ARG, "num_step_freq out of range [1, 8]");
+    if (c.sampling_method == QPMPC_METHOD_CEM && c.cem_elite < 2) return fail(QPMPC_E_ARG, "cem_elite must be >= 2");
+
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(QPMPC_E_NODEVICE, "no CUDA device: this library has no CPU fallback");
+    }
+    if (c.device < 0 || c.device >= ndev) return fail(QPMPC_E_ARG, "device ordinal out of range");
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, c.device));
+    if (prop.major != 10) return fail(QPMPC_E_NODEVICE, std::string("device is ") + prop.name + " (sm_" + std::to_string(prop.major) + std::to_string(prop.minor) + "); kernels are built for sm_100a only");
+    CU(cudaSetDevice(c.device));
+
+    qpmpc_handle *h = new (std::nothrow) qpmpc_handle();
+    if (!h) return fail(QPMPC_E_ARG, "out of host memory");
+    h->cfg = c;
+    h->device = c.device;
+    h->launches = 0;
+    DevCfg &d = h->dc;
+    memset(&d, 0, sizeof d);
+    d.H = c.horizon; d.param = c.parametrization; d.S = c.num_splines; d.ga = c.gait_adaptive ? 1 : 0;
+    d.method = c.sampling_method; d.N = c.num_parallel_computations; d.P = P; d.np = P / 4;
+    d.mass = c.mass; d.inv_mass = 1.0f / c.mass; d.mg = (float)((double)c.mass * 9.81);
+    memcpy(d.I, c.inertia, sizeof d.I);
+    inverse3(c.inertia, d.Iinv);
+    d.mu = c.mu; d.fzmin = c.f_z_min; d.fzmax = c.f_z_max;
+    memcpy(d.dts, c.dts, sizeof d.dts);
+    memcpy(d.q, c.q_diag, sizeof d.q);
+    d.duty = c.duty_factor; d.mpc_dt = c.mpc_dt;
+    memcpy(d.sig_rs, c.sigma_random_sampling, sizeof d.sig_rs);
+    d.sig_mppi = c.sigma_mppi;
+    d.nfreq = c.num_step_freq;
+    memcpy(d.freqs, c.step_freq_available, sizeof d.freqs);
+    d.cem_elite = c.cem_elite; d.cem_sqrt = c.cem_sqrt; d.cem_lo = c.cem_lo; d.cem_hi = c.cem_hi;
+    for (int k = 0; k <= d.S; ++k) d.bounds[k] = (float)((double)d.H * (double)k / (double)d.S);
+
+    h->max_smem = prop.sharedMemPerBlockOptin;
+    rollout_fn fn = pick_rollout(d.param, d.ga);
+    cudaError_t e = cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_smem);
+    if (e != cudaSuccess) { delete h; return fail(QPMPC_E_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e)); }
+    h->T_single = pick_threads(h, d.N);
+    h->T_batch = pick_threads(h, (long long)d.N * c.max_robots);
+
+    const int H = d.H;
+    h->in_floats = 24 + 24 + 4 * H + P + P + 4 + 2;  // state ref contact best sigma timing nominal oswing
+    h->out_floats = sizeof(qpmpc_result) / 4 + 2 * P;
+    const int nblk_max = (d.N + 31) / 32;
+    h->partial_floats = (size_t)c.max_robots * nblk_max * (PART_HDR + P);
+    bool ok = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaMallocHost(&h->h_in, h->in_floats * 4) == cudaSuccess &&
+              cudaMallocHost(&h->h_out, h->out_floats * 4 + (size_t)d.N * 4) == cudaSuccess &&
+              cudaMalloc(&h->d_in, h->in_floats * 4) == cudaSuccess &&
+              cudaMalloc(&h->d_out, h->out_floats * 4) == cudaSuccess &&
+              cudaMalloc(&h->d_costs, (size_t)c.max_robots * d.N * 4) == cudaSuccess &&
+              cudaMalloc(&h->d_partials, h->partial_floats * 4) == cudaSuccess;
+    if (!ok) {
+        std::string m = std::string("allocation failed: ") + cudaGetErrorString(cudaGetLastError());
+        qpmpc_destroy(h);
+        return fail(QPMPC_E_CUDA, m);
+    }
+    *out = h;
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_destroy(qpmpc_handle *h) {
+    if (!h) return QPMPC_OK;
+    cudaSetDevice(h->device);
+    if (h->stream) { cudaStreamSynchronize(h->stream); cudaStreamDestroy(h->stream); }
+    if (h->h_in) cudaFreeHost(h->h_in);
+    if (h->h_out) cudaFreeHost(h->h_out);
+    if (h->d_in) cudaFree(h->d_in);
+    if (h->d_out) cudaFree(h->d_out);
+    if (h->d_costs) cudaFree(h->d_costs);
+    if (h->d_partials) cudaFree(h->d_partials);
+    delete h;
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_num_params(const qpmpc_handle *h) { return h ? h->dc.P : QPMPC_E_ARG; }
+extern "C" void *qpmpc_stream(qpmpc_handle *h) { return h ? (void *)h->stream : nullptr; }
+extern "C" int64_t qpmpc_launch_count(const qpmpc_handle *h) { return h ? h->launches : 0; }
+
+// launches k_rollout + k_finalize for `b` on the handle's stream (no synchronisation)
+static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, uint64_t offset, int T) {
+    const DevCfg &d = h->dc;
+    const int R = b.num_robots, N = d.N, P = d.P;
+    const int nblk = (N + T - 1) / T;
+    if ((size_t)R * nblk * (PART_HDR + P) > h->partial_floats) return fail(QPMPC_E_ARG, "internal: partial buffer too small");
+    RolloutArgs ra;
+    ra.state = b.d_state; ra.reference = b.d_reference; ra.contact = b.d_contact_sequence; ra.best = b.d_best_in;
+    ra.sigma = b.d_sigma_in; ra.timing = b.d_timing; ra.nominal = b.d_nominal_freq; ra.oswing = b.d_optimize_swing;
+    ra.eps = b.d_eps; ra.freqs = b.d_freqs;
+    ra.costs = b.d_costs ? b.d_costs : h->d_costs; ra.partials = h->d_partials;
+    ra.key = NoiseKey{seed, offset}; ra.n = N; ra.costs_only = 0; ra.nblk = nblk;
+    const size_t smem = (size_t)rollout_smem_floats(P, d.H, T) * 4;
+    pick_rollout(d.param, d.ga)<<<dim3(nblk, R), T, smem, h->stream>>>(d, ra);
+    CU(cudaGetLastError());
+    FinalizeArgs fa;
+    fa.state = b.d_state; fa.reference = b.d_reference; fa.contact = b.d_contact_sequence; fa.best = b.d_best_in;
+    fa.sigma = b.d_sigma_in; fa.nominal = b.d_nominal_freq; fa.oswing = b.d_optimize_swing;
+    fa.eps = b.d_eps; fa.freqs = b.d_freqs; fa.costs = ra.costs; fa.partials = h->d_partials;
+    fa.result = b.d_result; fa.best_out = b.d_best_out; fa.sigma_out = b.d_sigma_out;
+    fa.key = ra.key; fa.nblk = nblk;
+    const size_t fsmem = (size_t)(P + 64 + (d.method == QPMPC_METHOD_CEM ? d.cem_elite : 0) + 8) * 4;
+    k_finalize<<<R, FIN_THREADS, fsmem, h->stream>>>(d, fa);
+    CU(cudaGetLastError());
+    h->launches += 2;
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_solve_batched(qpmpc_handle *h, const qpmpc_batch *batch, uint64_t seed, uint64_t offset) {
+    if (!h || !batch) return fail(QPMPC_E_ARG, "null argument");
+    const qpmpc_batch &b = *batch;
+    if (b.num_robots < 1 || b.num_robots > h->cfg.max_robots) return fail(QPMPC_E_ARG, "num_robots exceeds max_robots");
+    if (!b.d_state || !b.d_reference || !b.d_contact_sequence || !b.d_best_in || !b.d_result || !b.d_best_out)
+        return fail(QPMPC_E_ARG, "missing device pointer in qpmpc_batch");
+    if (h->dc.method == QPMPC_METHOD_CEM && !b.d_sigma_in) return fail(QPMPC_E_ARG, "cem_mppi needs d_sigma_in");
+    if (h->dc.ga && !b.d_timing) return fail(QPMPC_E_ARG, "gait adaptive needs d_timing");
+    if (h->dc.ga && !b.d_freqs && (!b.d_nominal_freq || !b.d_optimize_swing))
+        return fail(QPMPC_E_ARG, "gait adaptive needs d_nominal_freq and d_optimize_swing");
+    CU(cudaSetDevice(h->device));
+    return launch_solve(h, b, seed, offset, pick_threads(h, (long long)h->dc.N * b.num_robots));
+}
+
+extern "C" int qpmpc_solve(qpmpc_handle *h, const float *state, const float *reference, const float *contact_sequence,
+                           const float *best_in, uint64_t seed, uint64_t offset, const float *timing,
+                           float nominal_step_frequency, int32_t optimize_swing, const float *sigma_in,
+                           const float *d_eps, const float *d_freqs, qpmpc_result *out, float *best_out,
+                           float *sigma_out, float *costs_out) {
+    if (!h || !state || !reference || !contact_sequence || !best_in || !out || !best_out)
+        return fail(QPMPC_E_ARG, "null argument");
+    const DevCfg &d = h->dc;
+    const int H = d.H, P = d.P, N = d.N;
+    if (d.method == QPMPC_METHOD_CEM && !sigma_in) return fail(QPMPC_E_ARG, "cem_mppi needs sigma_in");
+    if (d.ga && !timing) return fail(QPMPC_E_ARG, "gait adaptive needs timing");
+    CU(cudaSetDevice(h->device));
+    // pack the inputs into one pinned block -> one H2D copy
+    float *p = h->h_in;
+    const size_t o_state = 0, o_ref = 24, o_contact = 48, o_best = o_contact + 4 * H, o_sigma = o_best + P,
+                 o_timing = o_sigma + P, o_nominal = o_timing + 4, o_oswing = o_nominal + 1;
+    memcpy(p + o_state, state, 24 * 4);
+    memcpy(p + o_ref, reference, 24 * 4);
+    memcpy(p + o_contact, contact_sequence, (size_t)4 * H * 4);
+    memcpy(p + o_best, best_in, (size_t)P * 4);
+    if (sigma_in) memcpy(p + o_sigma, sigma_in, (size_t)P * 4); else memset(p + o_sigma, 0, (size_t)P * 4);
+    if (timing) memcpy(p + o_timing, timing, 16); else memset(p + o_timing, 0, 16);
+    p[o_nominal] = nominal_step_frequency;
+    memcpy(p + o_oswing, &optimize_swing, 4);
+    CU(cudaMemcpyAsync(h->d_in, h->h_in, h->in_floats * 4, cudaMemcpyHostToDevice, h->stream));
+    qpmpc_batch b;
+    memset(&b, 0, sizeof b);
+    b.num_robots = 1;
+    b.d_state = h->d_in + o_state; b.d_reference = h->d_in + o_ref; b.d_contact_sequence = h->d_in + o_contact;
+    b.d_best_in = h->d_in + o_best; b.d_sigma_in = h->d_in + o_sigma; b.d_timing = h->d_in + o_timing;
+    b.d_nominal_freq = h->d_in + o_nominal; b.d_optimize_swing = reinterpret_cast<const int32_t *>(h->d_in + o_oswing);
+    b.d_eps = d_eps; b.d_freqs = d_freqs;
+    const size_t res_floats = sizeof(qpmpc_result) / 4;
+    b.d_result = reinterpret_cast<qpmpc_result *>(h->d_out);
+    b.d_best_out = h->d_out + res_floats;
+    b.d_sigma_out = (d.method == QPMPC_METHOD_CEM) ? h->d_out + res_floats + P : nullptr;
+    b.d_costs = h->d_costs;
+    int rc = launch_solve(h, b, seed, offset, h->T_single);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(h->h_out, h->d_out, h->out_floats * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (costs_out) CU(cudaMemcpyAsync(h->h_out + h->out_floats, h->d_costs, (size_t)N * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    memcpy(out, h->h_out, sizeof(qpmpc_result));
+    memcpy(best_out, h->h_out + res_floats, (size_t)P * 4);
+    if (sigma_out && d.method == QPMPC_METHOD_CEM) memcpy(sigma_out, h->h_out + res_floats + P, (size_t)P * 4);
+    if (costs_out) memcpy(costs_out, h->h_out + h->out_floats, (size_t)N * 4);
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_rollout_costs(qpmpc_handle *h, const float *state, const float *reference,
+                                   const float *contact_sequence, const float *timing, const float *d_params,
+                                   const float *d_freqs, int32_t n, float *d_costs) {
+    if (!h || !state || !reference || !contact_sequence || !d_params || !d_costs) return fail(QPMPC_E_ARG, "null argument");
+    if (n < 1) return fail(QPMPC_E_ARG, "n must be >= 1");
+    const DevCfg &d = h->dc;
+    if (d.ga && (!timing || !d_freqs)) return fail(QPMPC_E_ARG, "gait adaptive needs timing and d_freqs");
+    CU(cudaSetDevice(h->device));
+    const int H = d.H, P = d.P;
+    float *p = h->h_in;
+    memcpy(p, state, 24 * 4);
+    memcpy(p + 24, reference, 24 * 4);
+    memcpy(p + 48, contact_sequence, (size_t)4 * H * 4);
+    const size_t o_timing = 48 + 4 * H + 2 * P;
+    if (timing) memcpy(p + o_timing, timing, 16); else memset(p + o_timing, 0, 16);
+    CU(cudaMemcpyAsync(h->d_in, h->h_in, h->in_floats * 4, cudaMemcpyHostToDevice, h->stream));
+    RolloutArgs ra;
+    memset(&ra, 0, sizeof ra);
+    ra.state = h->d_in; ra.reference = h->d_in + 24; ra.contact = h->d_in + 48; ra.timing = h->d_in + o_timing;
+    ra.eps = d_params; ra.freqs = d_freqs; ra.costs = d_costs; ra.n = n; ra.costs_only = 1;
+    const int T = pick_threads(h, n);
+    ra.nblk = (n + T - 1) / T;
+    const size_t smem = (size_t)rollout_smem_floats(P, H, T) * 4;
+    pick_rollout(d.param, d.ga)<<<dim3(ra.nblk, 1), T, smem, h->stream>>>(d, ra);
+    CU(cudaGetLastError());
+    h->launches += 1;
+    CU(cudaStreamSynchronize(h->stream));
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_generate_noise(qpmpc_handle *h, uint64_t seed, uint64_t offset, int32_t robot, const float *sigma_in,
+                                    float nominal_step_frequency, int32_t optimize_swing, float *d_eps_out,
+                                    float *d_freqs_out) {
+    if (!h || !d_eps_out) return fail(QPMPC_E_ARG, "null argument");
+    const DevCfg &d = h->dc;
+    if (d.method == QPMPC_METHOD_CEM && !sigma_in) return fail(QPMPC_E_ARG, "cem_mppi needs sigma_in");
+    CU(cudaSetDevice(h->device));
+    const float *d_sigma = nullptr;
+    if (d.method == QPMPC_METHOD_CEM) {
+        const size_t o_sigma = 48 + 4 * d.H + d.P;
+        memcpy(h->h_in + o_sigma, sigma_in, (size_t)d.P * 4);
+        CU(cudaMemcpyAsync(h->d_in + o_sigma, h->h_in + o_sigma, (size_t)d.P * 4, cudaMemcpyHostToDevice, h->stream));
+        d_sigma = h->d_in + o_sigma;
+    }
+    const long long total = (long long)d.N * (d.P / 4);
+    const int threads = 256;
+    const long long blocks = (total + threads - 1) / threads;
+    k_dump_noise<<<(unsigned)blocks, threads, 0, h->stream>>>(d, NoiseKey{seed, offset}, (uint32_t)robot, d_sigma,
+                                                             nominal_step_frequency, optimize_swing, d_eps_out,
+                                                             d_freqs_out);
+    CU(cudaGetLastError());
+    h->launches += 1;
+    CU(cudaStreamSynchronize(h->stream));
+    return QPMPC_OK;
+}
