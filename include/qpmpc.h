@@ -148,6 +148,15 @@ int qpmpc_rollout_costs(qpmpc_handle *h, const float *state, const float *refere
 int qpmpc_generate_noise(qpmpc_handle *h, uint64_t seed, uint64_t offset, int32_t robot, const float *sigma_in,
                          float nominal_step_frequency, int32_t optimize_swing, float *d_eps_out, float *d_freqs_out);
 
+/* Measurement hooks (no reference counterpart: the reference only has wall-clock prints,
+ * interfaces/wb_interface.py:231,241).  With profiling on, each solve records CUDA events around its two kernels on
+ * the handle's stream; qpmpc_profile_last waits for the last solve and returns both durations in milliseconds. */
+int qpmpc_set_profiling(qpmpc_handle *h, int32_t on);
+int qpmpc_profile_last(qpmpc_handle *h, float *rollout_ms, float *finalize_ms);
+/* FP32 FMA-chain microbenchmark on `device`: the measured CUDA-core peak (TFLOP/s, FMA = 2) used as the denominator of
+ * the rollout kernel's roofline (nothing here is a dense contraction, so tensor-core peaks do not apply). */
+int qpmpc_measure_fp32_peak(int32_t device, float *tflops);
+
 #ifdef __cplusplus
 }
 #endif

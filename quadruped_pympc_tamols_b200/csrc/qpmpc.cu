@@ -454,6 +454,8 @@ struct qpmpc_handle {
     float *d_partials;  // [max_robots * nblk_max * (4 + P)]
     size_t partial_floats;
     int64_t launches;
+    int profiling;                  // qpmpc_set_profiling: record events around each kernel of a solve
+    cudaEvent_t ev[3];
 };
 
 static int num_params_of(const qpmpc_config &c) {
@@ -534,6 +536,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     h->cfg = c;
     h->device = c.device;
     h->launches = 0;
+    h->profiling = 0;
     DevCfg &d = h->dc;
     memset(&d, 0, sizeof d);
     d.H = c.horizon; d.param = c.parametrization; d.S = c.num_splines; d.ga = c.gait_adaptive ? 1 : 0;
@@ -565,6 +568,8 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     const int nblk_max = (d.N + 31) / 32;
     h->partial_floats = (size_t)c.max_robots * nblk_max * (PART_HDR + P);
     bool ok = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaEventCreate(&h->ev[0]) == cudaSuccess && cudaEventCreate(&h->ev[1]) == cudaSuccess &&
+              cudaEventCreate(&h->ev[2]) == cudaSuccess &&
               cudaMallocHost(&h->h_in, h->in_floats * 4) == cudaSuccess &&
               cudaMallocHost(&h->h_out, h->out_floats * 4 + (size_t)d.N * 4) == cudaSuccess &&
               cudaMalloc(&h->d_in, h->in_floats * 4) == cudaSuccess &&
@@ -584,6 +589,8 @@ extern "C" int qpmpc_destroy(qpmpc_handle *h) {
     if (!h) return QPMPC_OK;
     cudaSetDevice(h->device);
     if (h->stream) { cudaStreamSynchronize(h->stream); cudaStreamDestroy(h->stream); }
+    for (int k = 0; k < 3; ++k)
+        if (h->ev[k]) cudaEventDestroy(h->ev[k]);
     if (h->h_in) cudaFreeHost(h->h_in);
     if (h->h_out) cudaFreeHost(h->h_out);
     if (h->d_in) cudaFree(h->d_in);
@@ -611,8 +618,10 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
     ra.costs = b.d_costs ? b.d_costs : h->d_costs; ra.partials = h->d_partials;
     ra.key = NoiseKey{seed, offset}; ra.n = N; ra.costs_only = 0; ra.nblk = nblk;
     const size_t smem = (size_t)rollout_smem_floats(P, d.H, T) * 4;
+    if (h->profiling) CU(cudaEventRecord(h->ev[0], h->stream));
     pick_rollout(d.param, d.ga)<<<dim3(nblk, R), T, smem, h->stream>>>(d, ra);
     CU(cudaGetLastError());
+    if (h->profiling) CU(cudaEventRecord(h->ev[1], h->stream));
     FinalizeArgs fa;
     fa.state = b.d_state; fa.reference = b.d_reference; fa.contact = b.d_contact_sequence; fa.best = b.d_best_in;
     fa.sigma = b.d_sigma_in; fa.nominal = b.d_nominal_freq; fa.oswing = b.d_optimize_swing;
@@ -622,6 +631,7 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
     const size_t fsmem = (size_t)(P + 64 + (d.method == QPMPC_METHOD_CEM ? d.cem_elite : 0) + 8) * 4;
     k_finalize<<<R, FIN_THREADS, fsmem, h->stream>>>(d, fa);
     CU(cudaGetLastError());
+    if (h->profiling) CU(cudaEventRecord(h->ev[2], h->stream));
     h->launches += 2;
     return QPMPC_OK;
 }
@@ -742,5 +752,71 @@ extern "C" int qpmpc_generate_noise(qpmpc_handle *h, uint64_t seed, uint64_t off
     CU(cudaGetLastError());
     h->launches += 1;
     CU(cudaStreamSynchronize(h->stream));
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_set_profiling(qpmpc_handle *h, int32_t on) {
+    if (!h) return fail(QPMPC_E_ARG, "null argument");
+    h->profiling = on ? 1 : 0;
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_profile_last(qpmpc_handle *h, float *rollout_ms, float *finalize_ms) {
+    if (!h || !rollout_ms || !finalize_ms) return fail(QPMPC_E_ARG, "null argument");
+    if (!h->profiling) return fail(QPMPC_E_ARG, "profiling is off (qpmpc_set_profiling)");
+    CU(cudaSetDevice(h->device));
+    CU(cudaEventSynchronize(h->ev[2]));
+    CU(cudaEventElapsedTime(rollout_ms, h->ev[0], h->ev[1]));
+    CU(cudaEventElapsedTime(finalize_ms, h->ev[1], h->ev[2]));
+    return QPMPC_OK;
+}
+
+// FP32 FMA-chain microbenchmark: the measured denominator of the rollout kernel's roofline.
+namespace qp {
+__global__ void k_fma_peak(float *out, int iters, float a, float b) {
+    float x0 = threadIdx.x, x1 = x0 + 1.f, x2 = x0 + 2.f, x3 = x0 + 3.f, x4 = x0 + 4.f, x5 = x0 + 5.f, x6 = x0 + 6.f,
+          x7 = x0 + 7.f;
+#pragma unroll 4
+    for (int i = 0; i < iters; ++i) {
+        x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+        x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+    }
+    const float s = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+    if (s == 123.456f) out[0] = s;
+}
+}  // namespace qp
+
+extern "C" int qpmpc_measure_fp32_peak(int32_t device, float *tflops) {
+    if (!tflops) return fail(QPMPC_E_ARG, "null argument");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+        cudaGetLastError();
+        return fail(QPMPC_E_NODEVICE, "no such CUDA device");
+    }
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    float *d_out = nullptr;
+    CU(cudaMalloc(&d_out, 4));
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 1 << 15;
+    float best = 0.f;
+    for (int rep = 0; rep < 6; ++rep) {
+        CU(cudaEventRecord(e0, 0));
+        k_fma_peak<<<blocks, threads>>>(d_out, iters, 0.999f, 0.001f);
+        CU(cudaEventRecord(e1, 0));
+        CU(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, e0, e1));
+        const double fl = 2.0 * 8.0 * (double)iters * (double)blocks * threads;
+        const float tf = (float)(fl / (ms * 1e-3) / 1e12);
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d_out);
+    *tflops = best;
     return QPMPC_OK;
 }

@@ -1,0 +1,276 @@
+"""GPU parity tests of the sampling-MPC path: the CUDA kernels, called through the C ABI (include/qpmpc.h), against
+(a) the committed fixtures made from the reference's own source and (b) the C oracle on seeded inputs.
+
+Tolerances (BASELINE.json north_star): rollout costs 1e-4 relative (FP32), updated control sequence 1e-3 absolute.
+"""
+import os
+import zlib
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+
+from oracle import srbd_oracle as so  # noqa: E402  (checker only)
+from quadruped_pympc_tamols_b200 import _cabi  # noqa: E402
+from tests.util import fixture_kwargs, rel_err, sampling_fixtures  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+COST_RTOL = 1e-4
+BEST_ATOL = 1e-3
+
+ROBOTS = {
+    "aliengo": (24.637, [[0.2310941359705289, -0.0014987128245817424, -0.021400468992761768],
+                         [-0.0014987128245817424, 1.4485084687476608, 0.0004641447134275615],
+                         [-0.021400468992761768, 0.0004641447134275615, 1.503217877350808]], 0.33, (0.24, 0.15)),
+    "go2": (15.019, [[1.58460467e-01, 1.21660000e-04, -1.55444692e-02],
+                     [1.21660000e-04, 4.68645637e-01, -3.12000000e-05],
+                     [-1.55444692e-02, -3.12000000e-05, 5.24474661e-01]], 0.27, (0.19, 0.13)),
+    "hyqreal1": (108.40, [[4.55031444e+00, 2.75249434e-03, -5.11957307e-01],
+                          [2.75249434e-03, 2.02411774e+01, -7.38560592e-04],
+                          [-5.11957307e-01, -7.38560592e-04, 2.14269772e+01]], 0.55, (0.44, 0.30)),
+}
+GAITS = {"trot": ([0.5, 1.0, 1.0, 0.5], 1.4, 0.65), "pace": ([0.8, 0.3, 0.8, 0.3], 1.4, 0.7),
+         "bound": ([0.5, 0.5, 0.0, 0.0], 1.8, 0.65)}
+
+
+def synth_problem(robot, gait, rng, horizon=12, dt=0.02):
+    """SURVEY 8(d) C1 state / reference distribution + a host gait clock contact sequence."""
+    _, _, h, (hx, hy) = ROBOTS[robot]
+    st = np.zeros(24)
+    st[0:3] = [0.0, 0.0, h + rng.normal(0, 0.02)]
+    st[3:6] = rng.normal(0, 0.3, 3)
+    st[6:9] = rng.normal(0, 0.05, 3)
+    st[9:12] = rng.normal(0, 0.3, 3)
+    hips = np.array([[hx, hy, 0], [hx, -hy, 0], [-hx, hy, 0], [-hx, -hy, 0]], float)
+    st[12:24] = (hips + np.c_[rng.normal(0, 0.03, (4, 2)), np.zeros(4)]).ravel()
+    ref = np.zeros(24)
+    ref[2] = h
+    ref[3] = rng.uniform(-0.5, 0.5)
+    ref[12:24] = st[12:24]
+    offs, freq, duty = GAITS[gait]
+    t = (np.array(offs) + rng.uniform()) % 1.0
+    timing = t.copy()
+    seq = np.zeros((4, horizon))
+    for n in range(horizon):
+        seq[:, n] = (t < duty).astype(float)
+        t = (t + dt * freq) % 1.0
+    return st, ref, seq, timing, freq
+
+
+def dev(a):
+    return torch.as_tensor(np.ascontiguousarray(a, np.float32), device="cuda")
+
+
+def compare(r, o, method, tag=""):
+    assert rel_err(r["costs"], o["costs"]) < COST_RTOL, tag
+    assert r["best_index"] == o["best_index"] or abs(o["costs"][r["best_index"]] - o["best_cost"]) <= COST_RTOL * abs(o["best_cost"]), tag
+    assert abs(float(r["best_cost"]) - float(o["best_cost"])) <= COST_RTOL * abs(float(o["best_cost"])), tag
+    assert np.max(np.abs(r["best"] - o["best"])) < BEST_ATOL, tag
+    assert np.max(np.abs(r["grf"] - o["grf"])) < BEST_ATOL * 10, tag
+    assert rel_err(r["predicted_state"], o["predicted_state"], 1e-2) < 1e-4, tag
+    assert abs(float(r["best_freq"]) - float(o["best_freq"])) < 1e-6, tag
+    assert np.all(r["footholds"] == 0)
+    if method == "cem_mppi":
+        assert rel_err(r["sigma"], o["sigma"]) < 1e-3, tag
+
+
+@pytest.mark.parametrize("path", sampling_fixtures(), ids=lambda p: os.path.basename(p)[9:-4])
+def test_cuda_matches_reference_fixture(path):
+    g = np.load(path)
+    kw = fixture_kwargs(g)
+    method = str(g["method"])
+    n = int(g["n"])
+    h = _cabi.Handle(_cabi.make_config(sampling_method=method, num_parallel_computations=n,
+                                       step_freq_available=tuple(g["step_freq_available"]), **kw))
+    best = g["best_in"]
+    for it in range(int(g["iterations"])):
+        t = f"it{it}_"
+        eps = dev(g[t + "eps"])
+        freqs = dev(g[t + "freqs"]) if t + "freqs" in g else None
+        r = h.solve(g["state"], g["reference"], g["contact_sequence"], best, seed=0, offset=it, timing=g["timing"],
+                    nominal_freq=float(g["nominal_freq"]), optimize_swing=int(g["optimize_swing"]),
+                    sigma_in=g[t + "sigma_in"] if method == "cem_mppi" else None, d_eps=eps.data_ptr(),
+                    d_freqs=freqs.data_ptr() if freqs is not None else None)
+        assert rel_err(r["costs"], g[t + "costs"]) < COST_RTOL
+        assert np.max(np.abs(r["best"] - g[t + "best_out"])) < BEST_ATOL
+        assert np.max(np.abs(r["grf"] - g[t + "grf"])) < BEST_ATOL * 10
+        assert rel_err(r["predicted_state"], g[t + "predicted_state"], 1e-2) < 1e-4
+        assert abs(float(r["best_cost"]) - float(g[t + "best_cost"])) <= COST_RTOL * abs(float(g[t + "best_cost"]))
+        if t + "best_freq" in g:
+            assert abs(float(r["best_freq"]) - float(g[t + "best_freq"])) < 1e-6
+        if method == "cem_mppi":
+            assert rel_err(r["sigma"], g[t + "sigma_out"]) < 1e-3
+        best = g[t + "best_out"]
+    h.close()
+
+
+CASES = [  # (robot, gait, method, parametrization, gait_adaptive, N)  -- BASELINE.json configs C1..C3 at full size first
+    ("aliengo", "trot", "random_sampling", "zero_order", False, 10000),
+    ("go2", "bound", "mppi", "cubic_spline", True, 10000),
+    ("hyqreal1", "pace", "cem_mppi", "cubic_spline", False, 10000),
+    ("aliengo", "trot", "mppi", "zero_order", False, 4097),
+    ("aliengo", "trot", "mppi", "linear_spline", False, 1000),
+    ("go2", "trot", "random_sampling", "linear_spline", True, 3001),
+    ("go2", "trot", "mppi", "zero_order", True, 2048),
+    ("go2", "trot", "cem_mppi", "cubic_spline", True, 1500),
+    ("hyqreal1", "pace", "cem_mppi", "zero_order", False, 777),
+    ("aliengo", "trot", "random_sampling", "cubic_spline", False, 31),
+]
+
+
+@pytest.mark.parametrize("robot,gait,method,param,ga,n", CASES)
+def test_philox_solve_matches_oracle_on_same_noise(robot, gait, method, param, ga, n):
+    """In-kernel Philox path: dump the noise the solve draws for (seed, offset), feed it to the oracle, compare
+    every output; two iterations so CEM's sigma carry and the MPPI best carry are exercised."""
+    rng = np.random.default_rng(zlib.crc32(repr((robot, gait, method, param, ga, n)).encode()))
+    mass, inertia, _, _ = ROBOTS[robot]
+    kw = dict(mass=mass, inertia=np.array(inertia), parametrization=param, gait_adaptive=ga)
+    h = _cabi.Handle(_cabi.make_config(sampling_method=method, num_parallel_computations=n, **kw))
+    ocfg = so.make_cfg(**kw)
+    P = h.P
+    st, ref, seq, timing, nominal = synth_problem(robot, gait, rng)
+    best = (2.0 * rng.normal(size=P)).astype(np.float32)
+    sigma = np.full(P, 3.0, np.float32)
+    d_eps = torch.empty((n, P), dtype=torch.float32, device="cuda")
+    d_freqs = torch.empty(n, dtype=torch.float32, device="cuda")
+    for it in range(2):
+        oswing = 1 - it
+        h.generate_noise(42, it, d_eps.data_ptr(), d_freqs.data_ptr(), sigma_in=sigma if method == "cem_mppi" else None,
+                         nominal_freq=nominal, optimize_swing=oswing)
+        eps = d_eps.cpu().numpy()
+        freqs = d_freqs.cpu().numpy() if ga else None
+        assert np.all(eps[0] == 0)
+        r = h.solve(st, ref, seq, best, seed=42, offset=it, timing=timing, nominal_freq=nominal, optimize_swing=oswing,
+                    sigma_in=sigma if method == "cem_mppi" else None)
+        o = so.solve(ocfg, method, st, ref, seq, best, eps, timing=timing, freqs=freqs, fast=False)
+        compare(r, o, method, tag=f"it{it}")
+        # the supplied-noise path must agree with the Philox path bit for bit on the costs
+        r2 = h.solve(st, ref, seq, best, seed=42, offset=it, timing=timing, nominal_freq=nominal, optimize_swing=oswing,
+                     sigma_in=sigma if method == "cem_mppi" else None, d_eps=d_eps.data_ptr(),
+                     d_freqs=d_freqs.data_ptr() if ga else None)
+        assert np.array_equal(r["costs"], r2["costs"])
+        assert np.max(np.abs(r["best"] - r2["best"])) < 1e-5
+        best = r["best"]
+        if method == "cem_mppi":
+            sigma = r["sigma"]
+    h.close()
+
+
+def test_noise_statistics_and_structure():
+    mass, inertia, _, _ = ROBOTS["aliengo"]
+    n = 9001
+    for method in ("random_sampling", "mppi", "cem_mppi"):
+        h = _cabi.Handle(_cabi.make_config(mass=mass, inertia=inertia, sampling_method=method, parametrization="zero_order",
+                                           num_parallel_computations=n))
+        d_eps = torch.empty((n, h.P), dtype=torch.float32, device="cuda")
+        sig = np.linspace(0.5, 4.0, h.P).astype(np.float32)
+        h.generate_noise(7, 3, d_eps.data_ptr(), sigma_in=sig if method == "cem_mppi" else None)
+        e = d_eps.cpu().numpy().astype(np.float64)
+        assert np.all(e[0] == 0)
+        if method == "random_sampling":  # centroidal_nmpc_jax.py:647-677
+            t = n // 3
+            a, b, u = e[1:1 + t], e[1 + t:1 + 2 * t], e[1 + 2 * t:]
+            assert np.allclose(a / 0.2, b / 3.0, rtol=1e-5, atol=1e-6)  # same key -> same normals upstream
+            assert abs(a.std() / 0.2 - 1) < 0.01 and abs(a.mean()) < 0.002
+            assert u.min() >= -10 and u.max() < 10 and abs(u.mean()) < 0.05 and abs(u.std() - 20 / np.sqrt(12)) < 0.05
+        elif method == "mppi":
+            z = e[1:] / 3.0
+            assert abs(z.mean()) < 0.005 and abs(z.std() - 1) < 0.005
+            assert abs(np.mean(z ** 4) - 3) < 0.05  # kurtosis of a normal
+            assert abs(np.corrcoef(z[:, 0], z[:, 1])[0, 1]) < 0.05
+        else:
+            z = e[1:] / sig
+            assert abs(z.std() - 1) < 0.005
+        d2 = torch.empty_like(d_eps)
+        h.generate_noise(7, 4, d2.data_ptr(), sigma_in=sig if method == "cem_mppi" else None)
+        assert not torch.equal(d_eps[1:], d2[1:])  # with_newkey (offset + 1) gives a fresh stream
+        h.close()
+
+
+@pytest.mark.parametrize("param,ga", [("zero_order", False), ("linear_spline", True), ("cubic_spline", False), ("cubic_spline", True)])
+def test_rollout_costs_matches_oracle(param, ga):
+    """jit_vectorized_rollout: explicit parameter matrix -> raw costs, incl. a diverging (non-finite) rollout."""
+    rng = np.random.default_rng(11)
+    mass, inertia, _, _ = ROBOTS["go2"]
+    kw = dict(mass=mass, inertia=np.array(inertia), parametrization=param, gait_adaptive=ga)
+    n = 5000
+    h = _cabi.Handle(_cabi.make_config(sampling_method="mppi", num_parallel_computations=n, **kw))
+    ocfg = so.make_cfg(**kw)
+    st, ref, seq, timing, _ = synth_problem("go2", "trot", rng)
+    params = (20 * rng.normal(size=(n, h.P))).astype(np.float32)
+    freqs = rng.choice([1.4, 2.0, 2.4], size=n).astype(np.float32)
+    d_params, d_freqs = dev(params), dev(freqs)
+    d_costs = torch.empty(n, dtype=torch.float32, device="cuda")
+    h.rollout_costs(st, ref, seq, d_params.data_ptr(), n, d_costs.data_ptr(), timing=timing,
+                    d_freqs=d_freqs.data_ptr() if ga else None)
+    c = d_costs.cpu().numpy()
+    o = so.rollout_costs(ocfg, st, ref, seq, params, timing=timing, freqs=freqs if ga else None)
+    assert rel_err(c, o) < COST_RTOL
+    h.close()
+
+
+def test_known_answers_on_gpu():
+    """(i) rest -> fz = mg/4; (ii) swing leg force exactly 0; (iii) flight -> free fall; (vi) MPPI with
+    equal costs -> mean of eps; (vii) sample 0 reproduces the previous best."""
+    mass, inertia, _, _ = ROBOTS["aliengo"]
+    n = 256
+    h = _cabi.Handle(_cabi.make_config(mass=mass, inertia=inertia, sampling_method="mppi", parametrization="zero_order",
+                                       num_parallel_computations=n))
+    st = np.zeros(24)
+    st[2] = 0.33
+    st[12:24] = np.array([[0.24, 0.15, 0], [0.24, -0.15, 0], [-0.24, 0.15, 0], [-0.24, -0.15, 0]]).ravel()
+    zero = dev(np.zeros((n, h.P)))
+    r = h.solve(st, st.copy(), np.ones((4, 12)), np.zeros(h.P), 0, 0, d_eps=zero.data_ptr())
+    assert np.allclose(r["grf"].reshape(4, 3)[:, 2], mass * 9.81 / 4, rtol=1e-6) and np.all(r["costs"] < 1e-6)
+    seq = np.ones((4, 12))
+    seq[1] = 0
+    r = h.solve(st, st.copy(), seq, np.ones(h.P), 0, 0, d_eps=zero.data_ptr())
+    assert np.all(r["grf"][3:6] == 0) and np.allclose(r["grf"].reshape(4, 3)[[0, 2, 3], 2], mass * 9.81 / 3 + 1, rtol=1e-6)
+    eps = np.random.default_rng(0).normal(size=(n, h.P)).astype(np.float32)
+    eps[0] = 0
+    r = h.solve(st, st.copy(), np.zeros((4, 12)), np.zeros(h.P), 0, 0, d_eps=dev(eps).data_ptr())
+    assert np.all(r["grf"] == 0) and abs(r["predicted_state"][5] + 9.81 * 0.02) < 1e-6
+    assert np.allclose(r["costs"], r["costs"][0]) and np.allclose(r["best"], eps.mean(0), atol=1e-5)
+    best = np.random.default_rng(1).normal(size=h.P).astype(np.float32)
+    r1 = h.solve(st, st.copy(), np.ones((4, 12)), best, 5, 0)
+    r2 = h.solve(st, st.copy(), np.ones((4, 12)), best, 6, 9)
+    assert r1["costs"][0] == r2["costs"][0] and not np.array_equal(r1["costs"][1:], r2["costs"][1:])
+    h.close()
+
+
+def test_batched_robots_match_single_solves():
+    """qpmpc_solve_batched: R independent robots in one launch == R single solves with the same Philox subsequence
+    (robot r draws from subsequence r) and == the oracle on the dumped noise."""
+    rng = np.random.default_rng(3)
+    mass, inertia, _, _ = ROBOTS["aliengo"]
+    R, n = 5, 1024
+    kw = dict(mass=mass, inertia=np.array(inertia), parametrization="zero_order")
+    h = _cabi.Handle(_cabi.make_config(sampling_method="mppi", num_parallel_computations=n, max_robots=R, **kw))
+    ocfg = so.make_cfg(**kw)
+    P = h.P
+    probs = [synth_problem("aliengo", "trot", rng) for _ in range(R)]
+    bests = (rng.normal(size=(R, P))).astype(np.float32)
+    d_state, d_ref = dev(np.stack([p[0] for p in probs])), dev(np.stack([p[1] for p in probs]))
+    d_seq, d_best = dev(np.stack([p[2] for p in probs])), dev(bests)
+    d_res = torch.zeros((R, _cabi.RESULT_FLOATS), dtype=torch.float32, device="cuda")
+    d_bo = torch.zeros((R, P), dtype=torch.float32, device="cuda")
+    d_costs = torch.zeros((R, n), dtype=torch.float32, device="cuda")
+    b = _cabi.QpmpcBatch(num_robots=R, d_state=d_state.data_ptr(), d_reference=d_ref.data_ptr(),
+                         d_contact_sequence=d_seq.data_ptr(), d_best_in=d_best.data_ptr(), d_result=d_res.data_ptr(),
+                         d_best_out=d_bo.data_ptr(), d_costs=d_costs.data_ptr())
+    h.solve_batched(b, 99, 1)
+    torch.cuda.synchronize()
+    res, bo, costs = d_res.cpu().numpy(), d_bo.cpu().numpy(), d_costs.cpu().numpy()
+    d_eps = torch.empty((n, P), dtype=torch.float32, device="cuda")
+    for r in range(R):
+        h.generate_noise(99, 1, d_eps.data_ptr(), robot=r)
+        o = so.solve(ocfg, "mppi", probs[r][0], probs[r][1], probs[r][2], bests[r], d_eps.cpu().numpy())
+        assert rel_err(costs[r], o["costs"]) < COST_RTOL
+        assert np.max(np.abs(bo[r] - o["best"])) < BEST_ATOL
+        assert np.max(np.abs(res[r, :12] - o["grf"])) < BEST_ATOL * 10
+        assert rel_err(res[r, 24:48], o["predicted_state"], 1e-2) < 1e-4
+        assert abs(res[r, 48] - o["best_cost"]) <= COST_RTOL * abs(o["best_cost"])
+    assert not np.array_equal(costs[0, 1:], costs[1, 1:])
+    h.close()
