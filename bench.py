@@ -1,0 +1,338 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the sampling-MPC hot path on B200 (contract: see DESIGN.md "Measurement").
+
+Workload (BASELINE.json configs[1], "C2"): Go2, bound gait, MPPI, cubic-spline parameters (P = 96), per-sample
+step-frequency adaptation, 10,000 rollouts over a 12-step horizon.  One "step" = one MPC solve of that robot.
+
+  value        rollouts/s with the inputs resident in HBM (qpmpc_solve_batched on device tensors), device-timed
+               per step with CUDA events on the handle's stream; L2 is flushed between timed steps.
+  e2e          the same metric through the reference-facing call qpmpc_solve with HOST buffers: H2D copy of the
+               inputs, both kernels, D2H copy of the result, stream sync -- wall clock per call; p50 latency reported.
+  roofline     k_rollout against the FP32 CUDA-core peak measured in this run (no tensor cores: nothing on this path
+               is a dense contraction); algorithmic FLOPs per rollout from SURVEY.md 8(d).
+  cpu_baseline the CPU oracle port (-O3, OpenMP over rollouts, all host threads) on the same workload.
+  batched      BASELINE.json configs[4] ("C5", 8192 robots x 1024 rollouts, MPPI zero-order), sharded by robot over
+               the ranks with no collective on the control path.
+
+`--impl reference` times the reference's CPU implementation of the path.  jax is not installable here, so that arm
+is the oracle port of the reference's jax code (kind "port"), all host threads.
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+GO2 = dict(mass=15.019, inertia=np.array([[1.58460467e-01, 1.21660000e-04, -1.55444692e-02],
+                                          [1.21660000e-04, 4.68645637e-01, -3.12000000e-05],
+                                          [-1.55444692e-02, -3.12000000e-05, 5.24474661e-01]]))
+ALIENGO = dict(mass=24.637, inertia=np.array([[0.2310941359705289, -0.0014987128245817424, -0.021400468992761768],
+                                              [-0.0014987128245817424, 1.4485084687476608, 0.0004641447134275615],
+                                              [-0.021400468992761768, 0.0004641447134275615, 1.503217877350808]]))
+N_ROLLOUTS = 10000
+FLOP_PER_ROLLOUT = {"zero_order": 4380, "linear_spline": 4956, "cubic_spline": 7260, "cubic_spline_ga": 7550}
+WORKLOAD = "C2: go2 bound, MPPI, cubic_spline (P=96), per-sample step-frequency adaptation, 10000 rollouts x horizon 12"
+
+
+def synth_problem(rng, h, hip, gait=([0.5, 0.5, 0.0, 0.0], 1.8, 0.65), horizon=12, dt=0.02):
+    """SURVEY 8(d) state / reference distribution and a host gait-clock contact sequence."""
+    hx, hy = hip
+    st = np.zeros(24)
+    st[0:3] = [0.0, 0.0, h + rng.normal(0, 0.02)]
+    st[3:6], st[6:9], st[9:12] = rng.normal(0, 0.3, 3), rng.normal(0, 0.05, 3), rng.normal(0, 0.3, 3)
+    hips = np.array([[hx, hy, 0], [hx, -hy, 0], [-hx, hy, 0], [-hx, -hy, 0]], float)
+    st[12:24] = (hips + np.c_[rng.normal(0, 0.03, (4, 2)), np.zeros(4)]).ravel()
+    ref = np.zeros(24)
+    ref[2], ref[3], ref[12:24] = h, rng.uniform(-0.5, 0.5), st[12:24]
+    offs, freq, duty = gait
+    t = (np.array(offs) + rng.uniform()) % 1.0
+    timing = t.copy()
+    seq = np.zeros((4, horizon))
+    for n in range(horizon):
+        seq[:, n] = (t < duty).astype(float)
+        t = (t + dt * freq) % 1.0
+    return st.astype(np.float32), ref.astype(np.float32), seq.astype(np.float32), timing.astype(np.float32), freq
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+# ------------------------------------------------------------------------------------------- reference arm (CPU)
+def cpu_solve_loop(steps, warmup, seed=0):
+    """The CPU port of compute_control_mppi on the C2 workload: noise generation + 10k rollouts + update per step."""
+    from oracle import srbd_oracle as so
+    cfg = so.make_cfg(parametrization="cubic_spline", gait_adaptive=True, **GO2)
+    rng = np.random.default_rng(seed)
+    st, ref, seq, timing, nominal = synth_problem(rng, 0.27, (0.19, 0.13))
+    P = so.num_params(cfg)
+    best = np.zeros(P, np.float32)
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        eps = so.fill_noise(N_ROLLOUTS, P, 3.0, it, fast=True)
+        freqs = np.asarray([1.4, 2.0, 2.4], np.float32)[(np.arange(N_ROLLOUTS) * 7 + it) % 3]
+        r = so.solve(cfg, "mppi", st, ref, seq, best, eps, timing=timing, freqs=freqs, fast=True)
+        best = r["best"]
+        if it >= warmup:
+            times.append(time.perf_counter() - t0)
+    return np.array(times), so.max_threads(True)
+
+
+def run_reference(args):
+    rank, _, world = dist_env()
+    if rank != 0:
+        return
+    steps = max(args.steps, 1)
+    times, cores = cpu_solve_loop(steps, args.warmup)
+    ms = float(times.mean() * 1e3)
+    value = N_ROLLOUTS / times.mean()
+    sample = f"{steps} full solves of the C2 workload (noise + 10000 rollouts + MPPI update each), OpenMP over rollouts"
+    line = {"impl": "reference", "metric": "rollouts/sec at 10k samples (one MPPI solve)", "value": value, "unit": "rollouts/s",
+            "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup, "ms_per_step": ms, "p50_latency_ms": float(np.median(times) * 1e3),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "note": "reference jax unavailable on this box; CPU port of the reference math (oracle/srbd_oracle.c, -O3 -fopenmp)"},
+            "cpu_baseline": {"value": value, "unit": "rollouts/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": "rollouts/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------- clocks
+class Clocks:
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz, self.h = [], set(), None, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception as e:  # noqa: BLE001
+            self.err = repr(e)
+
+    def sample(self):
+        if self.h is None:
+            return
+        nv = self.nv
+        self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+        try:
+            bits = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+        except Exception:  # noqa: BLE001
+            bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+        names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+                 0x80: "hw_power_brake_slowdown"}
+        for bit, name in names.items():
+            if bits & bit:
+                self.reasons.add(name)
+
+    def summary(self):
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------- CUDA arm
+def run_cuda(args):
+    import torch
+    from quadruped_pympc_tamols_b200 import _cabi
+    rank, local_rank, world = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return float(x)
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return float(x)
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    K, W = max(args.steps, 1), max(args.warmup, 3)
+    rng = np.random.default_rng(1000 + rank)  # each rank = an independent robot instance (batched_simulations.py style)
+    st, ref, seq, timing, nominal = synth_problem(rng, 0.27, (0.19, 0.13))
+    h = _cabi.Handle(_cabi.make_config(sampling_method="mppi", parametrization="cubic_spline", gait_adaptive=True,
+                                       num_parallel_computations=N_ROLLOUTS, device=local_rank, **GO2))
+    P = h.P
+    stream = torch.cuda.ExternalStream(h.stream, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    clocks = Clocks(local_rank)
+
+    # ---- device-resident arm
+    t_ = lambda a, dt=torch.float32: torch.as_tensor(np.ascontiguousarray(a), dtype=dt, device=dev)  # noqa: E731
+    d_state, d_ref, d_seq, d_timing = t_(st[None]), t_(ref[None]), t_(seq[None]), t_(timing[None])
+    d_nom, d_osw = t_(np.array([nominal])), t_(np.array([1]), torch.int32)
+    d_best = [torch.zeros((1, P), device=dev), torch.zeros((1, P), device=dev)]
+    d_res = torch.zeros((1, _cabi.RESULT_FLOATS), device=dev)
+    launches0 = h.launch_count
+
+    def device_step(it):
+        b = _cabi.QpmpcBatch(num_robots=1, d_state=d_state.data_ptr(), d_reference=d_ref.data_ptr(),
+                             d_contact_sequence=d_seq.data_ptr(), d_best_in=d_best[it & 1].data_ptr(),
+                             d_timing=d_timing.data_ptr(), d_nominal_freq=d_nom.data_ptr(),
+                             d_optimize_swing=d_osw.data_ptr(), d_result=d_res.data_ptr(),
+                             d_best_out=d_best[(it + 1) & 1].data_ptr())
+        h.solve_batched(b, 42, it)
+
+    with torch.cuda.stream(stream):
+        for it in range(W):
+            device_step(it)
+        barrier()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        clocks.sample()
+        for it in range(K):
+            flush.fill_(it & 0xFF)  # untimed L2 flush between timed steps
+            ev[it][0].record(stream)
+            device_step(W + it)
+            ev[it][1].record(stream)
+            if it % max(1, K // 8) == 0:
+                clocks.sample()
+        clocks.sample()
+        barrier()
+    dev_ms = np.array([a.elapsed_time(b) for a, b in ev])
+    launches = h.launch_count - launches0 - 2 * W
+    total_ms = max_over_ranks(float(dev_ms.sum()))
+    value = N_ROLLOUTS * K * world / (total_ms * 1e-3)
+
+    # ---- roofline of the dominant kernel (k_rollout), events around each kernel inside the solve
+    h.set_profiling(True)
+    roll = []
+    with torch.cuda.stream(stream):
+        for it in range(min(K, 200)):
+            flush.fill_(it & 0xFF)
+            device_step(W + K + it)
+            roll.append(h.profile_last())
+    h.set_profiling(False)
+    roll = np.array(roll)
+    fp32_peak = _cabi.measure_fp32_peak(local_rank)
+    flop = FLOP_PER_ROLLOUT["cubic_spline_ga"] * N_ROLLOUTS
+    ach = flop / (roll[:, 0].mean() * 1e-3) / 1e12
+
+    # ---- end to end through the host-buffer C ABI call (H2D + kernels + D2H + sync), wall clock
+    best = np.zeros(P, np.float32)
+    e2e = []
+    for it in range(W + K):
+        t0 = time.perf_counter()
+        r = h.solve(st, ref, seq, best, 42, it, timing=timing, nominal_freq=nominal, optimize_swing=1, want_costs=False)
+        dt_ = time.perf_counter() - t0
+        best = r["best"]
+        if it >= W:
+            e2e.append(dt_)
+    e2e = np.array(e2e)
+    e2e_total = max_over_ranks(float(e2e.sum()))
+    e2e_value = N_ROLLOUTS * K * world / e2e_total
+    in_bytes = 4 * (24 + 24 + 4 * 12 + 2 * P + 4 + 2)
+    out_bytes = 4 * (_cabi.RESULT_FLOATS + 2 * P)
+
+    # ---- batched robots C5 (sharded by robot, no collective): extra information, not the headline
+    batched = None
+    if not args.no_batched:
+        batched = run_batched(torch, _cabi, dev, local_rank, rank, world, barrier, max_over_ranks, fp32_peak)
+
+    # ---- CPU baseline (rank 0, N=1 only): bounded sample of the same workload
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        nsolve = 300
+        times, cores = cpu_solve_loop(nsolve, 3)
+        cpu = {"value": N_ROLLOUTS / float(times.mean()), "unit": "rollouts/s", "cores": cores, "kind": "port",
+               "sample": f"{nsolve} full C2 solves (noise + 10000 rollouts + MPPI update), {times.sum():.1f} s of CPU work",
+               "p50_latency_ms": float(np.median(times) * 1e3)}
+
+    clk = clocks.summary()
+    if rank == 0:
+        line = {"metric": "rollouts/sec at 10k samples (one MPPI solve)", "value": value, "unit": "rollouts/s", "n_gpus": world,
+                "steps": K, "warmup": W, "ms_per_step": float(total_ms / K), "p50_latency_ms": float(np.median(dev_ms)),
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": WORKLOAD, "noise": "in-kernel Philox4x32-10 + Box-Muller", "l2": "flushed (256 MiB write) between timed steps",
+                           "multi_gpu": "one independent robot instance per rank, no collective on the control path"},
+                "e2e": {"value": e2e_value, "unit": "rollouts/s", "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": out_bytes,
+                        "p50_latency_ms": float(np.median(e2e) * 1e3), "p99_latency_ms": float(np.percentile(e2e, 99) * 1e3),
+                        "api": "qpmpc_solve (host buffers; costs[N] left on the device as upstream)"},
+                "gpu_launches": int(launches),
+                "roofline": {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak,
+                             "traffic": None, "kernel": "k_rollout<cubic,gait_adaptive>", "launch_ms": float(roll[:, 0].mean()),
+                             "finalize_ms": float(roll[:, 1].mean()), "flop_per_rollout": FLOP_PER_ROLLOUT["cubic_spline_ga"],
+                             "peak_source": "FP32 FMA-chain microbenchmark in this run (qpmpc_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 figure",
+                             "note": "10k rollouts = 75.5 MFLOP: latency-bound at this size; see batched.roofline for the throughput regime"},
+                "cpu_baseline": cpu, "clocks": clk, "batched": batched}
+        print(json.dumps(line))
+    h.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_batched(torch, _cabi, dev, local_rank, rank, world, barrier, max_over_ranks, fp32_peak, robots_total=8192, n=1024):
+    R = robots_total // world
+    rng = np.random.default_rng(77 + rank)
+    h = _cabi.Handle(_cabi.make_config(sampling_method="mppi", parametrization="zero_order", num_parallel_computations=n,
+                                       max_robots=R, device=local_rank, **ALIENGO))
+    P = h.P
+    probs = [synth_problem(rng, 0.33, (0.24, 0.15), gait=([0.5, 1.0, 1.0, 0.5], 1.4, 0.65)) for _ in range(64)]
+    idx = rng.integers(0, 64, R)
+    t_ = lambda a: torch.as_tensor(np.ascontiguousarray(a), dtype=torch.float32, device=dev)  # noqa: E731
+    d_state = t_(np.stack([probs[i][0] for i in idx]) + rng.normal(0, 1e-3, (R, 24)).astype(np.float32))
+    d_ref, d_seq = t_(np.stack([probs[i][1] for i in idx])), t_(np.stack([probs[i][2] for i in idx]))
+    d_best = [torch.zeros((R, P), device=dev), torch.zeros((R, P), device=dev)]
+    d_res = torch.zeros((R, _cabi.RESULT_FLOATS), device=dev)
+    stream = torch.cuda.ExternalStream(h.stream, device=dev)
+    h.set_profiling(True)
+    steps, roll = 10, []
+    with torch.cuda.stream(stream):
+        for it in range(3 + steps):
+            b = _cabi.QpmpcBatch(num_robots=R, d_state=d_state.data_ptr(), d_reference=d_ref.data_ptr(),
+                                 d_contact_sequence=d_seq.data_ptr(), d_best_in=d_best[it & 1].data_ptr(),
+                                 d_result=d_res.data_ptr(), d_best_out=d_best[(it + 1) & 1].data_ptr())
+            if it == 3:
+                barrier()
+            h.solve_batched(b, 7, it)
+            if it >= 3:
+                roll.append(h.profile_last())
+        barrier()
+    roll = np.array(roll)
+    step_ms = max_over_ranks(float((roll[:, 0] + roll[:, 1]).mean()))
+    roll_ms = max_over_ranks(float(roll[:, 0].mean()))
+    ach = FLOP_PER_ROLLOUT["zero_order"] * R * n / (roll_ms * 1e-3) / 1e12
+    h.close()
+    return {"workload": f"C5: {robots_total} robots x {n} rollouts, MPPI zero_order (P=144), aliengo trot; {R} robots per rank",
+            "value": robots_total * n / (step_ms * 1e-3), "unit": "rollouts/s", "robot_solves_per_s": robots_total / (step_ms * 1e-3),
+            "ms_per_step": step_ms, "scaling": "strong",
+            "roofline": {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak,
+                         "kernel": "k_rollout<zero_order,fixed>", "launch_ms": roll_ms, "flop_per_rollout": FLOP_PER_ROLLOUT["zero_order"]}}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
+    ap.add_argument("--no-batched", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_cuda(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -409,6 +409,36 @@ void oracle_solve(const oracle_cfg *c, int method, const float *state, const flo
     free(params);
 }
 
+/* ---- CPU noise for the timed baseline only (bench.py): Philox4x32-10 + Box-Muller, the same construction the CUDA
+ * path uses, so the CPU arm pays for its random numbers as the reference's jax.random.normal call does
+ * (centroidal_nmpc_jax.py:806-812).  Not used by any parity check (those feed explicit noise). */
+static void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
+    for (int r = 0; r < 10; ++r) {
+        uint64_t p0 = (uint64_t)0xD2511F53u * c[0], p1 = (uint64_t)0xCD9E8D57u * c[2];
+        uint32_t n0 = (uint32_t)(p1 >> 32) ^ c[1] ^ k0, n1 = (uint32_t)p1, n2 = (uint32_t)(p0 >> 32) ^ c[3] ^ k1, n3 = (uint32_t)p0;
+        c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+}
+void oracle_fill_noise(float *eps, int N, int P, float sigma, uint64_t seed) {
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < N; ++i) {
+        float *row = eps + (size_t)i * P;
+        if (i == 0) { memset(row, 0, (size_t)P * sizeof(float)); continue; }
+        for (int g = 0; g < P / 4; ++g) {
+            uint32_t c[4] = {(uint32_t)g, (uint32_t)i, 0u, (uint32_t)(seed >> 32)};
+            philox4x32_10(c, (uint32_t)seed, 0x1234567u);
+            for (int h = 0; h < 2; ++h) {
+                float u1 = ((float)(c[2 * h] >> 8) + 0.5f) * 5.9604644775390625e-08f;
+                float u2 = (float)(c[2 * h + 1] >> 8) * 5.9604644775390625e-08f;
+                float r = sqrtf(-2.0f * logf(u1)), a = 6.2831853071795864f * u2;
+                row[4 * g + 2 * h] = sigma * r * cosf(a);
+                row[4 * g + 2 * h + 1] = sigma * r * sinf(a);
+            }
+        }
+    }
+}
+
 int oracle_sizeof_cfg(void) { return (int)sizeof(oracle_cfg); }
 int oracle_sizeof_result(void) { return (int)sizeof(oracle_result); }
 int oracle_max_threads(void) {

@@ -126,3 +126,12 @@ def solve(cfg, method, state, ref, contact_seq, best, eps, timing=None, freqs=No
 
 def max_threads(fast=True):
     return _lib(fast).oracle_max_threads()
+
+
+def fill_noise(n, p, sigma, seed, fast=True):
+    """Multithreaded CPU noise for bench.py's timed CPU arm (row 0 zero, sigma applied)."""
+    eps = np.empty((n, p), np.float32)
+    lib = _lib(fast)
+    lib.oracle_fill_noise.argtypes = [C.POINTER(C.c_float), C.c_int, C.c_int, C.c_float, C.c_uint64]
+    lib.oracle_fill_noise(_p(eps), n, p, float(sigma), int(seed))
+    return eps
