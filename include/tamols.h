@@ -1,0 +1,124 @@
+/*
+ * include/tamols.h -- C ABI of the B200 (sm_100a) TAMOLS foothold-scoring hot path.
+ *
+ * The reference (Magicyw/Quadruped-PyMPC-TAMOLS) has no FFI layer: its boundary for this path is the Python class
+ * `VisualFootholdAdaptation` with adaptation_strategy='tamols'
+ * (quadruped_pympc/helpers/visual_foothold_adaptation.py:38-72, 86-99, 153-231), whose candidate loop (:188-206) is a
+ * Python `for` over every heightmap cell with scipy cKDTree nearest-neighbour height queries (:21-35).
+ * The entry points below replace that loop; the Python drop-in class in
+ * quadruped_pympc_tamols_b200/helpers/visual_foothold_adaptation.py binds them with ctypes (INTEGRATION.md shows the
+ * stub a reference maintainer would add).
+ *
+ * Data model.  A height map is a regular planar grid: the world xy of cell (r, c) is
+ *     origin + r * row_axis + c * col_axis          (orthogonal axes; the grid may be rotated by the sensor yaw)
+ * and its height is heights[map][r][c].  This is the layout of gym_quadruped's HeightMap.data[r, c, 0, :] = (x, y, z)
+ * as the reference consumes it (:27-28).  The reference's KD-tree nearest-neighbour query is replaced by the analytic
+ * nearest cell of that grid (round to nearest in grid coordinates, clamped to the candidate window), which is the same
+ * cell except for queries exactly equidistant from two cells (documented tie rule).
+ * One "leg job" = one leg of one robot: a candidate window of one map, the seed foothold, the hip, and the robot state
+ * the cost terms need.  Every cell of the window is a candidate (:240-243); the winner is the FIRST minimum in
+ * row-major order (:203-206).
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success and a negative TAMOLS_E_* code
+ * otherwise, with a message from tamols_last_error().  Pointers named d_* are DEVICE pointers, all others HOST.
+ * All arithmetic is FP64 like the reference (numpy defaults); heights may be stored as f64 or f32.
+ */
+#ifndef TAMOLS_H
+#define TAMOLS_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { TAMOLS_OK = 0, TAMOLS_E_ARG = -1, TAMOLS_E_CUDA = -2, TAMOLS_E_NODEVICE = -3 };
+enum { TAMOLS_F64 = 0, TAMOLS_F32 = 1 };
+enum {
+    TAMOLS_FLAG_HAS_VELOCITY = 1, /* forward_vel is not None (:388, :567) */
+    TAMOLS_FLAG_STABILITY = 2     /* base_position and current_feet_pos given and the leg is in swing (:631-658) */
+};
+
+/* cfg.simulation_params['tamols_params'] as read with .get(key, default) on every call (:298-305, :377-378, :438-439,
+ * :537, :636, :671, :214-215) plus the literals of the scoring code. */
+typedef struct tamols_params {
+    double gradient_delta;            /* 'gradient_delta' (0.04) :438,:484 */
+    double slope_threshold;           /* 'slope_threshold' (0.7) :439 */
+    double weight_edge_avoidance;     /* default 15.0 :298 (config.py:217 sets 10.0) */
+    double weight_roughness;          /* :299 */
+    double weight_deviation;          /* :300 */
+    double weight_nominal_kinematic;  /* :302 */
+    double weight_reference_tracking; /* :303 */
+    double weight_stability;          /* :305 */
+    double stability_margin;          /* :636 */
+    double estimated_swing_time;      /* :671 */
+    double h_des;                     /* :537 */
+    double l_min, l_max;              /* tamols_params['l_min'|'l_max'][robot] :377-378 */
+    double stance_duration;           /* literal 0.3 :387 */
+    double sensor_offset;             /* literal 0.02 added by FastHeightMap.get_height :35 */
+    double foot_clearance;            /* literal 0.005 :192 */
+    double collision_margin;          /* literal 0.02 :417 */
+    double collision_alphas[5];       /* np.linspace(0.2, 0.8, 5) :402 (host computes them so the doubles are numpy's) */
+    double constraint_box_dx;         /* :214 */
+    double constraint_box_dy;         /* :215 */
+} tamols_params;
+
+/* One leg of one robot (the body of `for leg_id, leg_name in enumerate(legs_order)`, :164-228). */
+typedef struct tamols_leg_job {
+    int32_t map;             /* which height map */
+    int32_t r0, c0, nr, nc;  /* candidate window = the per-leg heightmap the reference receives */
+    int32_t flags;           /* TAMOLS_FLAG_* */
+    double origin[2];        /* xy of cell (0,0) of the map */
+    double row_axis[2];      /* xy step between rows */
+    double col_axis[2];      /* xy step between columns */
+    double seed[3];          /* reference_footholds[leg] (:165) */
+    double hip[3];           /* hip_positions[leg] (:166) */
+    double diag_foot[2];     /* current_feet_pos[diagonal leg][:2] (:640-664) */
+    double base_xy[2];       /* base_position[:2] (:675) */
+    double vel[3];           /* forward_vel (:154) */
+} tamols_leg_job;
+
+typedef struct tamols_result {
+    int32_t best_index;  /* row-major index inside the window, -1 when no candidate is finite (fallback branch :223-228) */
+    int32_t num_finite;  /* number of candidates with a finite score */
+    double best_score;
+    double best_xyz[3];  /* best_candidate (:206) */
+    double vertex1[3];   /* footholds_constraints[leg][0] (:216-218) */
+    double vertex2[3];   /* footholds_constraints[leg][1] (:219-221) */
+} tamols_result;
+
+typedef struct tamols_handle tamols_handle;
+
+/* VisualFootholdAdaptation.__init__ for 'tamols' (:55-57).  max_jobs bounds the jobs per call. */
+int tamols_create(const tamols_params *params, int32_t device, int32_t max_jobs, tamols_handle **out);
+int tamols_destroy(tamols_handle *h);
+/* self.tamols_params is a live dict upstream; this replaces the handle's copy. */
+int tamols_set_params(tamols_handle *h, const tamols_params *params);
+const char *tamols_last_error(void);
+void *tamols_stream(tamols_handle *h);
+int64_t tamols_launch_count(const tamols_handle *h);
+
+/*
+ * The candidate loop of compute_adaptation (:164-228) for n_jobs legs in ONE launch, device buffers in and out,
+ * asynchronous on tamols_stream(h).
+ *   d_heights  [num_maps, rows, pitch] of height_dtype; pitch >= cols elements per row.  When pitch * sizeof(elem) is
+ *              a multiple of 16 and the base is 16-byte aligned the tile + halo is staged to shared memory by TMA,
+ *              otherwise by plain loads.
+ *   d_xy       optional [num_maps, rows, cols, 2] f64 candidate coordinates as stored by the sensor (:243); NULL =
+ *              computed from the job's grid.
+ *   d_jobs     [n_jobs]; d_results [n_jobs]; d_scores optional [n_jobs, scores_stride] per-candidate scores
+ *              (_compute_tamols_score, :261-373; +inf for rejected candidates), NULL to skip.
+ */
+int tamols_score_device(tamols_handle *h, const void *d_heights, int32_t height_dtype, int32_t num_maps, int32_t rows,
+                        int32_t cols, int32_t pitch, const double *d_xy, const tamols_leg_job *d_jobs, int32_t n_jobs,
+                        tamols_result *d_results, double *d_scores, int64_t scores_stride);
+
+/* Same with HOST buffers (what the Python class calls): copies heights (f64, [num_maps, rows, cols] dense), optional
+ * xy and the jobs to the device, runs the launch, copies results (and scores when not NULL) back, synchronises. */
+int tamols_score_host(tamols_handle *h, const double *heights, int32_t num_maps, int32_t rows, int32_t cols,
+                      const double *xy, const tamols_leg_job *jobs, int32_t n_jobs, tamols_result *results,
+                      double *scores, int64_t scores_stride);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TAMOLS_H */

@@ -1,0 +1,185 @@
+"""ctypes binding of the TAMOLS entry points of lib/libqpmpc_b200.so (C ABI: include/tamols.h).
+
+The only place the Python host touches native code for the TAMOLS path.  No CPU fallback: if the shared library is
+missing or no sm_100 GPU is present, calls raise `TamolsError`.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _cabi
+
+FLAG_HAS_VELOCITY = 1
+FLAG_STABILITY = 2
+F64, F32 = 0, 1
+LEGS = ("FL", "FR", "RL", "RR")
+DIAGONAL = {"FL": "RR", "FR": "RL", "RL": "FR", "RR": "FL"}  # visual_foothold_adaptation.py:640-645
+
+
+class TamolsError(RuntimeError):
+    pass
+
+
+class TamolsParams(C.Structure):
+    _fields_ = [(n, C.c_double) for n in (
+        "gradient_delta", "slope_threshold", "weight_edge_avoidance", "weight_roughness", "weight_deviation",
+        "weight_nominal_kinematic", "weight_reference_tracking", "weight_stability", "stability_margin",
+        "estimated_swing_time", "h_des", "l_min", "l_max", "stance_duration", "sensor_offset", "foot_clearance",
+        "collision_margin")] + [("collision_alphas", C.c_double * 5), ("constraint_box_dx", C.c_double),
+                                ("constraint_box_dy", C.c_double)]
+
+
+class TamolsLegJob(C.Structure):
+    _fields_ = [("map", C.c_int32), ("r0", C.c_int32), ("c0", C.c_int32), ("nr", C.c_int32), ("nc", C.c_int32),
+                ("flags", C.c_int32), ("origin", C.c_double * 2), ("row_axis", C.c_double * 2),
+                ("col_axis", C.c_double * 2), ("seed", C.c_double * 3), ("hip", C.c_double * 3),
+                ("diag_foot", C.c_double * 2), ("base_xy", C.c_double * 2), ("vel", C.c_double * 3)]
+
+
+class TamolsResult(C.Structure):
+    _fields_ = [("best_index", C.c_int32), ("num_finite", C.c_int32), ("best_score", C.c_double),
+                ("best_xyz", C.c_double * 3), ("vertex1", C.c_double * 3), ("vertex2", C.c_double * 3)]
+
+
+JOB_DTYPE = np.dtype([("map", "<i4"), ("r0", "<i4"), ("c0", "<i4"), ("nr", "<i4"), ("nc", "<i4"), ("flags", "<i4"),
+                      ("origin", "<f8", 2), ("row_axis", "<f8", 2), ("col_axis", "<f8", 2), ("seed", "<f8", 3),
+                      ("hip", "<f8", 3), ("diag_foot", "<f8", 2), ("base_xy", "<f8", 2), ("vel", "<f8", 3)])
+RESULT_DTYPE = np.dtype([("best_index", "<i4"), ("num_finite", "<i4"), ("best_score", "<f8"), ("best_xyz", "<f8", 3),
+                         ("vertex1", "<f8", 3), ("vertex2", "<f8", 3)])
+assert JOB_DTYPE.itemsize == C.sizeof(TamolsLegJob) and RESULT_DTYPE.itemsize == C.sizeof(TamolsResult)
+
+EXPORTS = ["tamols_create", "tamols_destroy", "tamols_set_params", "tamols_last_error", "tamols_stream",
+           "tamols_launch_count", "tamols_score_device", "tamols_score_host"]
+
+
+def make_params(tamols_params=None, robot_name="aliengo"):
+    """tamols_params dict -> struct with the reference's .get(key, default) defaults
+    (visual_foothold_adaptation.py:214-215, 298-305, 377-378, 438-439, 537, 636, 671)."""
+    tp = dict(tamols_params or {})
+    p = TamolsParams()
+    p.gradient_delta = float(tp.get("gradient_delta", 0.04))
+    p.slope_threshold = float(tp.get("slope_threshold", 0.7))
+    p.weight_edge_avoidance = float(tp.get("weight_edge_avoidance", 15.0))
+    p.weight_roughness = float(tp.get("weight_roughness", 10.0))
+    p.weight_deviation = float(tp.get("weight_deviation", 1.0))
+    p.weight_nominal_kinematic = float(tp.get("weight_nominal_kinematic", 20.0))
+    p.weight_reference_tracking = float(tp.get("weight_reference_tracking", 2.0))
+    p.weight_stability = float(tp.get("weight_stability", 10.0))
+    p.stability_margin = float(tp.get("stability_margin", 0.06))
+    p.estimated_swing_time = float(tp.get("estimated_swing_time", 0.25))
+    p.h_des = float(tp.get("h_des", 0.25))
+    p.l_min = float(tp.get("l_min", {}).get(robot_name, 0.15))
+    p.l_max = float(tp.get("l_max", {}).get(robot_name, 0.45))
+    p.stance_duration, p.sensor_offset, p.foot_clearance, p.collision_margin = 0.3, 0.02, 0.005, 0.02
+    p.collision_alphas[:] = [float(a) for a in np.linspace(0.2, 0.8, 5)]
+    p.constraint_box_dx = float(tp.get("constraint_box_dx", 0.05))
+    p.constraint_box_dy = float(tp.get("constraint_box_dy", 0.05))
+    return p
+
+
+def fit_grid(xy):
+    """Regular-grid description (origin, row_axis, col_axis) of sensor coordinates xy[R, C, 2]; raises when the
+    points are not a regular orthogonal grid (the analytic nearest-cell lookup needs one)."""
+    xy = np.asarray(xy, np.float64)
+    R, Cc = xy.shape[:2]
+    origin = xy[0, 0].copy()
+    row_axis = (xy[R - 1, 0] - origin) / (R - 1) if R > 1 else None
+    col_axis = (xy[0, Cc - 1] - origin) / (Cc - 1) if Cc > 1 else None
+    if row_axis is None and col_axis is None:
+        row_axis, col_axis = np.array([1.0, 0.0]), np.array([0.0, 1.0])
+    elif row_axis is None:
+        row_axis = np.array([-col_axis[1], col_axis[0]])
+    elif col_axis is None:
+        col_axis = np.array([row_axis[1], -row_axis[0]])
+    rr, cc = np.meshgrid(np.arange(R), np.arange(Cc), indexing="ij")
+    model = origin + rr[..., None] * row_axis + cc[..., None] * col_axis
+    scale = min(np.linalg.norm(row_axis), np.linalg.norm(col_axis))
+    if scale <= 0 or np.max(np.abs(model - xy)) > 1e-6 * max(scale, 1e-9) + 1e-9:
+        raise TamolsError("heightmap cells are not a regular grid: the analytic nearest-cell lookup does not apply")
+    if abs(float(row_axis @ col_axis)) > 1e-6 * scale * scale:
+        raise TamolsError("heightmap grid axes are not orthogonal")
+    return origin, row_axis, col_axis
+
+
+_BOUND = False
+
+
+def lib():
+    global _BOUND
+    L = _cabi.lib()
+    if not _BOUND:
+        vp = C.c_void_p
+        L.tamols_create.argtypes = [C.POINTER(TamolsParams), C.c_int32, C.c_int32, C.POINTER(vp)]
+        L.tamols_destroy.argtypes = [vp]
+        L.tamols_set_params.argtypes = [vp, C.POINTER(TamolsParams)]
+        L.tamols_last_error.restype = C.c_char_p
+        L.tamols_stream.argtypes = [vp]
+        L.tamols_stream.restype = vp
+        L.tamols_launch_count.argtypes = [vp]
+        L.tamols_launch_count.restype = C.c_int64
+        L.tamols_score_device.argtypes = [vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp, vp,
+                                          C.c_int32, vp, vp, C.c_int64]
+        L.tamols_score_host.argtypes = [vp, vp, C.c_int32, C.c_int32, C.c_int32, vp, vp, C.c_int32, vp, vp, C.c_int64]
+        _BOUND = True
+    return L
+
+
+def check(rc):
+    if rc != 0:
+        raise TamolsError(f"tamols error {rc}: {lib().tamols_last_error().decode()}")
+
+
+class Handle:
+    """Owns one tamols_handle (device scratch + stream).  Thin: every method is one C call."""
+
+    def __init__(self, params: TamolsParams, device=0, max_jobs=4):
+        self._h = C.c_void_p()
+        self.params = params
+        check(lib().tamols_create(C.byref(params), int(device), int(max_jobs), C.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            lib().tamols_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    @property
+    def stream(self):
+        return lib().tamols_stream(self._h)
+
+    @property
+    def launch_count(self):
+        return lib().tamols_launch_count(self._h)
+
+    def set_params(self, params: TamolsParams):
+        self.params = params
+        check(lib().tamols_set_params(self._h, C.byref(params)))
+
+    def score_host(self, heights, jobs, xy=None, want_scores=False):
+        """heights f64 [M, R, C]; jobs structured array (JOB_DTYPE); xy optional f64 [M, R, C, 2].
+        Returns (results structured array, scores [n_jobs, max cells] or None)."""
+        hm = np.ascontiguousarray(heights, np.float64)
+        M, R, Cc = hm.shape
+        jb = np.ascontiguousarray(jobs, JOB_DTYPE)
+        n = jb.shape[0]
+        res = np.zeros(n, RESULT_DTYPE)
+        xyp = None
+        if xy is not None:
+            xy = np.ascontiguousarray(xy, np.float64)
+            assert xy.shape == (M, R, Cc, 2)
+            xyp = xy.ctypes.data
+        scores, stride = None, 0
+        if want_scores:
+            stride = int(np.max(jb["nr"].astype(np.int64) * jb["nc"]))
+            scores = np.empty((n, stride), np.float64)
+        check(lib().tamols_score_host(self._h, hm.ctypes.data, M, R, Cc, xyp, jb.ctypes.data, n, res.ctypes.data,
+                                      scores.ctypes.data if scores is not None else None, stride))
+        return res, scores
+
+    def score_device(self, d_heights, height_dtype, num_maps, rows, cols, pitch, d_jobs, n_jobs, d_results, d_xy=None,
+                     d_scores=None, scores_stride=0):
+        """All pointers are device addresses (ints); asynchronous on self.stream."""
+        check(lib().tamols_score_device(self._h, d_heights, int(height_dtype), int(num_maps), int(rows), int(cols),
+                                        int(pitch), d_xy, d_jobs, int(n_jobs), d_results, d_scores,
+                                        int(scores_stride)))

@@ -23,3 +23,37 @@ def fixture_kwargs(g):
 def rel_err(a, b, floor=1e-6):
     a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
     return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), floor))) if a.size else 0.0
+
+
+def tamols_fixtures():
+    return sorted(glob.glob(os.path.join(GOLDEN, "tamols_*.npz")))
+
+
+def load_tamols_fixture(path):
+    """-> (TamolsParams, heights, xy, jobs, reference outputs dict)"""
+    from quadruped_pympc_tamols_b200 import _tamols_cabi as tc
+    g = np.load(path)
+    p = tc.TamolsParams.from_buffer_copy(g["params"].tobytes())
+    return p, g["heights"], g["xy"], g["jobs"].astype(tc.JOB_DTYPE), g
+
+
+def check_tamols_against_reference(res, scores, g, score_tol=1e-9, tie_tol=1e-6):
+    """Parity bar of the TAMOLS path (BASELINE.json north_star): per-candidate scores equal to the reference's within
+    float64 round-off, identical finite/inf pattern, and the selected cell index bit-exact except for documented cost
+    ties under 1e-6 (the chosen cell's reference score is then within 1e-6 of the reference minimum)."""
+    ref_scores, ref_idx = g["ref_scores"], g["ref_best_index"]
+    n = ref_scores.shape[1]
+    fin = np.isfinite(ref_scores)
+    assert np.array_equal(fin, np.isfinite(scores[:, :n])), "finite / rejected pattern differs from the reference"
+    if fin.any():
+        assert np.max(np.abs(scores[:, :n][fin] - ref_scores[fin])) < score_tol
+    for l in range(len(ref_idx)):
+        bi = int(res["best_index"][l])
+        if bi != int(ref_idx[l]):
+            assert bi >= 0 and ref_idx[l] >= 0, (l, bi, ref_idx[l])
+            assert abs(ref_scores[l, bi] - ref_scores[l, ref_idx[l]]) < tie_tol, (l, bi, ref_idx[l])
+        if ref_idx[l] >= 0 and bi == int(ref_idx[l]):
+            assert np.array_equal(res["best_xyz"][l], g["ref_best_xyz"][l])  # same cell -> same float64 coordinates
+            assert np.max(np.abs(res["vertex1"][l] - g["ref_vertex1"][l])) == 0.0
+            assert np.max(np.abs(res["vertex2"][l] - g["ref_vertex2"][l])) == 0.0
+        assert int(res["num_finite"][l]) == int(fin[l].sum())
