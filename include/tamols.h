@@ -105,12 +105,14 @@ int64_t tamols_launch_count(const tamols_handle *h);
  *              otherwise by plain loads.
  *   d_xy       optional [num_maps, rows, cols, 2] f64 candidate coordinates as stored by the sensor (:243); NULL =
  *              computed from the job's grid.
+ *   max_nr/nc  upper bounds of the jobs' nr / nc (the jobs live on the device; the bounds size the launch grid)
  *   d_jobs     [n_jobs]; d_results [n_jobs]; d_scores optional [n_jobs, scores_stride] per-candidate scores
  *              (_compute_tamols_score, :261-373; +inf for rejected candidates), NULL to skip.
  */
 int tamols_score_device(tamols_handle *h, const void *d_heights, int32_t height_dtype, int32_t num_maps, int32_t rows,
                         int32_t cols, int32_t pitch, const double *d_xy, const tamols_leg_job *d_jobs, int32_t n_jobs,
-                        tamols_result *d_results, double *d_scores, int64_t scores_stride);
+                        int32_t max_nr, int32_t max_nc, tamols_result *d_results, double *d_scores,
+                        int64_t scores_stride);
 
 /* Same with HOST buffers (what the Python class calls): copies heights (f64, [num_maps, rows, cols] dense), optional
  * xy and the jobs to the device, runs the launch, copies results (and scores when not NULL) back, synchronises. */

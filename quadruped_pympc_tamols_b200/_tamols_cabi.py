@@ -118,7 +118,7 @@ def lib():
         L.tamols_launch_count.argtypes = [vp]
         L.tamols_launch_count.restype = C.c_int64
         L.tamols_score_device.argtypes = [vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp, vp,
-                                          C.c_int32, vp, vp, C.c_int64]
+                                          C.c_int32, C.c_int32, C.c_int32, vp, vp, C.c_int64]
         L.tamols_score_host.argtypes = [vp, vp, C.c_int32, C.c_int32, C.c_int32, vp, vp, C.c_int32, vp, vp, C.c_int64]
         _BOUND = True
     return L
@@ -177,9 +177,9 @@ class Handle:
                                       scores.ctypes.data if scores is not None else None, stride))
         return res, scores
 
-    def score_device(self, d_heights, height_dtype, num_maps, rows, cols, pitch, d_jobs, n_jobs, d_results, d_xy=None,
-                     d_scores=None, scores_stride=0):
+    def score_device(self, d_heights, height_dtype, num_maps, rows, cols, pitch, d_jobs, n_jobs, max_nr, max_nc,
+                     d_results, d_xy=None, d_scores=None, scores_stride=0):
         """All pointers are device addresses (ints); asynchronous on self.stream."""
         check(lib().tamols_score_device(self._h, d_heights, int(height_dtype), int(num_maps), int(rows), int(cols),
-                                        int(pitch), d_xy, d_jobs, int(n_jobs), d_results, d_scores,
-                                        int(scores_stride)))
+                                        int(pitch), d_xy, d_jobs, int(n_jobs), int(max_nr), int(max_nc), d_results,
+                                        d_scores, int(scores_stride)))

@@ -1,0 +1,646 @@
+// tamols.cu -- TAMOLS candidate scoring + argmin for sm_100a behind the C ABI of include/tamols.h.
+//
+// One launch scores every cell of every leg job's candidate window:
+//   k_tamols_score  grid (tiles, jobs), 256 threads = an 8 x 32 tile of candidates.  The tile plus a 4-cell halo of the
+//                   height map is staged into shared memory with one TMA box load (cp.async.bulk.tensor.3d, UTMALDG)
+//                   when the map's row pitch allows a tensor map, else by plain coalesced loads; the 14 stencil
+//                   lookups of a candidate (its own height, 4 edge-gradient samples, the 3 x 3 roughness patch) hit
+//                   shared memory, the 5 leg-collision samples (which lie between hip and candidate, i.e. outside the
+//                   tile) go through L2.  Each thread scores one candidate in FP64 in the reference's operation order,
+//                   the block reduces (score, index) lexicographically (= first minimum, like the strict `<` of the
+//                   reference loop), and the last block of a job (atomic ticket) merges the per-tile partials and
+//                   writes the adapted foothold and its constraint box.
+// Reference semantics: quadruped_pympc/helpers/visual_foothold_adaptation.py:153-714 (see include/tamols.h).
+// Compiled with -fmad=false so that no FMA contraction changes the float64 rounding relative to numpy.
+// No CPU fallback: every entry point fails with TAMOLS_E_NODEVICE / TAMOLS_E_CUDA when the GPU path cannot run.
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "../../include/tamols.h"
+
+namespace tamols {
+
+constexpr int TW = 32, TH = 8, HALO = 4;
+constexpr int BW = TW + 2 * HALO, BH = TH + 2 * HALO;  // 40 x 16 cells staged per tile
+constexpr int THREADS = TW * TH;
+
+struct Partial {
+    double score;
+    int32_t index;
+    int32_t nfinite;
+};
+
+struct Args {
+    tamols_params p;
+    const void *heights;
+    const double *xy;
+    const tamols_leg_job *jobs;
+    tamols_result *results;
+    double *scores;
+    long long scores_stride;
+    Partial *partials;
+    unsigned int *tickets;
+    int rows, cols, pitch, max_tiles;
+};
+
+// per-block view of one leg job
+struct Ctx {
+    double ox, oy, rax, ray, cax, cay;  // grid
+    double arx, ary, acx, acy;          // axes / |axis|^2: grid coordinate = d . a
+    int map, r0, c0, nr, nc, flags;
+    int br, bc;                          // map coordinates of the staged box's first cell
+    long long map_base;                  // map * rows * pitch
+    int pitch;
+};
+
+template <typename HT>
+__device__ __forceinline__ double lookup(const Args &a, const Ctx &c, const HT *s_box, double x, double y) {
+    // FastHeightMap.get_height (:31-35): nearest cell of the leg's map + 0.02
+    const double dx = x - c.ox, dy = y - c.oy;
+    const double gr = dx * c.arx + dy * c.ary;
+    const double gc = dx * c.acx + dy * c.acy;
+    int ir = __double2int_rn(gr), ic = __double2int_rn(gc);
+    ir = min(max(ir, c.r0), c.r0 + c.nr - 1);
+    ic = min(max(ic, c.c0), c.c0 + c.nc - 1);
+    const int lr = ir - c.br, lc = ic - c.bc;
+    HT h;
+    if ((unsigned)lr < (unsigned)BH && (unsigned)lc < (unsigned)BW)
+        h = s_box[lr * BW + lc];
+    else
+        h = __ldg(static_cast<const HT *>(a.heights) + c.map_base + (long long)ir * c.pitch + ic);
+    return (double)h + a.p.sensor_offset;
+}
+
+__device__ __forceinline__ void candidate_xy(const Args &a, const Ctx &c, int R, int C, double &x, double &y) {
+    if (a.xy) {  // coordinates as stored by the sensor (:243)
+        const double2 q = __ldg(reinterpret_cast<const double2 *>(a.xy) + ((long long)c.map * a.rows + R) * a.cols + C);
+        x = q.x;
+        y = q.y;
+    } else {
+        x = (c.ox + (double)R * c.rax) + (double)C * c.cax;
+        y = (c.oy + (double)R * c.ray) + (double)C * c.cay;
+    }
+}
+
+// candidate construction (:188-196) + _compute_tamols_score (:261-373) for map cell (R, C)
+template <typename HT>
+__device__ double score_candidate(const Args &a, const Ctx &c, const tamols_leg_job &j, const HT *s_box, int R, int C,
+                                  double cand[3]) {
+    const tamols_params &p = a.p;
+    candidate_xy(a, c, R, C, cand[0], cand[1]);
+    cand[2] = lookup(a, c, s_box, cand[0], cand[1]) + p.foot_clearance;
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+    // _check_kinematic_feasibility (:375-395)
+    {
+        double d0 = cand[0] - j.hip[0], d1 = cand[1] - j.hip[1], d2 = cand[2] - j.hip[2];
+        const double dist_td = sqrt((d0 * d0 + d1 * d1) + d2 * d2);
+        if (!(p.l_min <= dist_td && dist_td <= p.l_max)) return inf;
+        if (c.flags & TAMOLS_FLAG_HAS_VELOCITY) {
+            d0 = cand[0] - (j.hip[0] + j.vel[0] * p.stance_duration);
+            d1 = cand[1] - (j.hip[1] + j.vel[1] * p.stance_duration);
+            d2 = cand[2] - (j.hip[2] + j.vel[2] * p.stance_duration);
+            const double dist_lo = sqrt((d0 * d0 + d1 * d1) + d2 * d2);
+            if (!(p.l_min <= dist_lo && dist_lo <= p.l_max)) return inf;
+        }
+    }
+    // _check_leg_collision (:397-420)
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        const double al = p.collision_alphas[k], be = 1.0 - al;
+        const double px = be * j.hip[0] + al * cand[0];
+        const double py = be * j.hip[1] + al * cand[1];
+        const double pz = be * j.hip[2] + al * cand[2];
+        const double h_ground = lookup(a, c, s_box, px, py) - p.sensor_offset;
+        if (pz < h_ground + p.collision_margin) return inf;
+    }
+    const double d = p.gradient_delta;
+    // _compute_roughness_cost (:468-521) and _compute_edge_cost (:422-466) share the 3 x 3 patch at spacing delta
+    double h[9];
+#pragma unroll
+    for (int i = -1; i <= 1; ++i)
+#pragma unroll
+        for (int k = -1; k <= 1; ++k)
+            h[(i + 1) * 3 + (k + 1)] = lookup(a, c, s_box, cand[0] + (double)i * d, cand[1] + (double)k * d);
+    double edge;
+    {
+        const double gx = fabs(h[2 * 3 + 1] - h[0 * 3 + 1]) / (2.0 * d);
+        const double gy = fabs(h[1 * 3 + 2] - h[1 * 3 + 0]) / (2.0 * d);
+        const double g = sqrt(gx * gx + gy * gy);
+        edge = g <= p.slope_threshold ? 0.0 : g - p.slope_threshold;
+    }
+    double rough;
+    {
+        double sxh = 0.0, syh = 0.0, sh = 0.0;
+#pragma unroll
+        for (int i = -1; i <= 1; ++i)
+#pragma unroll
+            for (int k = -1; k <= 1; ++k) {
+                const double v = h[(i + 1) * 3 + (k + 1)];
+                sxh += ((double)i * d) * v;
+                syh += ((double)k * d) * v;
+                sh += v;
+            }
+        const double s2 = 6.0 * (d * d);
+        const double pa = sxh / s2, pb = syh / s2, pc = sh / 9.0;
+        double res[9], mean = 0.0;
+#pragma unroll
+        for (int i = -1; i <= 1; ++i)
+#pragma unroll
+            for (int k = -1; k <= 1; ++k) {
+                const int q = (i + 1) * 3 + (k + 1);
+                res[q] = h[q] - ((((double)i * d) * pa + ((double)k * d) * pb) + pc);
+                mean += res[q];
+            }
+        mean /= 9.0;
+        double var = 0.0;
+#pragma unroll
+        for (int q = 0; q < 9; ++q) var += (res[q] - mean) * (res[q] - mean);
+        rough = var / 9.0;
+    }
+    // deviation from the seed (:344-345)
+    const double e0 = cand[0] - j.seed[0], e1 = cand[1] - j.seed[1], e2 = cand[2] - j.seed[2];
+    const double dev = (e0 * e0 + e1 * e1) + e2 * e2;
+    // _compute_nominal_kinematic_cost (:523-553)
+    double nom;
+    {
+        const double n0 = j.hip[0] - (cand[0] - 0.0), n1 = j.hip[1] - (cand[1] - 0.0);
+        const double n2 = j.hip[2] - (cand[2] - (-p.h_des));
+        nom = (n0 * n0 + n1 * n1) + n2 * n2;
+    }
+    // _compute_reference_tracking_cost (:555-609)
+    double trk = 0.0;
+    if (!(c.flags & TAMOLS_FLAG_HAS_VELOCITY)) {
+        trk = e0 < 0.0 ? e0 * e0 : 0.0;
+    } else {
+        const double vm = sqrt(j.vel[0] * j.vel[0] + j.vel[1] * j.vel[1]);
+        if (!(vm < 0.01) && ((j.vel[0] > 0.0 && e0 < 0.0) || (j.vel[0] < 0.0 && e0 > 0.0))) trk = e0 * e0;
+    }
+    // _compute_stability_cost (:611-714)
+    double stab = 0.0;
+    if (c.flags & TAMOLS_FLAG_STABILITY) {
+        const double comx = j.base_xy[0] + j.vel[0] * p.estimated_swing_time;
+        const double comy = j.base_xy[1] + j.vel[1] * p.estimated_swing_time;
+        const double vx = j.diag_foot[0] - cand[0], vy = j.diag_foot[1] - cand[1];
+        const double wx = comx - cand[0], wy = comy - cand[1];
+        const double vv = vx * vx + vy * vy;
+        double dist;
+        if (vv < 1e-8) {
+            dist = sqrt(wx * wx + wy * wy);
+        } else {
+            double t = (wx * vx + wy * vy) / vv;
+            t = t < 0.0 ? 0.0 : (t > 1.0 ? 1.0 : t);
+            const double ex = comx - (cand[0] + t * vx), ey = comy - (cand[1] + t * vy);
+            dist = sqrt(ex * ex + ey * ey);
+        }
+        if (dist > p.stability_margin) stab = (dist - p.stability_margin) * (dist - p.stability_margin);
+    }
+    // total (:368-371), kinematic_cost = 0.0 (:335)
+    return (((((0.0 + edge * p.weight_edge_avoidance) + rough * p.weight_roughness) + dev * p.weight_deviation) +
+             nom * p.weight_nominal_kinematic) + trk * p.weight_reference_tracking) + stab * p.weight_stability;
+}
+
+// ---------------------------------------------------------------- TMA / mbarrier helpers (sm_100a PTX) -------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t phase) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(phase) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *tmap, uint64_t *bar, int x, int y, int z) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(x), "r"(y), "r"(z) : "memory");
+}
+
+__device__ __forceinline__ void argmin_combine(double &s, int &i, double os, int oi) {
+    if (os < s || (os == s && oi < i)) {
+        s = os;
+        i = oi;
+    }
+}
+
+// ---------------------------------------------------------------- the kernel ---------------------------------
+template <typename HT, bool USE_TMA>
+__global__ void __launch_bounds__(THREADS) k_tamols_score(const __grid_constant__ CUtensorMap tmap, const Args a) {
+    __shared__ __align__(128) HT s_box[BH * BW];
+    __shared__ __align__(8) uint64_t s_bar;
+    __shared__ double s_rs[THREADS / 32];
+    __shared__ int s_ri[THREADS / 32], s_rn[THREADS / 32];
+    __shared__ unsigned int s_ticket;
+
+    const int job = blockIdx.y, t = threadIdx.x;
+    const tamols_leg_job &j = a.jobs[job];
+    Ctx c;
+    c.map = j.map; c.r0 = j.r0; c.c0 = j.c0; c.nr = j.nr; c.nc = j.nc; c.flags = j.flags;
+    const int tiles_c = (c.nc + TW - 1) / TW, tiles_r = (c.nr + TH - 1) / TH;
+    const int ntiles = tiles_c * tiles_r;
+    if ((int)blockIdx.x >= ntiles) return;
+    const int tile_r = blockIdx.x / tiles_c, tile_c = blockIdx.x % tiles_c;
+    c.br = c.r0 + tile_r * TH - HALO;
+    // TMA needs the box to start on a 16-byte boundary of the row (measured on B200: an odd f64 column raises
+    // 'illegal instruction'), so the left halo is HALO .. HALO + 16/sizeof(HT) - 1 cells
+    c.bc = (c.c0 + tile_c * TW - HALO) & ~(int)(16 / sizeof(HT) - 1);
+    c.pitch = a.pitch;
+    c.map_base = (long long)c.map * a.rows * a.pitch;
+
+    // ---- stage tile + halo
+    if (USE_TMA) {
+        if (t == 0) {
+            mbar_init(&s_bar, 1);
+            mbar_expect_tx(&s_bar, (uint32_t)(BH * BW * sizeof(HT)));
+            tma_load_3d(s_box, &tmap, &s_bar, c.bc, c.br, c.map);  // out-of-bounds cells are zero-filled, never read
+        }
+    } else {
+        const HT *src = static_cast<const HT *>(a.heights) + c.map_base;
+        for (int e = t; e < BH * BW; e += THREADS) {
+            const int rr = c.br + e / BW, cc = c.bc + e % BW;
+            s_box[e] = (rr >= 0 && rr < a.rows && cc >= 0 && cc < a.cols) ? __ldg(src + (long long)rr * a.pitch + cc) : HT(0);
+        }
+    }
+    // ---- per-job constants while the copy is in flight
+    c.ox = j.origin[0]; c.oy = j.origin[1];
+    c.rax = j.row_axis[0]; c.ray = j.row_axis[1]; c.cax = j.col_axis[0]; c.cay = j.col_axis[1];
+    {
+        const double r2 = c.rax * c.rax + c.ray * c.ray, c2 = c.cax * c.cax + c.cay * c.cay;
+        c.arx = c.rax / r2; c.ary = c.ray / r2; c.acx = c.cax / c2; c.acy = c.cay / c2;
+    }
+    __syncthreads();  // s_bar initialised (TMA) / s_box written (plain)
+    if (USE_TMA) mbar_wait(&s_bar, 0);
+
+    // ---- one candidate per thread
+    const int r = tile_r * TH + t / TW, q = tile_c * TW + t % TW;
+    const bool valid = r < c.nr && q < c.nc;
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+    double s = inf;
+    int idx = 0x7fffffff;
+    if (valid) {
+        double cand[3];
+        s = score_candidate<HT>(a, c, j, s_box, c.r0 + r, c.c0 + q, cand);
+        idx = r * c.nc + q;
+        if (a.scores) a.scores[(long long)job * a.scores_stride + idx] = s;
+        if (!(s < inf)) s = inf;  // NaN is never selected by the reference's `score < best_score`
+    }
+    int nfin = (valid && s < inf) ? 1 : 0;
+
+    // ---- block reduction: lexicographic (score, index) minimum = first minimum in row-major order
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double os = __shfl_xor_sync(0xffffffffu, s, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+        argmin_combine(s, idx, os, oi);
+        nfin += __shfl_xor_sync(0xffffffffu, nfin, o);
+    }
+    if ((t & 31) == 0) {
+        s_rs[t >> 5] = s;
+        s_ri[t >> 5] = idx;
+        s_rn[t >> 5] = nfin;
+    }
+    __syncthreads();
+    if (t == 0) {
+        for (int w = 1; w < THREADS / 32; ++w) {
+            argmin_combine(s, idx, s_rs[w], s_ri[w]);
+            nfin += s_rn[w];
+        }
+        Partial &pt = a.partials[(long long)job * a.max_tiles + blockIdx.x];
+        pt.score = s;
+        pt.index = idx;
+        pt.nfinite = nfin;
+        __threadfence();
+        s_ticket = atomicAdd(&a.tickets[job], 1u);
+    }
+    __syncthreads();
+    if (s_ticket != (unsigned)(ntiles - 1)) return;
+
+    // ---- last block of this job: merge the tile partials, write the result (:209-222)
+    __threadfence();
+    s = inf;
+    idx = 0x7fffffff;
+    nfin = 0;
+    for (int b = t; b < ntiles; b += THREADS) {
+        // written by other blocks: read through L2 (ld.global.cg), not this SM's L1
+        const int4 raw = __ldcg(reinterpret_cast<const int4 *>(a.partials + (long long)job * a.max_tiles + b));
+        argmin_combine(s, idx, __hiloint2double(raw.y, raw.x), raw.z);
+        nfin += raw.w;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double os = __shfl_xor_sync(0xffffffffu, s, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+        argmin_combine(s, idx, os, oi);
+        nfin += __shfl_xor_sync(0xffffffffu, nfin, o);
+    }
+    __syncthreads();
+    if ((t & 31) == 0) {
+        s_rs[t >> 5] = s;
+        s_ri[t >> 5] = idx;
+        s_rn[t >> 5] = nfin;
+    }
+    __syncthreads();
+    if (t == 0) {
+        for (int w = 1; w < THREADS / 32; ++w) {
+            argmin_combine(s, idx, s_rs[w], s_ri[w]);
+            nfin += s_rn[w];
+        }
+        tamols_result &out = a.results[job];
+        out.num_finite = nfin;
+        out.best_score = s;
+        double xyz[3] = {0.0, 0.0, 0.0};
+        if (s < inf) {
+            out.best_index = idx;
+            Ctx g = c;
+            g.br = -0x40000000;  // no staged box for this lookup: read the map through L2
+            g.bc = -0x40000000;
+            candidate_xy(a, g, c.r0 + idx / c.nc, c.c0 + idx % c.nc, xyz[0], xyz[1]);
+            xyz[2] = lookup<HT>(a, g, s_box, xyz[0], xyz[1]) + a.p.foot_clearance;
+        } else {
+            out.best_index = -1;
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            out.best_xyz[k] = xyz[k];
+            out.vertex1[k] = xyz[k];
+            out.vertex2[k] = xyz[k];
+        }
+        out.vertex1[0] -= a.p.constraint_box_dx;
+        out.vertex1[1] -= a.p.constraint_box_dy;
+        out.vertex2[0] += a.p.constraint_box_dx;
+        out.vertex2[1] += a.p.constraint_box_dy;
+        a.tickets[job] = 0;  // ready for the next launch on this stream
+    }
+}
+
+}  // namespace tamols
+
+// ================================================================ host side ================================
+using namespace tamols;
+
+static thread_local std::string g_terr;
+static int tfail(int code, const std::string &msg) {
+    g_terr = msg;
+    return code;
+}
+#define TCU(call)                                                                                   \
+    do {                                                                                            \
+        cudaError_t e_ = (call);                                                                    \
+        if (e_ != cudaSuccess)                                                                      \
+            return tfail(TAMOLS_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));        \
+    } while (0)
+
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+struct tamols_handle {
+    tamols_params p;
+    int device, max_jobs;
+    cudaStream_t stream;
+    encode_tiled_fn encode;
+    int64_t launches;
+    unsigned int *d_tickets;
+    Partial *d_partials;
+    size_t partial_cap;  // in Partial elements
+    // cached tensor map
+    CUtensorMap tmap;
+    const void *tm_ptr;
+    int tm_dtype, tm_maps, tm_rows, tm_cols, tm_pitch;
+    // staging for tamols_score_host
+    char *d_stage, *h_stage;
+    size_t stage_cap;
+};
+
+extern "C" const char *tamols_last_error(void) { return g_terr.c_str(); }
+extern "C" void *tamols_stream(tamols_handle *h) { return h ? (void *)h->stream : nullptr; }
+extern "C" int64_t tamols_launch_count(const tamols_handle *h) { return h ? h->launches : 0; }
+
+static int check_params(const tamols_params *p) {
+    if (!p) return tfail(TAMOLS_E_ARG, "null params");
+    if (!(p->gradient_delta > 0.0)) return tfail(TAMOLS_E_ARG, "gradient_delta must be > 0");
+    return TAMOLS_OK;
+}
+
+extern "C" int tamols_create(const tamols_params *params, int32_t device, int32_t max_jobs, tamols_handle **out) {
+    if (!out) return tfail(TAMOLS_E_ARG, "null argument");
+    *out = nullptr;
+    if (int rc = check_params(params)) return rc;
+    if (max_jobs < 1) return tfail(TAMOLS_E_ARG, "max_jobs must be >= 1");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return tfail(TAMOLS_E_NODEVICE, "no CUDA device: this library has no CPU fallback");
+    }
+    if (device < 0 || device >= ndev) return tfail(TAMOLS_E_ARG, "device ordinal out of range");
+    cudaDeviceProp prop;
+    TCU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return tfail(TAMOLS_E_NODEVICE, std::string("device is ") + prop.name + "; kernels are built for sm_100a only");
+    TCU(cudaSetDevice(device));
+    tamols_handle *h = new (std::nothrow) tamols_handle();
+    if (!h) return tfail(TAMOLS_E_ARG, "out of host memory");
+    memset(h, 0, sizeof *h);
+    h->p = *params;
+    h->device = device;
+    h->max_jobs = max_jobs;
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+        h->encode = (encode_tiled_fn)fn;
+    cudaGetLastError();
+    bool ok = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaMalloc(&h->d_tickets, (size_t)max_jobs * sizeof(unsigned int)) == cudaSuccess &&
+              cudaMemset(h->d_tickets, 0, (size_t)max_jobs * sizeof(unsigned int)) == cudaSuccess;
+    if (!ok) {
+        std::string m = std::string("allocation failed: ") + cudaGetErrorString(cudaGetLastError());
+        tamols_destroy(h);
+        return tfail(TAMOLS_E_CUDA, m);
+    }
+    *out = h;
+    return TAMOLS_OK;
+}
+
+extern "C" int tamols_destroy(tamols_handle *h) {
+    if (!h) return TAMOLS_OK;
+    cudaSetDevice(h->device);
+    if (h->stream) {
+        cudaStreamSynchronize(h->stream);
+        cudaStreamDestroy(h->stream);
+    }
+    if (h->d_tickets) cudaFree(h->d_tickets);
+    if (h->d_partials) cudaFree(h->d_partials);
+    if (h->d_stage) cudaFree(h->d_stage);
+    if (h->h_stage) cudaFreeHost(h->h_stage);
+    delete h;
+    return TAMOLS_OK;
+}
+
+extern "C" int tamols_set_params(tamols_handle *h, const tamols_params *params) {
+    if (!h) return tfail(TAMOLS_E_ARG, "null argument");
+    if (int rc = check_params(params)) return rc;
+    h->p = *params;
+    return TAMOLS_OK;
+}
+
+// builds (or reuses) the 3-D tensor map [maps][rows][cols] with an BW x BH x 1 box; returns false when TMA cannot
+// describe this buffer (pitch or base not 16-byte aligned, driver entry point missing) -> plain-load kernel
+static bool get_tensor_map(tamols_handle *h, const void *d_heights, int dtype, int maps, int rows, int cols, int pitch) {
+    const size_t es = dtype == TAMOLS_F64 ? 8 : 4;
+    if (!h->encode || ((uintptr_t)d_heights & 15) || ((size_t)pitch * es) % 16) return false;
+    if (h->tm_ptr == d_heights && h->tm_dtype == dtype && h->tm_maps == maps && h->tm_rows == rows &&
+        h->tm_cols == cols && h->tm_pitch == pitch)
+        return true;
+    const cuuint64_t gdim[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)maps};
+    const cuuint64_t gstride[2] = {(cuuint64_t)pitch * es, (cuuint64_t)pitch * es * (cuuint64_t)rows};
+    const cuuint32_t box[3] = {BW, BH, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    // CU_TENSOR_MAP_DATA_TYPE_FLOAT64 / FLOAT32: the copy is bit-exact for either
+    const CUresult r = h->encode(&h->tmap, dtype == TAMOLS_F64 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+                                 3, const_cast<void *>(d_heights), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                 CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        h->tm_ptr = nullptr;
+        return false;
+    }
+    h->tm_ptr = d_heights; h->tm_dtype = dtype; h->tm_maps = maps; h->tm_rows = rows; h->tm_cols = cols; h->tm_pitch = pitch;
+    return true;
+}
+
+static int launch_score(tamols_handle *h, const void *d_heights, int dtype, int maps, int rows, int cols, int pitch,
+                        const double *d_xy, const tamols_leg_job *d_jobs, int n_jobs, int max_nr, int max_nc,
+                        tamols_result *d_results, double *d_scores, int64_t scores_stride) {
+    const int max_tiles = ((max_nr + TH - 1) / TH) * ((max_nc + TW - 1) / TW);
+    const size_t need = (size_t)n_jobs * max_tiles;
+    if (need > h->partial_cap) {
+        if (h->d_partials) {
+            TCU(cudaStreamSynchronize(h->stream));
+            TCU(cudaFree(h->d_partials));
+            h->d_partials = nullptr;
+            h->partial_cap = 0;
+        }
+        TCU(cudaMalloc(&h->d_partials, need * sizeof(Partial)));
+        h->partial_cap = need;
+    }
+    Args a;
+    a.p = h->p;
+    a.heights = d_heights; a.xy = d_xy; a.jobs = d_jobs; a.results = d_results; a.scores = d_scores;
+    a.scores_stride = scores_stride; a.partials = h->d_partials; a.tickets = h->d_tickets;
+    a.rows = rows; a.cols = cols; a.pitch = pitch; a.max_tiles = max_tiles;
+    const bool tma = get_tensor_map(h, d_heights, dtype, maps, rows, cols, pitch);
+    const dim3 grid(max_tiles, n_jobs);
+    if (dtype == TAMOLS_F64) {
+        if (tma) k_tamols_score<double, true><<<grid, THREADS, 0, h->stream>>>(h->tmap, a);
+        else k_tamols_score<double, false><<<grid, THREADS, 0, h->stream>>>(h->tmap, a);
+    } else {
+        if (tma) k_tamols_score<float, true><<<grid, THREADS, 0, h->stream>>>(h->tmap, a);
+        else k_tamols_score<float, false><<<grid, THREADS, 0, h->stream>>>(h->tmap, a);
+    }
+    TCU(cudaGetLastError());
+    h->launches += 1;
+    return TAMOLS_OK;
+}
+
+extern "C" int tamols_score_device(tamols_handle *h, const void *d_heights, int32_t height_dtype, int32_t num_maps,
+                                   int32_t rows, int32_t cols, int32_t pitch, const double *d_xy,
+                                   const tamols_leg_job *d_jobs, int32_t n_jobs, int32_t max_nr, int32_t max_nc,
+                                   tamols_result *d_results, double *d_scores, int64_t scores_stride) {
+    if (!h || !d_heights || !d_jobs || !d_results) return tfail(TAMOLS_E_ARG, "null argument");
+    if (height_dtype != TAMOLS_F64 && height_dtype != TAMOLS_F32) return tfail(TAMOLS_E_ARG, "unknown height_dtype");
+    if (num_maps < 1 || rows < 1 || cols < 1 || pitch < cols) return tfail(TAMOLS_E_ARG, "bad map shape");
+    if (n_jobs < 1 || n_jobs > h->max_jobs) return tfail(TAMOLS_E_ARG, "n_jobs exceeds max_jobs");
+    if (max_nr < 1 || max_nc < 1 || max_nr > rows || max_nc > cols) return tfail(TAMOLS_E_ARG, "bad window bound");
+    if (d_scores && scores_stride < (int64_t)max_nr * max_nc) return tfail(TAMOLS_E_ARG, "scores_stride too small");
+    TCU(cudaSetDevice(h->device));
+    return launch_score(h, d_heights, height_dtype, num_maps, rows, cols, pitch, d_xy, d_jobs, n_jobs, max_nr, max_nc,
+                        d_results, d_scores, scores_stride);
+}
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+extern "C" int tamols_score_host(tamols_handle *h, const double *heights, int32_t num_maps, int32_t rows, int32_t cols,
+                                 const double *xy, const tamols_leg_job *jobs, int32_t n_jobs, tamols_result *results,
+                                 double *scores, int64_t scores_stride) {
+    if (!h || !heights || !jobs || !results) return tfail(TAMOLS_E_ARG, "null argument");
+    if (num_maps < 1 || rows < 1 || cols < 1) return tfail(TAMOLS_E_ARG, "bad map shape");
+    if (n_jobs < 1 || n_jobs > h->max_jobs) return tfail(TAMOLS_E_ARG, "n_jobs exceeds max_jobs");
+    int max_nr = 0, max_nc = 0;
+    for (int k = 0; k < n_jobs; ++k) {
+        const tamols_leg_job &j = jobs[k];
+        if (j.map < 0 || j.map >= num_maps || j.nr < 1 || j.nc < 1 || j.r0 < 0 || j.c0 < 0 || j.r0 + j.nr > rows ||
+            j.c0 + j.nc > cols)
+            return tfail(TAMOLS_E_ARG, "leg job window outside its map");
+        max_nr = j.nr > max_nr ? j.nr : max_nr;
+        max_nc = j.nc > max_nc ? j.nc : max_nc;
+    }
+    if (scores && scores_stride < (int64_t)max_nr * max_nc) return tfail(TAMOLS_E_ARG, "scores_stride too small");
+    TCU(cudaSetDevice(h->device));
+    // staging layout (device and pinned host mirror): heights (row pitch padded to 16 B so the TMA path applies) | xy |
+    // jobs | results | scores
+    const int pitch = (cols + 1) & ~1;
+    const size_t cells = (size_t)num_maps * rows;
+    const size_t o_h = 0, sz_h = cells * pitch * 8;
+    const size_t o_xy = align_up(o_h + sz_h, 256), sz_xy = xy ? cells * cols * 16 : 0;
+    const size_t o_j = align_up(o_xy + sz_xy, 256), sz_j = (size_t)n_jobs * sizeof(tamols_leg_job);
+    const size_t o_r = align_up(o_j + sz_j, 256), sz_r = (size_t)n_jobs * sizeof(tamols_result);
+    const size_t o_s = align_up(o_r + sz_r, 256), sz_s = scores ? (size_t)n_jobs * scores_stride * 8 : 0;
+    const size_t total = o_s + sz_s;
+    if (total > h->stage_cap) {
+        TCU(cudaStreamSynchronize(h->stream));
+        if (h->d_stage) cudaFree(h->d_stage);
+        if (h->h_stage) cudaFreeHost(h->h_stage);
+        h->d_stage = nullptr; h->h_stage = nullptr; h->stage_cap = 0; h->tm_ptr = nullptr;
+        const size_t cap = align_up(total + total / 4, 4096);
+        TCU(cudaMalloc(&h->d_stage, cap));
+        TCU(cudaMallocHost(&h->h_stage, cap));
+        h->stage_cap = cap;
+    }
+    char *hs = h->h_stage, *ds = h->d_stage;
+    if (pitch == cols) {
+        memcpy(hs + o_h, heights, sz_h);
+    } else {
+        for (size_t r = 0; r < cells; ++r) {
+            double *dst = reinterpret_cast<double *>(hs + o_h) + r * pitch;
+            memcpy(dst, heights + r * cols, (size_t)cols * 8);
+            dst[cols] = 0.0;
+        }
+    }
+    if (xy) memcpy(hs + o_xy, xy, sz_xy);
+    memcpy(hs + o_j, jobs, sz_j);
+    TCU(cudaMemcpyAsync(ds, hs, o_j + sz_j, cudaMemcpyHostToDevice, h->stream));  // one H2D copy
+    double *d_scores = scores ? reinterpret_cast<double *>(ds + o_s) : nullptr;
+    if (int rc = launch_score(h, ds + o_h, TAMOLS_F64, num_maps, rows, cols, pitch,
+                              xy ? reinterpret_cast<const double *>(ds + o_xy) : nullptr,
+                              reinterpret_cast<const tamols_leg_job *>(ds + o_j), n_jobs, max_nr, max_nc,
+                              reinterpret_cast<tamols_result *>(ds + o_r), d_scores, scores_stride))
+        return rc;
+    TCU(cudaMemcpyAsync(hs + o_r, ds + o_r, (scores ? o_s + sz_s : o_r + sz_r) - o_r, cudaMemcpyDeviceToHost, h->stream));
+    TCU(cudaStreamSynchronize(h->stream));
+    memcpy(results, hs + o_r, sz_r);
+    if (scores) {
+        // candidates beyond a job's own window are not written by the kernel: report them as rejected
+        for (int k = 0; k < n_jobs; ++k) {
+            const int64_t n = (int64_t)jobs[k].nr * jobs[k].nc;
+            const double *src = reinterpret_cast<const double *>(hs + o_s) + (size_t)k * scores_stride;
+            double *dst = scores + (size_t)k * scores_stride;
+            memcpy(dst, src, (size_t)n * 8);
+            for (int64_t i = n; i < scores_stride; ++i) dst[i] = INFINITY;
+        }
+    }
+    return TAMOLS_OK;
+}

@@ -25,6 +25,28 @@ def test_exports_every_declared_symbol(lib):
         assert hasattr(lib, name), name
 
 
+def test_exports_every_declared_tamols_symbol(lib):
+    from quadruped_pympc_tamols_b200 import _tamols_cabi as tc
+    hdr = open(os.path.join(ROOT, "include", "tamols.h")).read()
+    declared = set(re.findall(r"\b(tamols_[a-z0-9_]+)\s*\(", hdr))
+    assert declared == set(tc.EXPORTS), declared ^ set(tc.EXPORTS)
+    L = tc.lib()
+    for name in declared:
+        assert hasattr(L, name), name
+    assert C.sizeof(tc.TamolsParams) == 8 * 24
+    assert C.sizeof(tc.TamolsLegJob) == 24 + 8 * 19
+    assert C.sizeof(tc.TamolsResult) == 8 + 8 * 10
+
+
+def test_tamols_create_fails_loudly_without_gpu(lib):
+    import torch
+    from quadruped_pympc_tamols_b200 import _tamols_cabi as tc
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(tc.TamolsError, match="no CUDA device|CPU fallback"):
+        tc.Handle(tc.make_params({}, "go2"))
+
+
 def test_struct_sizes_match_header():
     assert C.sizeof(_cabi.QpmpcResult) == 4 * 52
     assert C.sizeof(_cabi.QpmpcBatch) == 8 + 14 * 8
