@@ -248,6 +248,11 @@ def run_cuda(args):
     if not args.no_batched:
         batched = run_batched(torch, _cabi, dev, local_rank, rank, world, barrier, max_over_ranks, fp32_peak)
 
+    tamols = None
+    if not args.no_tamols:
+        tamols = run_tamols(torch, dev, local_rank, rank, world, barrier, max_over_ranks,
+                            with_cpu=(rank == 0 and world == 1 and not args.no_cpu))
+
     # ---- CPU baseline (rank 0, N=1 only): bounded sample of the same workload
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -273,7 +278,7 @@ def run_cuda(args):
                              "finalize_ms": float(roll[:, 1].mean()), "flop_per_rollout": FLOP_PER_ROLLOUT["cubic_spline_ga"],
                              "peak_source": "FP32 FMA-chain microbenchmark in this run (qpmpc_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 figure",
                              "note": "10k rollouts = 75.5 MFLOP: latency-bound at this size; see batched.roofline for the throughput regime"},
-                "cpu_baseline": cpu, "clocks": clk, "batched": batched}
+                "cpu_baseline": cpu, "clocks": clk, "batched": batched, "tamols": tamols}
         print(json.dumps(line))
     h.close()
     if world > 1:
@@ -319,6 +324,130 @@ def run_batched(torch, _cabi, dev, local_rank, rank, world, barrier, max_over_ra
                          "kernel": "k_rollout<zero_order,fixed>", "launch_ms": roll_ms, "flop_per_rollout": FLOP_PER_ROLLOUT["zero_order"]}}
 
 
+def run_tamols(torch, dev, local_rank, rank, world, barrier, max_over_ranks, with_cpu):
+    """TAMOLS foothold scoring (BASELINE.json configs[2] "C3-T" and configs[3] "C4"): footholds/s and candidates/s.
+    Device-resident sweep timed with CUDA events on the handle's stream (L2 flushed between launches), the e2e call
+    with host buffers (what VisualFootholdAdaptation.compute_adaptation makes) by wall clock, the CPU oracle beside."""
+    import synthetic as sy
+    from quadruped_pympc_tamols_b200 import _tamols_cabi as tc
+    hbm_peak = None
+    try:
+        hbm_peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
+    except Exception:  # noqa: BLE001
+        pass
+    peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if hbm_peak else "B200_PROFILING.md fallback 6650 GB/s (of fallback)"
+    hbm_peak = hbm_peak or 6650.0
+    p = tc.make_params(sy.tamols_params_for("go2"), "go2")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    out = {"dtype": "f64", "l2": "flushed (256 MiB write) between timed launches"}
+
+    def timed(h, call, reps):
+        stream = torch.cuda.ExternalStream(h.stream, device=dev)
+        ms = []
+        with torch.cuda.stream(stream):
+            for _ in range(3):
+                call()
+            torch.cuda.synchronize()
+            for it in range(reps):
+                flush.fill_(it & 0xFF)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                call()
+                e1.record(stream)
+                e1.synchronize()
+                ms.append(e0.elapsed_time(e1))
+        return np.array(ms)
+
+    def device_scene(sc):
+        d_h = torch.from_numpy(np.ascontiguousarray(sc["heights"])).to(dev)
+        d_jobs = torch.from_numpy(np.frombuffer(sc["jobs"].tobytes(), np.uint8).copy()).to(dev)
+        d_res = torch.zeros(len(sc["jobs"]) * tc.RESULT_DTYPE.itemsize, dtype=torch.uint8, device=dev)
+        return d_h, d_jobs, d_res
+
+    # ---- C4 sweep: 4 legs x window^2 candidates on one 2048 x 2048 @ 0.02 m map (one robot = the latency regime)
+    rng = np.random.default_rng(4 + rank)
+    sweep = []
+    base = sy.sweep_scene("go2", rng, "stepping_stones_tall", window=256, seed=4)
+    d_h = torch.from_numpy(np.ascontiguousarray(base["heights"])).to(dev)
+    for w in (32, 64, 128, 256):
+        sc = sy.sweep_scene("go2", np.random.default_rng(40 + w), "flat", window=w, map_rows=2048, map_cols=2048, seed=4)
+        jobs = sc["jobs"]
+        d_jobs = torch.from_numpy(np.frombuffer(jobs.tobytes(), np.uint8).copy()).to(dev)
+        d_res = torch.zeros(4 * tc.RESULT_DTYPE.itemsize, dtype=torch.uint8, device=dev)
+        h = tc.Handle(p, device=local_rank, max_jobs=4)
+        ms = timed(h, lambda: h.score_device(d_h.data_ptr(), tc.F64, 1, 2048, 2048, 2048, d_jobs.data_ptr(), 4, w, w,
+                                             d_res.data_ptr()), 50)
+        h.close()
+        sweep.append({"window": w, "candidates": 4 * w * w, "p50_ms": float(np.median(ms)),
+                      "footholds_per_s": 4 / (np.median(ms) * 1e-3), "candidates_per_s": 4 * w * w / (np.median(ms) * 1e-3)})
+    out["sweep_c4"] = sweep
+
+    # ---- batched sweep (the bandwidth-meaningful point): robots x 4 legs x 64 x 64 windows, sharded by robot
+    robots_total, w = 2048, 64
+    R = robots_total // world
+    sc = sy.sweep_scene("go2", np.random.default_rng(90 + rank), "stepping_stones_tall", window=w, seed=4, robots=R)
+    d_jobs = torch.from_numpy(np.frombuffer(sc["jobs"].tobytes(), np.uint8).copy()).to(dev)
+    d_res = torch.zeros(4 * R * tc.RESULT_DTYPE.itemsize, dtype=torch.uint8, device=dev)
+    h = tc.Handle(p, device=local_rank, max_jobs=4 * R)
+    barrier()
+    ms = timed(h, lambda: h.score_device(d_h.data_ptr(), tc.F64, 1, 2048, 2048, 2048, d_jobs.data_ptr(), 4 * R, w, w,
+                                         d_res.data_ptr()), 20)
+    launches = h.launch_count
+    h.close()
+    step_ms = max_over_ranks(float(ms.mean()))
+    cand = robots_total * 4 * w * w
+    alg_bytes = cand * 8 / world  # each window cell read once per launch on this rank, f64
+    ach = alg_bytes / (float(ms.mean()) * 1e-3) / 1e9
+    out["batched"] = {"workload": f"{robots_total} robots x 4 legs x {w}x{w} candidate windows on a 2048x2048 f64 map; {R} robots per rank",
+                      "ms_per_step": step_ms, "footholds_per_s": robots_total * 4 / (step_ms * 1e-3),
+                      "candidates_per_s": cand / (step_ms * 1e-3), "scaling": "strong", "gpu_launches_per_step": 1,
+                      "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+                                   "traffic": None, "kernel": "k_tamols_score<double,TMA>", "launch_ms": float(ms.mean()),
+                                   "algorithmic_bytes_per_candidate": 8, "peak_source": peak_src,
+                                   "note": "FP64 arithmetic (about 330 FP64 instructions per feasible candidate) binds long before HBM: see DESIGN.md"}}
+    out["launch_count_check"] = int(launches)
+
+    # ---- e2e: one compute_adaptation-sized call (C3-T: 4 legs x 13 x 7 sensor maps) through tamols_score_host
+    rs = np.random.default_rng(300 + rank)
+    scenes = [sy.robot_scene("hyqreal1", rs, "stepping_stones") for _ in range(16)]
+    ph = tc.make_params(sy.tamols_params_for("hyqreal1"), "hyqreal1")
+    h = tc.Handle(ph, device=local_rank, max_jobs=4)
+    wall = []
+    for it in range(10 + 200):
+        s = scenes[it % 16]
+        t0 = time.perf_counter()
+        h.score_host(s["heights"], s["jobs"], xy=s["xy"])
+        if it >= 10:
+            wall.append(time.perf_counter() - t0)
+    h.close()
+    wall = np.array(wall)
+    in_b = 4 * 13 * 8 * 8 + 4 * 13 * 7 * 16 + 4 * tc.JOB_DTYPE.itemsize
+    out["e2e_c3t"] = {"workload": "C3-T: hyqreal1, 4 legs x 13x7 sensor maps (stepping stones), tamols_score_host",
+                      "p50_ms": float(np.median(wall) * 1e3), "footholds_per_s": 4 / float(np.median(wall)),
+                      "h2d_bytes_per_step": in_b, "d2h_bytes_per_step": 4 * tc.RESULT_DTYPE.itemsize}
+
+    if with_cpu:
+        from oracle import tamols_oracle as to
+        cores = to.max_threads(True)
+        t0 = time.perf_counter()
+        n = 0
+        while time.perf_counter() - t0 < 3.0:
+            s = scenes[n % 16]
+            to.score(ph, s["heights"], s["jobs"], xy=s["xy"], want_scores=False, fast=True)
+            n += 1
+        c3t = (time.perf_counter() - t0) / n
+        sub = sy.sweep_scene("go2", np.random.default_rng(91), "stepping_stones_tall", window=64, seed=4, robots=32)
+        t0 = time.perf_counter()
+        to.score(p, sub["heights"], sub["jobs"], want_scores=False, fast=True)
+        tb = time.perf_counter() - t0
+        out["cpu_baseline"] = {"kind": "port", "cores": cores,
+                               "c3t_footholds_per_s": 4 / c3t, "c3t_p50_ms": c3t * 1e3,
+                               "batched_candidates_per_s": 32 * 4 * 64 * 64 / tb,
+                               "sample": f"{n} C3-T calls (3 s) and one 32-robot x 4 x 64x64 batch ({tb:.2f} s), oracle/tamols_oracle.c -O3 OpenMP",
+                               "reference_python": "the reference's own Python loop measured 0.75 ms/candidate (15 footholds/s) in the build container (BASELINE.md section 2); it cannot travel to the GPU box"}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -327,6 +456,7 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--no-batched", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-tamols", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
