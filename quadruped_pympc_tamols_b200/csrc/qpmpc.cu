@@ -21,11 +21,12 @@
 #include "../../include/qpmpc.h"
 #include "philox.cuh"
 #include "srbd.cuh"
+#include "rollout12.cuh"
 
 namespace qp {
 
 constexpr int PART_HDR = 4;  // per-block partial: [min cost, sum w, argmin cost, argmin index bits] + V[P]
-constexpr int FIN_THREADS = 256;
+constexpr int FIN_THREADS_MAX = 512;
 
 struct RolloutArgs {
     const float *state, *reference, *contact, *best, *sigma, *timing, *nominal;
@@ -134,28 +135,33 @@ __device__ __forceinline__ float block_sum(float v, float *s_red) {
 }
 
 // ---------------------------------------------------------------- rollout kernel ---------------------------
-// Shared memory layout (floats): best[P] | sigma[P] | state[24] | ref[12] | stance[4H] | ref_fz[H] | q[H] |
-// index[H] (int) | mgk[8] | red[64] | w[T] | eps[P*T]  (eps column t belongs to thread t: conflict-free).
-__host__ __device__ inline int rollout_smem_floats(int P, int H, int T) {
-    return 2 * P + 24 + 12 + 4 * H + 3 * H + 8 + 64 + T + P * T;
+// Shared memory layout (floats):
+//   w[T] | par[P][T+1] | best[P] | sigma[P] | state[24] | ref[12] | timing[4] | st[8H] | ref_fz[H] | q[H] | index[H] (int)
+//   | mgk[8] | red[64]
+// par[p][t] = best[p] + eps[t][p] is the parameter vector of thread t's rollout, one COLUMN per thread: the rollout's
+// own reads are conflict-free, and with the row stride T+1 so are the row-wise reads of the softmin-weighted sum.
+// (sigma only exists for cem_mppi: at P = 144, T = 128 leaving it out is what lets three blocks share an SM)
+__host__ __device__ inline int rollout_smem_floats(int P, int H, int T, bool cem) {
+    return T + P * (T + 1) + (cem ? 2 : 1) * P + 24 + 12 + 4 + 8 * H + 3 * H + 8 + 64;
 }
 
-template <int PARAM, bool GA>
-__global__ void k_rollout(const __grid_constant__ DevCfg c, const RolloutArgs a) {
-    extern __shared__ float smem[];
-    const int P = c.P, H = c.H, T = blockDim.x, t = threadIdx.x;
-    float *s_best = smem;
+template <int PARAM, bool GA, int HC>
+__global__ void __launch_bounds__(128, 3) k_rollout(const __grid_constant__ DevCfg c, const RolloutArgs a) {
+    extern __shared__ __align__(16) float smem[];
+    const int P = c.P, H = c.H, T = blockDim.x, t = threadIdx.x, stride = T + 1;
+    float *s_w = smem;
+    float *s_par = s_w + T;
+    float *s_best = s_par + P * stride;
     float *s_sigma = s_best + P;
-    float *s_state = s_sigma + P;
+    float *s_state = s_sigma + (c.method == QPMPC_METHOD_CEM ? P : 0);
     float *s_ref = s_state + 24;
-    float *s_stance = s_ref + 12;
-    float *s_reffz = s_stance + 4 * H;
+    float *s_timing = s_ref + 12;
+    float *s_st = s_timing + 4;
+    float *s_reffz = s_st + 8 * H;
     float *s_q = s_reffz + H;
     int *s_index = reinterpret_cast<int *>(s_q + H);
     float *s_mgk = s_q + 2 * H;
     float *s_red = s_mgk + 8;
-    float *s_w = s_red + 64;
-    float *s_eps = s_w + T;
 
     const int r = blockIdx.y;
     const int i = blockIdx.x * T + t;
@@ -164,57 +170,81 @@ __global__ void k_rollout(const __grid_constant__ DevCfg c, const RolloutArgs a)
     // ---- stage the per-robot problem
     for (int p = t; p < P; p += T) {
         s_best[p] = a.costs_only ? 0.f : a.best[(size_t)r * P + p];
-        s_sigma[p] = (c.method == QPMPC_METHOD_CEM && a.sigma) ? a.sigma[(size_t)r * P + p] : 0.f;
+        if (c.method == QPMPC_METHOD_CEM) s_sigma[p] = a.sigma ? a.sigma[(size_t)r * P + p] : 0.f;
     }
     for (int k = t; k < 24; k += T) s_state[k] = a.state[r * 24 + k];
     for (int k = t; k < 12; k += T) s_ref[k] = a.reference[r * 24 + k];
     if (!GA) {
-        for (int k = t; k < 4 * H; k += T) s_stance[k] = a.contact[(size_t)r * 4 * H + k];
+        const float *cs = a.contact + (size_t)r * 4 * H;
         for (int n = t; n < H; n += T) {
-            const float *cs = a.contact + (size_t)r * 4 * H;
-            const float nst = ((cs[n] + cs[H + n]) + cs[2 * H + n]) + cs[3 * H + n];
-            s_reffz[n] = c.mg / nst;
-            const int idx = chunk_index(c, (float)n);
-            s_index[n] = idx;
-            s_q[n] = chunk_tau(c, (float)n, (float)H, idx);
+            const float s0 = cs[n], s1 = cs[H + n], s2 = cs[2 * H + n], s3 = cs[3 * H + n];
+            s_reffz[n] = c.mg / (((s0 + s1) + s2) + s3);
+            if (HC == H12) {  // [n][8] = {st[4], st[4] / 3}
+                s_st[8 * n + 0] = s0; s_st[8 * n + 1] = s1; s_st[8 * n + 2] = s2; s_st[8 * n + 3] = s3;
+                s_st[8 * n + 4] = s0 * (1.0f / 3.0f); s_st[8 * n + 5] = s1 * (1.0f / 3.0f);
+                s_st[8 * n + 6] = s2 * (1.0f / 3.0f); s_st[8 * n + 7] = s3 * (1.0f / 3.0f);
+            } else {          // [leg][H] as the generic path reads it
+                s_st[n] = s0; s_st[H + n] = s1; s_st[2 * H + n] = s2; s_st[3 * H + n] = s3;
+                const int idx = chunk_index(c, (float)n);
+                s_index[n] = idx;
+                s_q[n] = chunk_tau(c, (float)n, (float)H, idx);
+            }
         }
-    } else if (t < 5) {
-        s_mgk[t] = c.mg / (float)t;
+    } else {
+        if (t < 5) s_mgk[t] = c.mg / (float)t;
+        if (t < 4) s_timing[t] = a.timing[r * 4 + t];
     }
     __syncthreads();
 
-    // ---- this thread's noise row -> shared column t
+    // ---- this thread's parameter vector -> shared column t
     const uint32_t robot = (uint32_t)r;
     if (a.eps) {
         const float *src = a.eps + ((size_t)r * a.n + (size_t)blockIdx.x * T) * P;
         const int rows = min(T, a.n - blockIdx.x * T);
-        for (int e = t; e < rows * P; e += T) s_eps[(e % P) * T + e / P] = src[e];
+        for (int e = t; e < rows * P; e += T) {
+            const int row = e / P, p = e - row * P;
+            s_par[p * stride + row] = s_best[p] + src[e];
+        }
+        if (!valid)
+            for (int p = 0; p < P; ++p) s_par[p * stride + t] = 0.f;
         __syncthreads();
     } else if (valid) {
+#pragma unroll 2
         for (int g = 0; g < P / 4; ++g) {
             const float4 e = noise_group(c, a.key, s_sigma, i, g, robot);
-            s_eps[(4 * g + 0) * T + t] = e.x;
-            s_eps[(4 * g + 1) * T + t] = e.y;
-            s_eps[(4 * g + 2) * T + t] = e.z;
-            s_eps[(4 * g + 3) * T + t] = e.w;
+            const float4 b = *reinterpret_cast<const float4 *>(s_best + 4 * g);
+            float *dst = s_par + (4 * g) * stride + t;
+            dst[0] = b.x + e.x;
+            dst[stride] = b.y + e.y;
+            dst[2 * stride] = b.z + e.z;
+            dst[3 * stride] = b.w + e.w;
         }
+    } else {
+        for (int p = 0; p < P; ++p) s_par[p * stride + t] = 0.f;  // tail block: keeps the weighted sum finite
     }
 
     // ---- rollout
     float cost = INFINITY;
     if (valid) {
-        const int np = c.np;
-        auto par = [&](int leg, int j) { return s_best[leg * np + j] + s_eps[(leg * np + j) * T + t]; };
-        if (GA) {
-            float timing[4];
-#pragma unroll
-            for (int l = 0; l < 4; ++l) timing[l] = a.timing[r * 4 + l];
-            const float freq = a.freqs ? a.freqs[(size_t)r * a.n + i]
-                                       : freq_sample(c, a.key, i, robot, a.nominal[r], a.oswing[r]);
-            cost = rollout_gait_adaptive<PARAM>(c, s_state, s_ref, s_mgk, timing, freq, par);
+        const float *col = s_par + t;
+        float freq = 0.f;
+        if (GA)
+            freq = a.freqs ? a.freqs[(size_t)r * a.n + i] : freq_sample(c, a.key, i, robot, a.nominal[r], a.oswing[r]);
+        if (HC == H12) {
+            cost = GA ? rollout12_ga<PARAM>(c, s_state, s_ref, s_mgk, s_timing, freq, col, stride)
+                      : rollout12_fixed<PARAM>(c, s_state, s_ref, s_st, s_reffz, col, stride);
         } else {
-            const StepTables tb = {s_stance, s_reffz, s_index, s_q};
-            cost = rollout_fixed<PARAM>(c, s_state, s_ref, tb, par);
+            const int np = c.np;
+            auto par = [&](int leg, int j) { return col[(leg * np + j) * stride]; };
+            if (GA) {
+                float timing[4];
+#pragma unroll
+                for (int l = 0; l < 4; ++l) timing[l] = s_timing[l];
+                cost = rollout_gait_adaptive<PARAM>(c, s_state, s_ref, s_mgk, timing, freq, par);
+            } else {
+                const StepTables tb = {s_st, s_reffz, s_index, s_q};
+                cost = rollout_fixed<PARAM>(c, s_state, s_ref, tb, par);
+            }
         }
         if (!a.costs_only) {  // centroidal_nmpc_jax.py:686-687
             cost = isnan(cost) ? 1000000.0f : cost;
@@ -239,7 +269,7 @@ __global__ void k_rollout(const __grid_constant__ DevCfg c, const RolloutArgs a)
         return;
     }
     // softmin numerators relative to the block minimum (merged exactly in k_finalize), :828-836
-    const float w = valid ? expf(-(cost - bc)) : 0.f;
+    const float w = valid ? __expf(-(cost - bc)) : 0.f;
     s_w[t] = w;
     const float sw = block_sum(w, s_red);  // contains the __syncthreads that publishes s_w
     if (t == 0) {
@@ -248,15 +278,279 @@ __global__ void k_rollout(const __grid_constant__ DevCfg c, const RolloutArgs a)
         part[2] = bc;
         part[3] = __int_as_float(bi);
     }
+    // V[p] = sum_t w_t par[p][t]; k_finalize turns sum_b scale_b V_b / sum_b scale_b sw_b into the updated parameters
     for (int p = t; p < P; p += T) {
-        const float *row = s_eps + p * T;
-        float acc = 0.f;
-        for (int k = 0; k < T; ++k) {
-            const int tt = (k + t) & (T - 1);  // skew: lanes of a warp hit distinct banks (T is a power of two)
-            const float wt = s_w[tt];
-            acc += (wt == 0.f) ? 0.f : wt * row[tt];  // rows of invalid threads are never initialised
+        const float *row = s_par + p * stride;
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll 4
+        for (int k = 0; k < T; k += 4) {
+            const float4 w4 = *reinterpret_cast<const float4 *>(s_w + k);
+            a0 = fmaf(w4.x, row[k], a0);
+            a1 = fmaf(w4.y, row[k + 1], a1);
+            a2 = fmaf(w4.z, row[k + 2], a2);
+            a3 = fmaf(w4.w, row[k + 3], a3);
         }
-        part[PART_HDR + p] = acc;
+        part[PART_HDR + p] = (a0 + a1) + (a2 + a3);
+    }
+}
+
+// ---------------------------------------------------------------- quad rollout kernel (latency regime) ------
+// One solve of ONE robot is 10,000 rollouts = 313 warps for 592 warp schedulers: with a thread per rollout most of
+// the machine idles and every warp runs a ~9,000-instruction dependent chain.  Here FOUR lanes share a rollout, one
+// per leg: a lane generates a quarter of the rollout's noise, evaluates its own leg's spline, force limits, lever arm
+// and torque, the quad sums the six force/torque components with two shuffle stages, the three sin/cos pairs are
+// computed by three different lanes and exchanged, and each lane accumulates a quarter of the stage cost.  4x the
+// warps, a ~3x shorter chain per warp, and a looped (not unrolled) body that stays in the instruction cache on a
+// first and only wave.  Runtime horizon / spline count: this is also the kernel for any non-default horizon when
+// the launch is small.
+// Shared memory (floats): w[QB] | par[P][QB+1] | best[P] | sigma[P] | state[24] | ref[12] | timing[4] | stance[4H] |
+//   ref_fz[H] | q[H] | index[H] | mgk[8] | cost[QB]
+constexpr int QB = 32;  // rollouts per 128-thread block
+__host__ __device__ inline int quad_smem_floats(int P, int H) {
+    return QB + P * (QB + 1) + 2 * P + 24 + 12 + 4 + 4 * H + 3 * H + 8 + QB;
+}
+
+__device__ __forceinline__ float quad_sum(float v) {
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    return v;
+}
+
+template <int PARAM, bool GA>
+__global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__ DevCfg c, const RolloutArgs a) {
+    extern __shared__ __align__(16) float smem[];
+    constexpr int T = 4 * QB, stride = QB + 1;
+    const int P = c.P, H = c.H, t = threadIdx.x;
+    const int leg = t & 3, rb = t >> 2, lane = t & 31, qbase = lane & ~3;
+    float *s_w = smem;
+    float *s_par = s_w + QB;
+    float *s_best = s_par + P * stride;
+    float *s_sigma = s_best + P;
+    float *s_state = s_sigma + P;
+    float *s_ref = s_state + 24;
+    float *s_timing = s_ref + 12;
+    float *s_stance = s_timing + 4;
+    float *s_reffz = s_stance + 4 * H;
+    float *s_q = s_reffz + H;
+    int *s_index = reinterpret_cast<int *>(s_q + H);
+    float *s_mgk = s_q + 2 * H;
+    float *s_cost = s_mgk + 8;
+
+    const int r = blockIdx.y;
+    const int i = blockIdx.x * QB + rb;
+    const bool valid = i < a.n;
+
+    // ---- stage the per-robot problem
+    for (int p = t; p < P; p += T) {
+        s_best[p] = a.costs_only ? 0.f : a.best[(size_t)r * P + p];
+        s_sigma[p] = (c.method == QPMPC_METHOD_CEM && a.sigma) ? a.sigma[(size_t)r * P + p] : 0.f;
+    }
+    if (t < 24) s_state[t] = a.state[r * 24 + t];
+    if (t >= 32 && t < 44) s_ref[t - 32] = a.reference[r * 24 + t - 32];
+    if (!GA) {
+        const float *cs = a.contact + (size_t)r * 4 * H;
+        for (int k = t; k < 4 * H; k += T) s_stance[k] = cs[k];
+        for (int n = t; n < H; n += T) {
+            s_reffz[n] = c.mg / (((cs[n] + cs[H + n]) + cs[2 * H + n]) + cs[3 * H + n]);
+            const int idx = chunk_index(c, (float)n);
+            s_index[n] = idx;
+            s_q[n] = chunk_tau(c, (float)n, (float)H, idx);
+        }
+    } else {
+        if (t >= 64 && t < 69) s_mgk[t - 64] = c.mg / (float)(t - 64);
+        if (t >= 96 && t < 100) s_timing[t - 96] = a.timing[r * 4 + t - 96];
+    }
+    __syncthreads();
+
+    // ---- parameters of the block's 32 rollouts -> columns of s_par; lane `leg` draws groups leg, leg + 4, ...
+    const uint32_t robot = (uint32_t)r;
+    if (a.eps) {
+        const float *src = a.eps + ((size_t)r * a.n + (size_t)blockIdx.x * QB) * P;
+        const int rows = min(QB, a.n - blockIdx.x * QB);
+        for (int e = t; e < QB * P; e += T) {
+            const int row = e / P, p = e - row * P;
+            s_par[p * stride + row] = row < rows ? s_best[p] + src[e] : 0.f;
+        }
+        __syncthreads();
+    } else {
+        for (int g = leg; g < P / 4; g += 4) {
+            float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
+            float4 b = e;
+            if (valid) {
+                e = noise_group(c, a.key, s_sigma, i, g, robot);
+                b = *reinterpret_cast<const float4 *>(s_best + 4 * g);
+            }
+            float *dst = s_par + (4 * g) * stride + rb;
+            dst[0] = b.x + e.x;
+            dst[stride] = b.y + e.y;
+            dst[2 * stride] = b.z + e.z;
+            dst[3 * stride] = b.w + e.w;
+        }
+        __syncwarp();
+    }
+
+    // ---- rollout: lane = leg
+    float x[12], ref[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) {
+        x[k] = s_state[k];
+        ref[k] = s_ref[k];
+    }
+    const float footx = s_state[12 + 3 * leg], footy = s_state[13 + 3 * leg], footz = s_state[14 + 3 * leg];
+    const float qa = c.q[3 * leg], qb = c.q[3 * leg + 1], qc = c.q[3 * leg + 2];
+    const float *col = s_par + rb;
+    const int np = c.np;
+    float freq = 0.f, hl = (float)H;
+    uint32_t bits = 0;
+    if (GA) {
+        // step frequency of this rollout, then the leg's own trot clock (periodic_gait_generator_jax.py:68-89)
+        freq = valid ? (a.freqs ? a.freqs[(size_t)r * a.n + i] : freq_sample(c, a.key, i, robot, a.nominal[r], a.oswing[r]))
+                     : 1.0f;
+        const float inc = __fmul_rn(c.mpc_dt, freq);
+        float tt = s_timing[leg];
+        for (int n = 0; n < H; ++n) {
+            tt = (tt >= 1.0f) ? 0.0f : tt;
+            tt = __fadd_rn(tt, inc);
+            bits |= (tt < c.duty ? 1u : 0u) << n;
+        }
+        hl = (float)(__popc(bits) + 1);  // horizon_leg = sum(contact) + 1, ..._gait_adaptive.py:345-348
+    }
+    float cost = 0.f;
+    int ncnt = -1;
+#pragma unroll 1
+    for (int n = 0; n < H; ++n) {
+        float st, ref_fz, q;
+        int istep, index;
+        if (GA) {
+            const int on = (bits >> n) & 1;
+            const unsigned bal = __ballot_sync(0xffffffffu, on);
+            st = (float)on;
+            ref_fz = s_mgk[__popc((bal >> qbase) & 0xFu)];
+            ncnt += on;  // the leg's own step counter advances only in stance, :353-356
+            istep = ncnt;
+            index = 0;
+            q = 0.f;
+            if (PARAM != QPMPC_PARAM_ZERO_ORDER) {
+                index = chunk_index(c, (float)ncnt);
+                q = chunk_tau(c, (float)ncnt, hl, index);
+            }
+        } else {
+            st = s_stance[leg * H + n];
+            ref_fz = s_reffz[n];
+            istep = n;
+            index = s_index[n];
+            q = s_q[n];
+        }
+        CubicBasis B = {1.f, 0.f, 0.f, 0.f};
+        if (PARAM == QPMPC_PARAM_CUBIC) B = cubic_basis(q);
+        float f[3];
+        spline_eval<PARAM>(c, [&](int j) { return col[(leg * np + j) * stride]; }, istep, index, q, B, f);
+        shape_leg(c, f, st, st * (1.0f / 3.0f), ref_fz);
+        // this leg's share of the net force and of the torque about the centre of mass, summed over the quad
+        const float fzs = f[2] * st;
+        const float rx = footx - x[0], ry = footy - x[1], rz = footz - x[2];
+        const float lx = quad_sum(f[0]), ly = quad_sum(f[1]), lz = quad_sum(fzs);
+        const float tx = quad_sum(ry * fzs - rz * f[1]);
+        const float ty = quad_sum(rz * f[0] - rx * fzs);
+        const float tz = quad_sum(rx * f[1] - ry * f[0]);
+        // lanes 0, 1, 2 of the quad evaluate sin/cos of roll, pitch, yaw and hand them round
+        const float ang = leg == 0 ? x[6] : (leg == 1 ? x[7] : x[8]);
+        float sa, ca;
+        sincosf(ang, &sa, &ca);
+        const float sr = __shfl_sync(0xffffffffu, sa, qbase), cr = __shfl_sync(0xffffffffu, ca, qbase);
+        const float sp = __shfl_sync(0xffffffffu, sa, qbase + 1), cp = __shfl_sync(0xffffffffu, ca, qbase + 1);
+        const float sy = __shfl_sync(0xffffffffu, sa, qbase + 2), cy = __shfl_sync(0xffffffffu, ca, qbase + 2);
+        const float wx = x[9], wy = x[10], wz = x[11];
+        const float yaw_rate = (sr * wy + cr * wz) / cp;
+        const float pitch_rate = cr * wy - sr * wz;
+        const float roll_rate = wx + sp * yaw_rate;
+        const float bx = cp * cy * tx + cp * sy * ty - sp * tz;
+        const float by = (sr * sp * cy - cr * sy) * tx + (sr * sp * sy + cr * cy) * ty + sr * cp * tz;
+        const float bz = (cr * sp * cy + sr * sy) * tx + (cr * sp * sy - sr * cy) * ty + cr * cp * tz;
+        const float Iwx = c.I[0] * wx + c.I[1] * wy + c.I[2] * wz;
+        const float Iwy = c.I[3] * wx + c.I[4] * wy + c.I[5] * wz;
+        const float Iwz = c.I[6] * wx + c.I[7] * wy + c.I[8] * wz;
+        const float gx = bx - (wy * Iwz - wz * Iwy);
+        const float gy = by - (wz * Iwx - wx * Iwz);
+        const float gz = bz - (wx * Iwy - wy * Iwx);
+        const float dt = c.dts[n];
+        x[0] += x[3] * dt;
+        x[1] += x[4] * dt;
+        x[2] += x[5] * dt;
+        x[3] += (c.inv_mass * lx) * dt;
+        x[4] += (c.inv_mass * ly) * dt;
+        x[5] += (c.inv_mass * lz - 9.81f) * dt;
+        x[6] += roll_rate * dt;
+        x[7] += pitch_rate * dt;
+        x[8] += yaw_rate * dt;
+        x[9] += (c.Iinv[0] * gx + c.Iinv[1] * gy + c.Iinv[2] * gz) * dt;
+        x[10] += (c.Iinv[3] * gx + c.Iinv[4] * gy + c.Iinv[5] * gz) * dt;
+        x[11] += (c.Iinv[6] * gx + c.Iinv[7] * gy + c.Iinv[8] * gz) * dt;
+        // stage cost: lane `leg` owns the terms of states 3 leg .. 3 leg + 2
+        const float ea = (leg == 0 ? x[0] : leg == 1 ? x[3] : leg == 2 ? x[6] : x[9]) -
+                         (leg == 0 ? ref[0] : leg == 1 ? ref[3] : leg == 2 ? ref[6] : ref[9]);
+        const float eb = (leg == 0 ? x[1] : leg == 1 ? x[4] : leg == 2 ? x[7] : x[10]) -
+                         (leg == 0 ? ref[1] : leg == 1 ? ref[4] : leg == 2 ? ref[7] : ref[10]);
+        const float ec = (leg == 0 ? x[2] : leg == 1 ? x[5] : leg == 2 ? x[8] : x[11]) -
+                         (leg == 0 ? ref[2] : leg == 1 ? ref[5] : leg == 2 ? ref[8] : ref[11]);
+        cost += (ea * qa) * ea;
+        cost += (eb * qb) * eb;
+        cost += (ec * qc) * ec;
+    }
+    cost = quad_sum(cost);
+    if (GA) {
+        const float df = freq - 1.3f;
+        cost += df * 100.f * df;  // ..._gait_adaptive.py:500
+    }
+    if (!a.costs_only) {  // centroidal_nmpc_jax.py:686-687
+        cost = isnan(cost) ? 1000000.0f : cost;
+        cost = isinf(cost) ? 1000000.0f : cost;
+    }
+    if (leg == 0) {
+        if (valid) a.costs[(size_t)r * a.n + i] = cost;
+        s_cost[rb] = valid ? cost : INFINITY;
+    }
+    if (a.costs_only) return;
+    __syncthreads();
+
+    // ---- block partials: warp 0 owns the 32 costs
+    float *part = a.partials + ((size_t)r * a.nblk + blockIdx.x) * (PART_HDR + P);
+    if (t < 32) {
+        const float ct = s_cost[t];
+        const int it = blockIdx.x * QB + t;
+        float bc = ct;
+        int bi = it < a.n ? it : 0x7fffffff;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float oc = __shfl_xor_sync(0xffffffffu, bc, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            argmin_combine(bc, bi, oc, oi);
+        }
+        float w = it < a.n ? __expf(-(ct - bc)) : 0.f;
+        s_w[t] = w;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) w += __shfl_xor_sync(0xffffffffu, w, o);
+        if (t == 0) {
+            part[0] = bc;
+            part[1] = c.method == QPMPC_METHOD_RANDOM ? 0.f : w;
+            part[2] = bc;
+            part[3] = __int_as_float(bi);
+        }
+    }
+    if (c.method == QPMPC_METHOD_RANDOM) return;
+    __syncthreads();
+    for (int p = t; p < P; p += T) {
+        const float *row = s_par + p * stride;
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+        for (int k = 0; k < QB; k += 4) {
+            const float4 w4 = *reinterpret_cast<const float4 *>(s_w + k);
+            a0 = fmaf(w4.x, row[k], a0);
+            a1 = fmaf(w4.y, row[k + 1], a1);
+            a2 = fmaf(w4.z, row[k + 2], a2);
+            a3 = fmaf(w4.w, row[k + 3], a3);
+        }
+        part[PART_HDR + p] = (a0 + a1) + (a2 + a3);
     }
 }
 
@@ -296,12 +590,15 @@ __device__ void grf_and_prediction(const DevCfg &c, const float *s_best, const f
     }
 }
 
-__global__ void __launch_bounds__(FIN_THREADS) k_finalize(const __grid_constant__ DevCfg c, const FinalizeArgs a) {
+__global__ void __launch_bounds__(FIN_THREADS_MAX) k_finalize(const __grid_constant__ DevCfg c, const FinalizeArgs a) {
     extern __shared__ float smem[];
     const int P = c.P, N = c.N, t = threadIdx.x, r = blockIdx.x;
+    const int lane = t & 31, wid = t >> 5, nw = blockDim.x >> 5;
     float *s_best = smem;
     float *s_red = s_best + P;
     int *s_sel = reinterpret_cast<int *>(s_red + 64);
+    float *s_sc = reinterpret_cast<float *>(s_sel + ((c.method == QPMPC_METHOD_CEM ? c.cem_elite : 0) + 8));
+    float *s_acc = s_sc + a.nblk;  // [nw][P]
     const float *part = a.partials + (size_t)r * a.nblk * (PART_HDR + P);
     const int stride = PART_HDR + P;
     const uint32_t robot = (uint32_t)r;
@@ -325,16 +622,35 @@ __global__ void __launch_bounds__(FIN_THREADS) k_finalize(const __grid_constant_
             }
             s_best[p] = __fadd_rn(a.best[(size_t)r * P + p], e);
         }
-    } else {  // best += sum_i w_i eps_i, w = softmin(costs), :828-836
-        float den = 0.f;
-        for (int b = 0; b < a.nblk; ++b) den += part[(size_t)b * stride + 1] * expf(-(part[(size_t)b * stride] - bc));
+    } else {
+        // best + sum_i w_i eps_i = sum_i w_i par_i / sum_i w_i with w = softmin(costs), :828-836.  Each rollout block
+        // left {min_b, sum_t w, V[P]} relative to its own minimum; rescale by exp(-(min_b - min)) and merge:
+        // warps stride over the blocks, lanes over the parameters (coalesced rows), then a cross-warp sum.
+        float dpart = 0.f;
+        for (int b = t; b < a.nblk; b += blockDim.x) {
+            const float sc = __expf(-(part[(size_t)b * stride] - bc));
+            s_sc[b] = sc;
+            dpart += part[(size_t)b * stride + 1] * sc;
+        }
+        const float den = block_sum(dpart, s_red);  // its barriers also publish s_sc
+        for (int p0 = 0; p0 < P; p0 += 32) {
+            const int p = p0 + lane;
+            float acc = 0.f;
+            if (p < P) {
+#pragma unroll 4
+                for (int b = wid; b < a.nblk; b += nw) {
+                    const float sc = s_sc[b];
+                    const float v = part[(size_t)b * stride + PART_HDR + p];
+                    acc += (sc == 0.f) ? 0.f : sc * v;
+                }
+                s_acc[wid * P + p] = acc;
+            }
+        }
+        __syncthreads();
         for (int p = t; p < P; p += blockDim.x) {
             float num = 0.f;
-            for (int b = 0; b < a.nblk; ++b) {
-                const float sc = expf(-(part[(size_t)b * stride] - bc));
-                num += (sc == 0.f) ? 0.f : sc * part[(size_t)b * stride + PART_HDR + p];
-            }
-            s_best[p] = a.best[(size_t)r * P + p] + num / den;
+            for (int w = 0; w < nw; ++w) num += s_acc[w * P + p];
+            s_best[p] = num / den;
         }
     }
     __syncthreads();
@@ -439,12 +755,15 @@ static int fail(int code, const std::string &msg) {
             return fail(QPMPC_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));               \
     } while (0)
 
+typedef void (*rollout_fn)(const qp::DevCfg, const qp::RolloutArgs);
+
 struct qpmpc_handle {
     qpmpc_config cfg;
     DevCfg dc;
     int device;
     cudaStream_t stream;
-    int T_single, T_batch;
+    int num_sms;
+    rollout_fn fn, fn_quad;
     size_t max_smem;
     // single-robot staging: one pinned input block, one pinned output block
     float *h_in, *d_in;
@@ -480,23 +799,69 @@ static void inverse3(const float A[9], float out[9]) {
     out[8] = (a22 * a11 - a21 * a12) / det;
 }
 
-typedef void (*rollout_fn)(const DevCfg, const RolloutArgs);
-static rollout_fn pick_rollout(int param, int ga) {
-    switch (param * 2 + (ga ? 1 : 0)) {
-        case 0: return k_rollout<QPMPC_PARAM_ZERO_ORDER, false>;
-        case 1: return k_rollout<QPMPC_PARAM_ZERO_ORDER, true>;
-        case 2: return k_rollout<QPMPC_PARAM_LINEAR, false>;
-        case 3: return k_rollout<QPMPC_PARAM_LINEAR, true>;
-        case 4: return k_rollout<QPMPC_PARAM_CUBIC, false>;
-        default: return k_rollout<QPMPC_PARAM_CUBIC, true>;
+// fast = the fully unrolled horizon-12 kernels (rollout12.cuh); otherwise the generic runtime-horizon kernels
+static rollout_fn pick_rollout(int param, int ga, bool fast) {
+    switch (param * 2 + (ga ? 1 : 0) + (fast ? 6 : 0)) {
+        case 0: return k_rollout<QPMPC_PARAM_ZERO_ORDER, false, 0>;
+        case 1: return k_rollout<QPMPC_PARAM_ZERO_ORDER, true, 0>;
+        case 2: return k_rollout<QPMPC_PARAM_LINEAR, false, 0>;
+        case 3: return k_rollout<QPMPC_PARAM_LINEAR, true, 0>;
+        case 4: return k_rollout<QPMPC_PARAM_CUBIC, false, 0>;
+        case 5: return k_rollout<QPMPC_PARAM_CUBIC, true, 0>;
+        case 6: return k_rollout<QPMPC_PARAM_ZERO_ORDER, false, H12>;
+        case 7: return k_rollout<QPMPC_PARAM_ZERO_ORDER, true, H12>;
+        case 8: return k_rollout<QPMPC_PARAM_LINEAR, false, H12>;
+        case 9: return k_rollout<QPMPC_PARAM_LINEAR, true, H12>;
+        case 10: return k_rollout<QPMPC_PARAM_CUBIC, false, H12>;
+        default: return k_rollout<QPMPC_PARAM_CUBIC, true, H12>;
     }
 }
+static rollout_fn pick_quad(int param, int ga) {
+    switch (param * 2 + (ga ? 1 : 0)) {
+        case 0: return k_rollout_quad<QPMPC_PARAM_ZERO_ORDER, false>;
+        case 1: return k_rollout_quad<QPMPC_PARAM_ZERO_ORDER, true>;
+        case 2: return k_rollout_quad<QPMPC_PARAM_LINEAR, false>;
+        case 3: return k_rollout_quad<QPMPC_PARAM_LINEAR, true>;
+        case 4: return k_rollout_quad<QPMPC_PARAM_CUBIC, false>;
+        default: return k_rollout_quad<QPMPC_PARAM_CUBIC, true>;
+    }
+}
+// QPMPC_KERNEL=quad|thread|generic pins the kernel choice (tests exercise every kernel at every size with it)
+static const char *kernel_override() {
+    const char *e = getenv("QPMPC_KERNEL");
+    return e ? e : "";
+}
+static bool is_fast(const DevCfg &d) {
+    return d.H == H12 && (d.param == QPMPC_PARAM_ZERO_ORDER || d.S == 2) && strcmp(kernel_override(), "generic") != 0;
+}
 
-static int pick_threads(const qpmpc_handle *h, long long total_rollouts) {
-    // enough blocks to cover the 148 SMs several times -> 128-thread blocks; otherwise 64 (latency regime)
-    int T = total_rollouts >= 148LL * 128 * 8 ? 128 : 64;
-    while (T > 32 && (size_t)rollout_smem_floats(h->dc.P, h->dc.H, T) * 4 > h->max_smem) T >>= 1;
-    return T;
+struct LaunchPlan {
+    bool quad;    // k_rollout_quad (4 lanes per rollout) instead of k_rollout (1 thread per rollout)
+    int T, nblk;  // threads per block, blocks per robot
+    size_t smem;
+};
+// Latency regime (fewer than two rollouts-as-threads warps per SM sub-partition, e.g. one robot x 10,000 rollouts):
+// the quad kernel.  Throughput regime (batched robots): one thread per rollout, 128-thread blocks.
+static LaunchPlan plan_launch(const qpmpc_handle *h, int n, long long total_rollouts) {
+    const DevCfg &d = h->dc;
+    const long long subparts = (long long)h->num_sms * 4;
+    LaunchPlan pl;
+    pl.quad = total_rollouts < subparts * 32 * 2;
+    if (!strcmp(kernel_override(), "quad")) pl.quad = true;
+    if (!strcmp(kernel_override(), "thread") || !strcmp(kernel_override(), "generic")) pl.quad = false;
+    if (pl.quad && (size_t)quad_smem_floats(d.P, d.H) * 4 > h->max_smem) pl.quad = false;
+    if (pl.quad) {
+        pl.T = 4 * QB;
+        pl.nblk = (n + QB - 1) / QB;
+        pl.smem = (size_t)quad_smem_floats(d.P, d.H) * 4;
+    } else {
+        int T = total_rollouts < subparts * 32 * 8 ? 64 : 128;
+        while (T > 32 && (size_t)rollout_smem_floats(d.P, d.H, T, d.method == QPMPC_METHOD_CEM) * 4 > h->max_smem) T >>= 1;
+        pl.T = T;
+        pl.nblk = (n + T - 1) / T;
+        pl.smem = (size_t)rollout_smem_floats(d.P, d.H, T, d.method == QPMPC_METHOD_CEM) * 4;
+    }
+    return pl;
 }
 
 extern "C" const char *qpmpc_last_error(void) { return g_err.c_str(); }
@@ -556,11 +921,15 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     for (int k = 0; k <= d.S; ++k) d.bounds[k] = (float)((double)d.H * (double)k / (double)d.S);
 
     h->max_smem = prop.sharedMemPerBlockOptin;
-    rollout_fn fn = pick_rollout(d.param, d.ga);
+    h->num_sms = prop.multiProcessorCount;
+    rollout_fn fn = pick_rollout(d.param, d.ga, is_fast(d));
+    h->fn = fn;
     cudaError_t e = cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_smem);
     if (e != cudaSuccess) { delete h; return fail(QPMPC_E_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e)); }
-    h->T_single = pick_threads(h, d.N);
-    h->T_batch = pick_threads(h, (long long)d.N * c.max_robots);
+    h->fn_quad = pick_quad(d.param, d.ga);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute((const void *)h->fn_quad, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_smem);
+    if (e != cudaSuccess) { delete h; return fail(QPMPC_E_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e)); }
 
     const int H = d.H;
     h->in_floats = 24 + 24 + 4 * H + P + P + 4 + 2;  // state ref contact best sigma timing nominal oswing
@@ -606,10 +975,11 @@ extern "C" void *qpmpc_stream(qpmpc_handle *h) { return h ? (void *)h->stream : 
 extern "C" int64_t qpmpc_launch_count(const qpmpc_handle *h) { return h ? h->launches : 0; }
 
 // launches k_rollout + k_finalize for `b` on the handle's stream (no synchronisation)
-static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, uint64_t offset, int T) {
+static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, uint64_t offset) {
     const DevCfg &d = h->dc;
     const int R = b.num_robots, N = d.N, P = d.P;
-    const int nblk = (N + T - 1) / T;
+    const LaunchPlan pl = plan_launch(h, N, (long long)N * R);
+    const int nblk = pl.nblk;
     if ((size_t)R * nblk * (PART_HDR + P) > h->partial_floats) return fail(QPMPC_E_ARG, "internal: partial buffer too small");
     RolloutArgs ra;
     ra.state = b.d_state; ra.reference = b.d_reference; ra.contact = b.d_contact_sequence; ra.best = b.d_best_in;
@@ -617,9 +987,8 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
     ra.eps = b.d_eps; ra.freqs = b.d_freqs;
     ra.costs = b.d_costs ? b.d_costs : h->d_costs; ra.partials = h->d_partials;
     ra.key = NoiseKey{seed, offset}; ra.n = N; ra.costs_only = 0; ra.nblk = nblk;
-    const size_t smem = (size_t)rollout_smem_floats(P, d.H, T) * 4;
     if (h->profiling) CU(cudaEventRecord(h->ev[0], h->stream));
-    pick_rollout(d.param, d.ga)<<<dim3(nblk, R), T, smem, h->stream>>>(d, ra);
+    (pl.quad ? h->fn_quad : h->fn)<<<dim3(nblk, R), pl.T, pl.smem, h->stream>>>(d, ra);
     CU(cudaGetLastError());
     if (h->profiling) CU(cudaEventRecord(h->ev[1], h->stream));
     FinalizeArgs fa;
@@ -628,8 +997,11 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
     fa.eps = b.d_eps; fa.freqs = b.d_freqs; fa.costs = ra.costs; fa.partials = h->d_partials;
     fa.result = b.d_result; fa.best_out = b.d_best_out; fa.sigma_out = b.d_sigma_out;
     fa.key = ra.key; fa.nblk = nblk;
-    const size_t fsmem = (size_t)(P + 64 + (d.method == QPMPC_METHOD_CEM ? d.cem_elite : 0) + 8) * 4;
-    k_finalize<<<R, FIN_THREADS, fsmem, h->stream>>>(d, fa);
+    // one block per robot: 512 threads when there are many rollout blocks to merge (single robot), 128 otherwise
+    const int fin_threads = nblk > 16 ? FIN_THREADS_MAX : 128;
+    const size_t fsmem = (size_t)(P + 64 + (d.method == QPMPC_METHOD_CEM ? d.cem_elite : 0) + 8 + nblk +
+                                  (fin_threads / 32) * P) * 4;
+    k_finalize<<<R, fin_threads, fsmem, h->stream>>>(d, fa);
     CU(cudaGetLastError());
     if (h->profiling) CU(cudaEventRecord(h->ev[2], h->stream));
     h->launches += 2;
@@ -647,7 +1019,7 @@ extern "C" int qpmpc_solve_batched(qpmpc_handle *h, const qpmpc_batch *batch, ui
     if (h->dc.ga && !b.d_freqs && (!b.d_nominal_freq || !b.d_optimize_swing))
         return fail(QPMPC_E_ARG, "gait adaptive needs d_nominal_freq and d_optimize_swing");
     CU(cudaSetDevice(h->device));
-    return launch_solve(h, b, seed, offset, pick_threads(h, (long long)h->dc.N * b.num_robots));
+    return launch_solve(h, b, seed, offset);
 }
 
 extern "C" int qpmpc_solve(qpmpc_handle *h, const float *state, const float *reference, const float *contact_sequence,
@@ -687,7 +1059,7 @@ extern "C" int qpmpc_solve(qpmpc_handle *h, const float *state, const float *ref
     b.d_best_out = h->d_out + res_floats;
     b.d_sigma_out = (d.method == QPMPC_METHOD_CEM) ? h->d_out + res_floats + P : nullptr;
     b.d_costs = h->d_costs;
-    int rc = launch_solve(h, b, seed, offset, h->T_single);
+    int rc = launch_solve(h, b, seed, offset);
     if (rc) return rc;
     CU(cudaMemcpyAsync(h->h_out, h->d_out, h->out_floats * 4, cudaMemcpyDeviceToHost, h->stream));
     if (costs_out) CU(cudaMemcpyAsync(h->h_out + h->out_floats, h->d_costs, (size_t)N * 4, cudaMemcpyDeviceToHost, h->stream));
@@ -719,10 +1091,9 @@ extern "C" int qpmpc_rollout_costs(qpmpc_handle *h, const float *state, const fl
     memset(&ra, 0, sizeof ra);
     ra.state = h->d_in; ra.reference = h->d_in + 24; ra.contact = h->d_in + 48; ra.timing = h->d_in + o_timing;
     ra.eps = d_params; ra.freqs = d_freqs; ra.costs = d_costs; ra.n = n; ra.costs_only = 1;
-    const int T = pick_threads(h, n);
-    ra.nblk = (n + T - 1) / T;
-    const size_t smem = (size_t)rollout_smem_floats(P, H, T) * 4;
-    pick_rollout(d.param, d.ga)<<<dim3(ra.nblk, 1), T, smem, h->stream>>>(d, ra);
+    const LaunchPlan pl = plan_launch(h, n, n);
+    ra.nblk = pl.nblk;
+    (pl.quad ? h->fn_quad : h->fn)<<<dim3(pl.nblk, 1), pl.T, pl.smem, h->stream>>>(d, ra);
     CU(cudaGetLastError());
     h->launches += 1;
     CU(cudaStreamSynchronize(h->stream));

@@ -87,7 +87,7 @@ def test_sampling_mpc_driven_like_the_interface(robot, gait, method, param, ga, 
         r = dict(grf=np.asarray(grf), footholds=np.asarray(footholds), predicted_state=np.asarray(pred),
                  best=np.asarray(controller.best_control_parameters), best_cost=best_cost, best_freq=best_freq,
                  costs=np.asarray(costs), sigma=sigma, best_index=int(np.argmin(costs)))
-        compare(r, o, method, tag=f"iteration {it}")
+        compare(r, o, method, tag=f"iteration {it}", eps=d_eps.cpu().numpy(), best_in=o_best)
     assert np.asarray(grf).shape == (12,) and np.asarray(pred).shape == (24,) and np.asarray(costs).shape == (n,)
     # swing legs of the passed-in sequence carry no force in the returned GRFs
     for leg in range(4):
