@@ -21,7 +21,7 @@
 #include "../../include/qpmpc.h"
 #include "philox.cuh"
 #include "srbd.cuh"
-#include "rollout12.cuh"
+#include "rollout.cuh"
 
 namespace qp {
 
@@ -55,29 +55,63 @@ struct FinalizeArgs {
 //   random_sampling centroidal_nmpc_jax.py:647-677 (the two Gaussian thirds share ONE key upstream, hence the
 //   same normals scaled by sigma[0] and sigma[1]; the uniform block is U(-sigma[2], sigma[2]));
 //   mppi :806-812; cem_mppi :951-958 (normals * sigma vector).  Row 0 is always zero.
-__device__ __forceinline__ float4 noise_group(const DevCfg &c, const NoiseKey &nk, const float *sigma_vec, int i,
-                                              int g, uint32_t robot) {
-    if (i == 0) return make_float4(0.f, 0.f, 0.f, 0.f);
-    if (c.method == QPMPC_METHOD_RANDOM) {
+// Everything that depends only on the row i is resolved once per rollout (RowNoise), so the per-group work is the
+// Philox block and the Box-Muller transform; a scalar sigma is folded into the square root's argument.
+struct RowNoise {
+    int mode;         // 0: N(0, sigma^2) with scalar sigma; 1: U[-a, a); 2: N(0,1) * sigma_vec[p]; 3: zero row
+    uint32_t stream, sample;
+    float k;          // mode 0: sigma^2 * NEG_2LN2; mode 1: a; mode 2: NEG_2LN2
+};
+
+__device__ __forceinline__ RowNoise row_noise(const DevCfg &c, int i) {
+    RowNoise rn;
+    rn.stream = STREAM_NORMAL;
+    rn.sample = (uint32_t)(i - 1);
+    if (i == 0) {
+        rn.mode = 3;
+        rn.k = 0.f;
+    } else if (c.method == QPMPC_METHOD_RANDOM) {
         const int third = c.N / 3;
         if (i < 1 + 2 * third) {
             const bool first = i < 1 + third;
-            const float4 z = normal4(draw(nk, STREAM_NORMAL, g, first ? i - 1 : i - 1 - third, robot));
             const float s = first ? c.sig_rs[0] : c.sig_rs[1];
-            return make_float4(__fmul_rn(s, z.x), __fmul_rn(s, z.y), __fmul_rn(s, z.z), __fmul_rn(s, z.w));
+            rn.mode = 0;
+            rn.sample = (uint32_t)(first ? i - 1 : i - 1 - third);
+            rn.k = __fmul_rn(__fmul_rn(s, s), NEG_2LN2);
+        } else {
+            rn.mode = 1;
+            rn.stream = STREAM_UNIFORM;
+            rn.sample = (uint32_t)(i - 1 - 2 * third);
+            rn.k = c.sig_rs[2];
         }
-        const uint4 u = draw(nk, STREAM_UNIFORM, g, i - 1 - 2 * third, robot);
-        const float a = c.sig_rs[2], w = __fmul_rn(2.0f, a);
-        return make_float4(__fmaf_rn(u01_half_open(u.x), w, -a), __fmaf_rn(u01_half_open(u.y), w, -a),
-                           __fmaf_rn(u01_half_open(u.z), w, -a), __fmaf_rn(u01_half_open(u.w), w, -a));
+    } else if (c.method == QPMPC_METHOD_MPPI) {
+        rn.mode = 0;
+        rn.k = __fmul_rn(__fmul_rn(c.sig_mppi, c.sig_mppi), NEG_2LN2);
+    } else {
+        rn.mode = 2;
+        rn.k = NEG_2LN2;
     }
-    const float4 z = normal4(draw(nk, STREAM_NORMAL, g, i - 1, robot));
-    if (c.method == QPMPC_METHOD_MPPI) {
-        const float s = c.sig_mppi;
-        return make_float4(__fmul_rn(s, z.x), __fmul_rn(s, z.y), __fmul_rn(s, z.z), __fmul_rn(s, z.w));
+    return rn;
+}
+
+__device__ __forceinline__ float4 noise_group_row(const RowNoise &rn, const NoiseKey &nk, const float *sigma_vec, int g,
+                                                  uint32_t robot) {
+    if (rn.mode == 3) return make_float4(0.f, 0.f, 0.f, 0.f);
+    const uint4 x = draw(nk, rn.stream, g, rn.sample, robot);
+    if (rn.mode == 1) {
+        const float a = rn.k, w = __fmul_rn(2.0f, a);
+        return make_float4(__fmaf_rn(u01_half_open(x.x), w, -a), __fmaf_rn(u01_half_open(x.y), w, -a),
+                           __fmaf_rn(u01_half_open(x.z), w, -a), __fmaf_rn(u01_half_open(x.w), w, -a));
     }
+    const float4 z = normal4_scaled(x, rn.k);
+    if (rn.mode == 0) return z;
     return make_float4(__fmul_rn(z.x, sigma_vec[4 * g]), __fmul_rn(z.y, sigma_vec[4 * g + 1]),
                        __fmul_rn(z.z, sigma_vec[4 * g + 2]), __fmul_rn(z.w, sigma_vec[4 * g + 3]));
+}
+
+__device__ __forceinline__ float4 noise_group(const DevCfg &c, const NoiseKey &nk, const float *sigma_vec, int i,
+                                              int g, uint32_t robot) {
+    return noise_group_row(row_noise(c, i), nk, sigma_vec, g, robot);
 }
 
 // step_frequencies_vec[i]: ..._gait_adaptive.py:687-692 (random_sampling), :834-838 (mppi), :994-999 (cem)
@@ -134,40 +168,74 @@ __device__ __forceinline__ float block_sum(float v, float *s_red) {
     return s;
 }
 
-// ---------------------------------------------------------------- rollout kernel ---------------------------
+// ---------------------------------------------------------------- rollout kernel (throughput regime) -------
 // Shared memory layout (floats):
-//   w[T] | par[P][T+1] | best[P] | sigma[P] | state[24] | ref[12] | timing[4] | st[8H] | ref_fz[H] | q[H] | index[H] (int)
-//   | mgk[8] | red[64]
+//   w[T] | live[T] (int) | par[P][T+1] | best[P] | sigma[P] (cem only) | state[24] | ref[12] | timing[4] | st[8H] |
+//   ref_fz[H] | basis[4H] | index[H] (int) | mgk[8] | red[64]
 // par[p][t] = best[p] + eps[t][p] is the parameter vector of thread t's rollout, one COLUMN per thread: the rollout's
 // own reads are conflict-free, and with the row stride T+1 so are the row-wise reads of the softmin-weighted sum.
-// (sigma only exists for cem_mppi: at P = 144, T = 128 leaving it out is what lets three blocks share an SM)
+// (sigma only exists for cem_mppi: at P = 144, T = 128 leaving it out is what lets three blocks share an SM.)
 __host__ __device__ inline int rollout_smem_floats(int P, int H, int T, bool cem) {
-    return T + P * (T + 1) + (cem ? 2 : 1) * P + 24 + 12 + 4 + 8 * H + 3 * H + 8 + 64;
+    return 2 * T + P * (T + 1) + (cem ? 2 : 1) * P + 24 + 12 + 4 + 8 * H + H + 4 * H + H + 8 + 64;
 }
 
-template <int PARAM, bool GA, int HC>
-__global__ void __launch_bounds__(128, 3) k_rollout(const __grid_constant__ DevCfg c, const RolloutArgs a) {
+// V[p] = sum_t w_t par[p][t] over the block, written to part[PART_HDR + p].  At temperature 1 with costs of 1e3..1e5
+// almost every weight underflows to exactly 0 (the reference multiplies those by eps and adds 0): the live (t, w)
+// pairs are compacted in ascending t (deterministic summation order) and only they are visited.
+template <int STRIDE>
+__device__ __forceinline__ void weighted_rows(const float *s_par, float *s_w, int *s_live, float *s_red, float w, int P,
+                                              float *part) {
+    const int t = threadIdx.x, T = blockDim.x, lane = t & 31, wid = t >> 5, nw = T >> 5;
+    const bool live = w > 0.f;
+    const unsigned m = __ballot_sync(0xffffffffu, live);
+    __syncthreads();  // s_red free again
+    if (lane == 0) s_red[wid] = __int_as_float(__popc(m));
+    __syncthreads();
+    int base = 0, total = 0;
+    for (int k = 0; k < nw; ++k) {
+        const int cnt = __float_as_int(s_red[k]);
+        base += k < wid ? cnt : 0;
+        total += cnt;
+    }
+    if (live) {
+        const int k = base + __popc(m & ((1u << lane) - 1u));
+        s_live[k] = t;
+        s_w[k] = w;
+    }
+    __syncthreads();
+    for (int p = t; p < P; p += T) {
+        const float *row = s_par + p * STRIDE;
+        float acc = 0.f;
+        for (int k = 0; k < total; ++k) acc = fmaf(s_w[k], row[s_live[k]], acc);
+        part[PART_HDR + p] = acc;
+    }
+}
+
+template <int PARAM, bool GA, int T>
+__global__ void __launch_bounds__(T, T == 128 ? 3 : 1) k_rollout(const __grid_constant__ DevCfg c, const RolloutArgs a) {
     extern __shared__ __align__(16) float smem[];
-    const int P = c.P, H = c.H, T = blockDim.x, t = threadIdx.x, stride = T + 1;
+    constexpr int STRIDE = T + 1;
+    const int P = c.P, H = c.H, t = threadIdx.x;
     float *s_w = smem;
-    float *s_par = s_w + T;
-    float *s_best = s_par + P * stride;
+    int *s_live = reinterpret_cast<int *>(s_w + T);
+    float *s_par = s_w + 2 * T;
+    float *s_best = s_par + P * STRIDE;
     float *s_sigma = s_best + P;
     float *s_state = s_sigma + (c.method == QPMPC_METHOD_CEM ? P : 0);
     float *s_ref = s_state + 24;
     float *s_timing = s_ref + 12;
     float *s_st = s_timing + 4;
     float *s_reffz = s_st + 8 * H;
-    float *s_q = s_reffz + H;
-    int *s_index = reinterpret_cast<int *>(s_q + H);
-    float *s_mgk = s_q + 2 * H;
+    float *s_basis = s_reffz + H;
+    int *s_index = reinterpret_cast<int *>(s_basis + 4 * H);
+    float *s_mgk = s_basis + 5 * H;
     float *s_red = s_mgk + 8;
 
     const int r = blockIdx.y;
     const int i = blockIdx.x * T + t;
     const bool valid = i < a.n;
 
-    // ---- stage the per-robot problem
+    // ---- stage the per-robot problem and its step tables
     for (int p = t; p < P; p += T) {
         s_best[p] = a.costs_only ? 0.f : a.best[(size_t)r * P + p];
         if (c.method == QPMPC_METHOD_CEM) s_sigma[p] = a.sigma ? a.sigma[(size_t)r * P + p] : 0.f;
@@ -179,16 +247,13 @@ __global__ void __launch_bounds__(128, 3) k_rollout(const __grid_constant__ DevC
         for (int n = t; n < H; n += T) {
             const float s0 = cs[n], s1 = cs[H + n], s2 = cs[2 * H + n], s3 = cs[3 * H + n];
             s_reffz[n] = c.mg / (((s0 + s1) + s2) + s3);
-            if (HC == H12) {  // [n][8] = {st[4], st[4] / 3}
-                s_st[8 * n + 0] = s0; s_st[8 * n + 1] = s1; s_st[8 * n + 2] = s2; s_st[8 * n + 3] = s3;
-                s_st[8 * n + 4] = s0 * (1.0f / 3.0f); s_st[8 * n + 5] = s1 * (1.0f / 3.0f);
-                s_st[8 * n + 6] = s2 * (1.0f / 3.0f); s_st[8 * n + 7] = s3 * (1.0f / 3.0f);
-            } else {          // [leg][H] as the generic path reads it
-                s_st[n] = s0; s_st[H + n] = s1; s_st[2 * H + n] = s2; s_st[3 * H + n] = s3;
-                const int idx = chunk_index(c, (float)n);
-                s_index[n] = idx;
-                s_q[n] = chunk_tau(c, (float)n, (float)H, idx);
-            }
+            s_st[8 * n + 0] = s0; s_st[8 * n + 1] = s1; s_st[8 * n + 2] = s2; s_st[8 * n + 3] = s3;
+            s_st[8 * n + 4] = s0 * (1.0f / 3.0f); s_st[8 * n + 5] = s1 * (1.0f / 3.0f);
+            s_st[8 * n + 6] = s2 * (1.0f / 3.0f); s_st[8 * n + 7] = s3 * (1.0f / 3.0f);
+            const int idx = chunk_index(c, (float)n);
+            s_index[n] = idx;
+            const float4 B = chunk_basis<PARAM>(chunk_tau(c, (float)n, (float)H, idx));
+            *reinterpret_cast<float4 *>(s_basis + 4 * n) = B;
         }
     } else {
         if (t < 5) s_mgk[t] = c.mg / (float)t;
@@ -201,50 +266,40 @@ __global__ void __launch_bounds__(128, 3) k_rollout(const __grid_constant__ DevC
     if (a.eps) {
         const float *src = a.eps + ((size_t)r * a.n + (size_t)blockIdx.x * T) * P;
         const int rows = min(T, a.n - blockIdx.x * T);
-        for (int e = t; e < rows * P; e += T) {
+        for (int e = t; e < T * P; e += T) {
             const int row = e / P, p = e - row * P;
-            s_par[p * stride + row] = s_best[p] + src[e];
+            s_par[p * STRIDE + row] = row < rows ? s_best[p] + src[e] : 0.f;
         }
-        if (!valid)
-            for (int p = 0; p < P; ++p) s_par[p * stride + t] = 0.f;
         __syncthreads();
-    } else if (valid) {
+    } else {
+        const RowNoise rn = row_noise(c, valid ? i : 0);
+        float *dst = s_par + t;
 #pragma unroll 2
         for (int g = 0; g < P / 4; ++g) {
-            const float4 e = noise_group(c, a.key, s_sigma, i, g, robot);
-            const float4 b = *reinterpret_cast<const float4 *>(s_best + 4 * g);
-            float *dst = s_par + (4 * g) * stride + t;
+            float4 e = make_float4(0.f, 0.f, 0.f, 0.f), b = e;  // tail block: zero columns keep everything finite
+            if (valid) {
+                e = noise_group_row(rn, a.key, s_sigma, g, robot);
+                b = *reinterpret_cast<const float4 *>(s_best + 4 * g);
+            }
             dst[0] = b.x + e.x;
-            dst[stride] = b.y + e.y;
-            dst[2 * stride] = b.z + e.z;
-            dst[3 * stride] = b.w + e.w;
+            dst[STRIDE] = b.y + e.y;
+            dst[2 * STRIDE] = b.z + e.z;
+            dst[3 * STRIDE] = b.w + e.w;
+            dst += 4 * STRIDE;
         }
-    } else {
-        for (int p = 0; p < P; ++p) s_par[p * stride + t] = 0.f;  // tail block: keeps the weighted sum finite
     }
 
     // ---- rollout
     float cost = INFINITY;
     if (valid) {
         const float *col = s_par + t;
-        float freq = 0.f;
-        if (GA)
-            freq = a.freqs ? a.freqs[(size_t)r * a.n + i] : freq_sample(c, a.key, i, robot, a.nominal[r], a.oswing[r]);
-        if (HC == H12) {
-            cost = GA ? rollout12_ga<PARAM>(c, s_state, s_ref, s_mgk, s_timing, freq, col, stride)
-                      : rollout12_fixed<PARAM>(c, s_state, s_ref, s_st, s_reffz, col, stride);
+        if (GA) {
+            const float freq = a.freqs ? a.freqs[(size_t)r * a.n + i]
+                                       : freq_sample(c, a.key, i, robot, a.nominal[r], a.oswing[r]);
+            cost = rollout_gait_adaptive<PARAM, STRIDE>(c, s_state, s_ref, s_mgk, s_timing, freq, col);
         } else {
-            const int np = c.np;
-            auto par = [&](int leg, int j) { return col[(leg * np + j) * stride]; };
-            if (GA) {
-                float timing[4];
-#pragma unroll
-                for (int l = 0; l < 4; ++l) timing[l] = s_timing[l];
-                cost = rollout_gait_adaptive<PARAM>(c, s_state, s_ref, s_mgk, timing, freq, par);
-            } else {
-                const StepTables tb = {s_st, s_reffz, s_index, s_q};
-                cost = rollout_fixed<PARAM>(c, s_state, s_ref, tb, par);
-            }
+            const FixedTables tb = {s_st, s_reffz, s_basis, s_index};
+            cost = rollout_fixed<PARAM, STRIDE>(c, s_state, s_ref, tb, col);
         }
         if (!a.costs_only) {  // centroidal_nmpc_jax.py:686-687
             cost = isnan(cost) ? 1000000.0f : cost;
@@ -270,28 +325,15 @@ __global__ void __launch_bounds__(128, 3) k_rollout(const __grid_constant__ DevC
     }
     // softmin numerators relative to the block minimum (merged exactly in k_finalize), :828-836
     const float w = valid ? __expf(-(cost - bc)) : 0.f;
-    s_w[t] = w;
-    const float sw = block_sum(w, s_red);  // contains the __syncthreads that publishes s_w
+    const float sw = block_sum(w, s_red);
     if (t == 0) {
         part[0] = bc;
         part[1] = sw;
         part[2] = bc;
         part[3] = __int_as_float(bi);
     }
-    // V[p] = sum_t w_t par[p][t]; k_finalize turns sum_b scale_b V_b / sum_b scale_b sw_b into the updated parameters
-    for (int p = t; p < P; p += T) {
-        const float *row = s_par + p * stride;
-        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-#pragma unroll 4
-        for (int k = 0; k < T; k += 4) {
-            const float4 w4 = *reinterpret_cast<const float4 *>(s_w + k);
-            a0 = fmaf(w4.x, row[k], a0);
-            a1 = fmaf(w4.y, row[k + 1], a1);
-            a2 = fmaf(w4.z, row[k + 2], a2);
-            a3 = fmaf(w4.w, row[k + 3], a3);
-        }
-        part[PART_HDR + p] = (a0 + a1) + (a2 + a3);
-    }
+    // k_finalize turns sum_b scale_b V_b / sum_b scale_b sw_b into the updated parameters
+    weighted_rows<STRIDE>(s_par, s_w, s_live, s_red, w, P, part);
 }
 
 // ---------------------------------------------------------------- quad rollout kernel (latency regime) ------
@@ -373,11 +415,12 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
         }
         __syncthreads();
     } else {
+        const RowNoise rn = row_noise(c, valid ? i : 0);
         for (int g = leg; g < P / 4; g += 4) {
             float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
             float4 b = e;
             if (valid) {
-                e = noise_group(c, a.key, s_sigma, i, g, robot);
+                e = noise_group_row(rn, a.key, s_sigma, g, robot);
                 b = *reinterpret_cast<const float4 *>(s_best + 4 * g);
             }
             float *dst = s_par + (4 * g) * stride + rb;
@@ -399,7 +442,6 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
     const float footx = s_state[12 + 3 * leg], footy = s_state[13 + 3 * leg], footz = s_state[14 + 3 * leg];
     const float qa = c.q[3 * leg], qb = c.q[3 * leg + 1], qc = c.q[3 * leg + 2];
     const float *col = s_par + rb;
-    const int np = c.np;
     float freq = 0.f, hl = (float)H;
     uint32_t bits = 0;
     if (GA) {
@@ -415,36 +457,59 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
         }
         hl = (float)(__popc(bits) + 1);  // horizon_leg = sum(contact) + 1, ..._gait_adaptive.py:345-348
     }
+    // the three reference values of this lane's share of the stage cost (states 3 leg .. 3 leg + 2)
+    const float ra = leg == 0 ? ref[0] : leg == 1 ? ref[3] : leg == 2 ? ref[6] : ref[9];
+    const float rb_ = leg == 0 ? ref[1] : leg == 1 ? ref[4] : leg == 2 ? ref[7] : ref[10];
+    const float rc = leg == 0 ? ref[2] : leg == 1 ? ref[5] : leg == 2 ? ref[8] : ref[11];
+    const float rq = __fdividef((float)c.S, hl);  // position in chunk = step / (horizon_leg / S) - index
+    const int hs = H * stride;
     float cost = 0.f;
-    int ncnt = -1;
+    float kc[3][4];
+    int ncnt = -1, cur = -1;
 #pragma unroll 1
     for (int n = 0; n < H; ++n) {
-        float st, ref_fz, q;
-        int istep, index;
+        float st, ref_fz;
+        int istep;
+        float4 B = make_float4(0.f, 0.f, 0.f, 0.f);
         if (GA) {
             const int on = (bits >> n) & 1;
             const unsigned bal = __ballot_sync(0xffffffffu, on);
             st = (float)on;
             ref_fz = s_mgk[__popc((bal >> qbase) & 0xFu)];
             ncnt += on;  // the leg's own step counter advances only in stance, :353-356
-            istep = ncnt;
-            index = 0;
-            q = 0.f;
+            istep = max(ncnt, 0);  // a swing leg's value is multiplied by 0: any finite stand-in does
             if (PARAM != QPMPC_PARAM_ZERO_ORDER) {
-                index = chunk_index(c, (float)ncnt);
-                q = chunk_tau(c, (float)ncnt, hl, index);
+                const float stepf = (float)istep;
+                int idx = 0;
+                for (int j = 1; j <= c.S; ++j) idx += (stepf >= c.bounds[j]) ? 1 : 0;
+                if (idx != cur) {
+                    load_chunk<PARAM, stride>(c, col, leg, idx, kc);
+                    cur = idx;
+                }
+                B = chunk_basis<PARAM>(stepf * rq - (float)idx);
             }
         } else {
             st = s_stance[leg * H + n];
             ref_fz = s_reffz[n];
             istep = n;
-            index = s_index[n];
-            q = s_q[n];
+            if (PARAM != QPMPC_PARAM_ZERO_ORDER) {
+                const int idx = s_index[n];
+                if (idx != cur) {
+                    load_chunk<PARAM, stride>(c, col, leg, idx, kc);
+                    cur = idx;
+                }
+                B = chunk_basis<PARAM>(s_q[n]);
+            }
         }
-        CubicBasis B = {1.f, 0.f, 0.f, 0.f};
-        if (PARAM == QPMPC_PARAM_CUBIC) B = cubic_basis(q);
         float f[3];
-        spline_eval<PARAM>(c, [&](int j) { return col[(leg * np + j) * stride]; }, istep, index, q, B, f);
+        if (PARAM == QPMPC_PARAM_ZERO_ORDER) {
+            const float *p = col + leg * 3 * hs + istep * stride;
+            f[0] = p[0];
+            f[1] = p[hs];
+            f[2] = p[2 * hs];
+        } else {
+            eval_chunk<PARAM>(kc, B, f);
+        }
         shape_leg(c, f, st, st * (1.0f / 3.0f), ref_fz);
         // this leg's share of the net force and of the torque about the centre of mass, summed over the quad
         const float fzs = f[2] * st;
@@ -461,7 +526,7 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
         const float sp = __shfl_sync(0xffffffffu, sa, qbase + 1), cp = __shfl_sync(0xffffffffu, ca, qbase + 1);
         const float sy = __shfl_sync(0xffffffffu, sa, qbase + 2), cy = __shfl_sync(0xffffffffu, ca, qbase + 2);
         const float wx = x[9], wy = x[10], wz = x[11];
-        const float yaw_rate = (sr * wy + cr * wz) / cp;
+        const float yaw_rate = __fdividef(sr * wy + cr * wz, cp);
         const float pitch_rate = cr * wy - sr * wz;
         const float roll_rate = wx + sp * yaw_rate;
         const float bx = cp * cy * tx + cp * sy * ty - sp * tz;
@@ -487,12 +552,9 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
         x[10] += (c.Iinv[3] * gx + c.Iinv[4] * gy + c.Iinv[5] * gz) * dt;
         x[11] += (c.Iinv[6] * gx + c.Iinv[7] * gy + c.Iinv[8] * gz) * dt;
         // stage cost: lane `leg` owns the terms of states 3 leg .. 3 leg + 2
-        const float ea = (leg == 0 ? x[0] : leg == 1 ? x[3] : leg == 2 ? x[6] : x[9]) -
-                         (leg == 0 ? ref[0] : leg == 1 ? ref[3] : leg == 2 ? ref[6] : ref[9]);
-        const float eb = (leg == 0 ? x[1] : leg == 1 ? x[4] : leg == 2 ? x[7] : x[10]) -
-                         (leg == 0 ? ref[1] : leg == 1 ? ref[4] : leg == 2 ? ref[7] : ref[10]);
-        const float ec = (leg == 0 ? x[2] : leg == 1 ? x[5] : leg == 2 ? x[8] : x[11]) -
-                         (leg == 0 ? ref[2] : leg == 1 ? ref[5] : leg == 2 ? ref[8] : ref[11]);
+        const float ea = (leg == 0 ? x[0] : leg == 1 ? x[3] : leg == 2 ? x[6] : x[9]) - ra;
+        const float eb = (leg == 0 ? x[1] : leg == 1 ? x[4] : leg == 2 ? x[7] : x[10]) - rb_;
+        const float ec = (leg == 0 ? x[2] : leg == 1 ? x[5] : leg == 2 ? x[8] : x[11]) - rc;
         cost += (ea * qa) * ea;
         cost += (eb * qb) * eb;
         cost += (ec * qc) * ec;
@@ -637,11 +699,11 @@ __global__ void __launch_bounds__(FIN_THREADS_MAX) k_finalize(const __grid_const
             const int p = p0 + lane;
             float acc = 0.f;
             if (p < P) {
-#pragma unroll 4
+                // most blocks' minima sit far above the global one: their scale underflows to exactly 0 and their row
+                // is not even fetched (upstream those samples contribute 0 * eps = 0)
                 for (int b = wid; b < a.nblk; b += nw) {
                     const float sc = s_sc[b];
-                    const float v = part[(size_t)b * stride + PART_HDR + p];
-                    acc += (sc == 0.f) ? 0.f : sc * v;
+                    if (sc != 0.f) acc = fmaf(sc, part[(size_t)b * stride + PART_HDR + p], acc);
                 }
                 s_acc[wid * P + p] = acc;
             }
@@ -763,7 +825,7 @@ struct qpmpc_handle {
     int device;
     cudaStream_t stream;
     int num_sms;
-    rollout_fn fn, fn_quad;
+    rollout_fn fn128, fn32, fn_quad;
     size_t max_smem;
     // single-robot staging: one pinned input block, one pinned output block
     float *h_in, *d_in;
@@ -799,21 +861,16 @@ static void inverse3(const float A[9], float out[9]) {
     out[8] = (a22 * a11 - a21 * a12) / det;
 }
 
-// fast = the fully unrolled horizon-12 kernels (rollout12.cuh); otherwise the generic runtime-horizon kernels
-static rollout_fn pick_rollout(int param, int ga, bool fast) {
-    switch (param * 2 + (ga ? 1 : 0) + (fast ? 6 : 0)) {
-        case 0: return k_rollout<QPMPC_PARAM_ZERO_ORDER, false, 0>;
-        case 1: return k_rollout<QPMPC_PARAM_ZERO_ORDER, true, 0>;
-        case 2: return k_rollout<QPMPC_PARAM_LINEAR, false, 0>;
-        case 3: return k_rollout<QPMPC_PARAM_LINEAR, true, 0>;
-        case 4: return k_rollout<QPMPC_PARAM_CUBIC, false, 0>;
-        case 5: return k_rollout<QPMPC_PARAM_CUBIC, true, 0>;
-        case 6: return k_rollout<QPMPC_PARAM_ZERO_ORDER, false, H12>;
-        case 7: return k_rollout<QPMPC_PARAM_ZERO_ORDER, true, H12>;
-        case 8: return k_rollout<QPMPC_PARAM_LINEAR, false, H12>;
-        case 9: return k_rollout<QPMPC_PARAM_LINEAR, true, H12>;
-        case 10: return k_rollout<QPMPC_PARAM_CUBIC, false, H12>;
-        default: return k_rollout<QPMPC_PARAM_CUBIC, true, H12>;
+// thread-per-rollout kernels: 128-thread blocks, or 32-thread blocks when P is too large for 128 columns of shared memory
+template <int T>
+static rollout_fn pick_rollout(int param, int ga) {
+    switch (param * 2 + (ga ? 1 : 0)) {
+        case 0: return k_rollout<QPMPC_PARAM_ZERO_ORDER, false, T>;
+        case 1: return k_rollout<QPMPC_PARAM_ZERO_ORDER, true, T>;
+        case 2: return k_rollout<QPMPC_PARAM_LINEAR, false, T>;
+        case 3: return k_rollout<QPMPC_PARAM_LINEAR, true, T>;
+        case 4: return k_rollout<QPMPC_PARAM_CUBIC, false, T>;
+        default: return k_rollout<QPMPC_PARAM_CUBIC, true, T>;
     }
 }
 static rollout_fn pick_quad(int param, int ga) {
@@ -826,13 +883,10 @@ static rollout_fn pick_quad(int param, int ga) {
         default: return k_rollout_quad<QPMPC_PARAM_CUBIC, true>;
     }
 }
-// QPMPC_KERNEL=quad|thread|generic pins the kernel choice (tests exercise every kernel at every size with it)
+// QPMPC_KERNEL=quad|thread pins the kernel choice (the tests exercise both kernels at every size with it)
 static const char *kernel_override() {
     const char *e = getenv("QPMPC_KERNEL");
     return e ? e : "";
-}
-static bool is_fast(const DevCfg &d) {
-    return d.H == H12 && (d.param == QPMPC_PARAM_ZERO_ORDER || d.S == 2) && strcmp(kernel_override(), "generic") != 0;
 }
 
 struct LaunchPlan {
@@ -848,15 +902,14 @@ static LaunchPlan plan_launch(const qpmpc_handle *h, int n, long long total_roll
     LaunchPlan pl;
     pl.quad = total_rollouts < subparts * 32 * 2;
     if (!strcmp(kernel_override(), "quad")) pl.quad = true;
-    if (!strcmp(kernel_override(), "thread") || !strcmp(kernel_override(), "generic")) pl.quad = false;
+    if (!strcmp(kernel_override(), "thread")) pl.quad = false;
     if (pl.quad && (size_t)quad_smem_floats(d.P, d.H) * 4 > h->max_smem) pl.quad = false;
     if (pl.quad) {
         pl.T = 4 * QB;
         pl.nblk = (n + QB - 1) / QB;
         pl.smem = (size_t)quad_smem_floats(d.P, d.H) * 4;
     } else {
-        int T = total_rollouts < subparts * 32 * 8 ? 64 : 128;
-        while (T > 32 && (size_t)rollout_smem_floats(d.P, d.H, T, d.method == QPMPC_METHOD_CEM) * 4 > h->max_smem) T >>= 1;
+        const int T = (size_t)rollout_smem_floats(d.P, d.H, 128, d.method == QPMPC_METHOD_CEM) * 4 <= h->max_smem ? 128 : 32;
         pl.T = T;
         pl.nblk = (n + T - 1) / T;
         pl.smem = (size_t)rollout_smem_floats(d.P, d.H, T, d.method == QPMPC_METHOD_CEM) * 4;
@@ -922,13 +975,17 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
 
     h->max_smem = prop.sharedMemPerBlockOptin;
     h->num_sms = prop.multiProcessorCount;
-    rollout_fn fn = pick_rollout(d.param, d.ga, is_fast(d));
-    h->fn = fn;
-    cudaError_t e = cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_smem);
-    if (e != cudaSuccess) { delete h; return fail(QPMPC_E_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e)); }
+    if ((size_t)rollout_smem_floats(P, d.H, 32, d.method == QPMPC_METHOD_CEM) * 4 > h->max_smem) {
+        delete h;
+        return fail(QPMPC_E_ARG, "control parameter vector too large for shared memory");
+    }
+    h->fn128 = pick_rollout<128>(d.param, d.ga);
+    h->fn32 = pick_rollout<32>(d.param, d.ga);
     h->fn_quad = pick_quad(d.param, d.ga);
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute((const void *)h->fn_quad, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_smem);
+    cudaError_t e = cudaSuccess;
+    for (rollout_fn f : {h->fn128, h->fn32, h->fn_quad})
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute((const void *)f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_smem);
     if (e != cudaSuccess) { delete h; return fail(QPMPC_E_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e)); }
 
     const int H = d.H;
@@ -988,7 +1045,7 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
     ra.costs = b.d_costs ? b.d_costs : h->d_costs; ra.partials = h->d_partials;
     ra.key = NoiseKey{seed, offset}; ra.n = N; ra.costs_only = 0; ra.nblk = nblk;
     if (h->profiling) CU(cudaEventRecord(h->ev[0], h->stream));
-    (pl.quad ? h->fn_quad : h->fn)<<<dim3(nblk, R), pl.T, pl.smem, h->stream>>>(d, ra);
+    (pl.quad ? h->fn_quad : (pl.T == 128 ? h->fn128 : h->fn32))<<<dim3(nblk, R), pl.T, pl.smem, h->stream>>>(d, ra);
     CU(cudaGetLastError());
     if (h->profiling) CU(cudaEventRecord(h->ev[1], h->stream));
     FinalizeArgs fa;
@@ -1093,7 +1150,7 @@ extern "C" int qpmpc_rollout_costs(qpmpc_handle *h, const float *state, const fl
     ra.eps = d_params; ra.freqs = d_freqs; ra.costs = d_costs; ra.n = n; ra.costs_only = 1;
     const LaunchPlan pl = plan_launch(h, n, n);
     ra.nblk = pl.nblk;
-    (pl.quad ? h->fn_quad : h->fn)<<<dim3(pl.nblk, 1), pl.T, pl.smem, h->stream>>>(d, ra);
+    (pl.quad ? h->fn_quad : (pl.T == 128 ? h->fn128 : h->fn32))<<<dim3(pl.nblk, 1), pl.T, pl.smem, h->stream>>>(d, ra);
     CU(cudaGetLastError());
     h->launches += 1;
     CU(cudaStreamSynchronize(h->stream));

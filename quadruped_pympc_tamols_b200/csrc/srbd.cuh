@@ -6,8 +6,9 @@
 //   controllers/sampling/centroidal_nmpc_jax.py:316-496            compute_rollout (given contact sequence)
 //   controllers/sampling/centroidal_nmpc_jax_gait_adaptive.py:326-501  compute_rollout (per-sample gait)
 //   helpers/periodic_gait_generator_jax.py:68-89,136-151           trot clock -> contact sequence
-// One thread owns one rollout: the 12 body states, lever arms and forces live in registers; everything that is
-// the same for all samples of a robot (feet, reference, Q, per-step tables) is read from shared memory.
+// The building blocks in the reference's operation order (generic spline evaluation, force shaping, one SRBD step,
+// stage cost); k_finalize uses them for the first-step GRF and the one-step prediction, rollout.cuh builds the hot
+// loops on the same formulas.
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -177,97 +178,6 @@ __device__ __forceinline__ float stage_cost(const DevCfg &c, const float x[12], 
         acc += (e * c.q[k]) * e;
     }
     return acc;
-}
-
-// Shared per-robot tables for the fixed-gait rollout (identical for every sample).
-struct StepTables {
-    const float *stance;  // [4*H] contact_sequence as given
-    const float *ref_fz;  // [H]   mg / sum_legs contact[:, n]
-    const int *index;     // [H]   spline chunk of step n
-    const float *q;       // [H]   position inside the chunk
-};
-
-// Fixed contact sequence: centroidal_nmpc_jax.py:316-496.
-template <int PARAM, class ParLeg>
-__device__ __forceinline__ float rollout_fixed(const DevCfg &c, const float *s_state, const float *s_ref,
-                                               const StepTables &tb, ParLeg par) {
-    float x[12];
-#pragma unroll
-    for (int k = 0; k < 12; ++k) x[k] = s_state[k];
-    float cost = 0.f;
-#pragma unroll 1
-    for (int n = 0; n < c.H; ++n) {
-        float st[4], f[4][3];
-        const int index = tb.index[n];
-        const float q = tb.q[n];
-        const CubicBasis B = cubic_basis(q);
-#pragma unroll
-        for (int l = 0; l < 4; ++l) {
-            st[l] = tb.stance[l * c.H + n];
-            spline_eval<PARAM>(c, [&](int j) { return par(l, j); }, n, index, q, B, f[l]);
-        }
-        shape_forces(c, f, st, tb.ref_fz[n]);
-        srbd_step(c, x, s_state + 12, f, st, c.dts[n]);
-        cost += stage_cost(c, x, s_ref);
-    }
-    return cost;
-}
-
-// Per-sample gait: centroidal_nmpc_jax_gait_adaptive.py:326-501 with the trot clock of
-// periodic_gait_generator_jax.py:68-89 (restart at t >= 1, advance by mpc_dt * f, stance while t < duty).
-// s_mgk[k] = mg / k for k = 0..4 (k = 0 -> +inf as upstream).
-template <int PARAM, class ParLeg>
-__device__ __forceinline__ float rollout_gait_adaptive(const DevCfg &c, const float *s_state, const float *s_ref,
-                                                       const float *s_mgk, const float timing[4], float freq,
-                                                       ParLeg par) {
-    uint32_t bits[4];
-    float hl[4];
-    const float inc = __fmul_rn(c.mpc_dt, freq);
-#pragma unroll
-    for (int l = 0; l < 4; ++l) {
-        float t = timing[l];
-        uint32_t b = 0;
-        for (int n = 0; n < c.H; ++n) {
-            t = (t >= 1.0f) ? 0.0f : t;
-            t = __fadd_rn(t, inc);
-            b |= (t < c.duty ? 1u : 0u) << n;
-        }
-        bits[l] = b;
-        hl[l] = (float)(__popc(b) + 1);  // horizon_leg = sum(contact) + 1, ..._gait_adaptive.py:345-348
-    }
-    float x[12];
-#pragma unroll
-    for (int k = 0; k < 12; ++k) x[k] = s_state[k];
-    float cost = 0.f;
-    int ncnt[4] = {-1, -1, -1, -1};  // ..._gait_adaptive.py:339
-#pragma unroll 1
-    for (int n = 0; n < c.H; ++n) {
-        float st[4], f[4][3];
-        int nst = 0;
-#pragma unroll
-        for (int l = 0; l < 4; ++l) {
-            const int on = (bits[l] >> n) & 1;
-            st[l] = (float)on;
-            nst += on;
-            ncnt[l] += on;  // the per-leg step counter advances only in stance, :353-356
-            int index = 0;
-            float q = 0.f;
-            CubicBasis B = {1.f, 0.f, 0.f, 0.f};
-            if (PARAM != QPMPC_PARAM_ZERO_ORDER) {
-                const float step = (float)ncnt[l];
-                index = chunk_index(c, step);
-                q = chunk_tau(c, step, hl[l], index);
-                if (PARAM == QPMPC_PARAM_CUBIC) B = cubic_basis(q);
-            }
-            spline_eval<PARAM>(c, [&](int j) { return par(l, j); }, ncnt[l], index, q, B, f[l]);
-        }
-        shape_forces(c, f, st, s_mgk[nst]);
-        srbd_step(c, x, s_state + 12, f, st, c.dts[n]);
-        cost += stage_cost(c, x, s_ref);
-    }
-    const float df = freq - 1.3f;
-    cost += df * 100.f * df;  // ..._gait_adaptive.py:500
-    return cost;
 }
 
 }  // namespace qp

@@ -35,11 +35,10 @@ GAITS = {"trot": ([0.5, 1.0, 1.0, 0.5], 1.4, 0.65), "pace": ([0.8, 0.3, 0.8, 0.3
          "bound": ([0.5, 0.5, 0.0, 0.0], 1.8, 0.65)}
 
 
-@pytest.fixture(params=["auto", "quad", "thread", "generic"])
+@pytest.fixture(params=["auto", "quad", "thread"])
 def kernel(request, monkeypatch):
     """Every rollout kernel at every size: QPMPC_KERNEL pins the choice the library otherwise makes from the launch size
-    (quad = 4 lanes per rollout, latency regime; thread = unrolled horizon-12 thread-per-rollout, throughput regime;
-    generic = runtime-horizon thread-per-rollout)."""
+    (quad = 4 lanes per rollout, latency regime; thread = one thread per rollout, throughput regime)."""
     if request.param == "auto":
         monkeypatch.delenv("QPMPC_KERNEL", raising=False)
     else:
