@@ -28,27 +28,23 @@ namespace qp {
 constexpr int PART_HDR = 4;  // per-block partial: [min cost, sum w, argmin cost, argmin index bits] + V[P]
 constexpr int FIN_THREADS_MAX = 512;
 
-struct RolloutArgs {
+// Everything one solve needs on the device; the rollout kernels and the finalize step share it.
+struct SolveArgs {
     const float *state, *reference, *contact, *best, *sigma, *timing, *nominal;
     const int32_t *oswing;
     const float *eps, *freqs;  // reference-supplied noise (or the parameter matrix in costs_only mode)
     float *costs, *partials;
+    qpmpc_result *result;
+    float *best_out, *sigma_out;
+    unsigned int *tickets;  // [robots] arrival counters of the fused finalize (zero between launches)
     NoiseKey key;
     int n;            // rollouts per robot in this launch
     int costs_only;   // 1: jit_vectorized_rollout semantics (eps = parameters, no saturation, no partials)
-    int nblk;         // blocks per robot
+    int nblk;         // rollout blocks per robot
+    int fused;        // 1: the last rollout block of a robot runs finalize_robot itself (one launch per solve)
 };
-
-struct FinalizeArgs {
-    const float *state, *reference, *contact, *best, *sigma, *nominal;
-    const int32_t *oswing;
-    const float *eps, *freqs;
-    const float *costs, *partials;
-    qpmpc_result *result;
-    float *best_out, *sigma_out;
-    NoiseKey key;
-    int nblk;
-};
+typedef SolveArgs RolloutArgs;
+typedef SolveArgs FinalizeArgs;
 
 // ---------------------------------------------------------------- noise ------------------------------------
 // additional_random_parameters[i, 4g..4g+3] (sigma applied) for robot `robot`:
@@ -168,22 +164,264 @@ __device__ __forceinline__ float block_sum(float v, float *s_red) {
     return s;
 }
 
+// ---------------------------------------------------------------- finalize kernel --------------------------
+// Shared: best_out[P] | sel (elite indices) [cem_elite] | red[64] | misc
+template <int PARAM>
+__device__ void grf_and_prediction(const DevCfg &c, const float *s_best, const float *state, const float *contact,
+                                   qpmpc_result *out) {
+    // centroidal_nmpc_jax.py:707-784: spline at (step = 0.0, horizon_leg = 1), passed-in contact_sequence[:, 0]
+    float f[4][3], st[4];
+    const int index = chunk_index(c, 0.0f);
+    const float q = chunk_tau(c, 0.0f, 1.0f, index);
+    const CubicBasis B = cubic_basis(q);
+#pragma unroll
+    for (int l = 0; l < 4; ++l) {
+        st[l] = contact[l * c.H];
+        const float *pl = s_best + l * c.np;
+        spline_eval<PARAM>(c, [&](int j) { return pl[j]; }, 0, index, q, B, f[l]);
+    }
+    const float nst = ((st[0] + st[1]) + st[2]) + st[3];
+    shape_forces(c, f, st, c.mg / nst);
+    float x[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) x[k] = state[k];
+    srbd_step(c, x, state + 12, f, st, c.dts[0]);
+#pragma unroll
+    for (int l = 0; l < 4; ++l)
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            out->grf[3 * l + k] = f[l][k];
+            out->footholds[3 * l + k] = 0.f;
+        }
+#pragma unroll
+    for (int k = 0; k < 12; ++k) {
+        out->predicted_state[k] = x[k];
+        out->predicted_state[12 + k] = state[12 + k];
+    }
+}
+
+// Finalize step of robot r, run by ALL threads of one block (any multiple of 32): either the last rollout block of
+// the robot (fused, scratch = that block's parameter columns, no longer needed) or the stand-alone k_finalize.
+// Partials and costs were written by other blocks: they are read through L2 (ld.global.cg).
+__host__ __device__ inline int finalize_smem_floats(int P, int nblk, int cem_elite, int threads) {
+    const int G = threads / (P / 4) > 1 ? threads / (P / 4) : 1;
+    return G * P + P + 64 + 3 * nblk + 1 + cem_elite + 8;
+}
+
+#ifdef QPMPC_TIMING
+#define QP_TICK(k) do { if (threadIdx.x == 0) { unsigned long long g_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g_)); tick_[k] = g_; } } while (0)
+#else
+#define QP_TICK(k)
+#endif
+__device__ void finalize_robot(const DevCfg &c, const FinalizeArgs &a, const int r, float *smem) {
+    const int P = c.P, N = c.N, t = threadIdx.x;
+#ifdef QPMPC_TIMING
+    unsigned long long tick_[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#endif
+    QP_TICK(0);
+    // scratch: acc[G][P] | best[P] | red[64] | sc[nblk] | sw[nblk] | lb[nblk + 1] | sel[cem_elite]
+    const int G_ = max(1, (int)blockDim.x / (P >> 2));
+    float *s_acc = smem;
+    float *s_best = s_acc + G_ * P;
+    float *s_red = s_best + P;
+    float *s_sc = s_red + 64;
+    float *s_sw = s_sc + a.nblk;
+    int *s_lb = reinterpret_cast<int *>(s_sw + a.nblk);
+    int *s_sel = s_lb + a.nblk + 1;
+    __syncthreads();  // fused call: every thread is done with the columns this scratch overlays
+    const float *part = a.partials + (size_t)r * a.nblk * (PART_HDR + P);
+    const int stride = PART_HDR + P;
+    const uint32_t robot = (uint32_t)r;
+
+    // One pass over the block headers {min_b, sum_t w, min_b, argmin}: kept in shared memory for the rescale.
+    // global minimum / first argmin (nanargmin: lowest index among equal minima)
+    float bc = INFINITY;
+    int bi = 0x7fffffff;
+    for (int b = t; b < a.nblk; b += blockDim.x) {
+        const float4 hd = __ldcg(reinterpret_cast<const float4 *>(part + (size_t)b * stride));
+        s_sc[b] = hd.x;
+        s_sw[b] = hd.y;
+        argmin_combine(bc, bi, hd.z, __float_as_int(hd.w));
+    }
+    block_argmin(bc, bi, s_red);
+    QP_TICK(1);
+
+    if (c.method == QPMPC_METHOD_RANDOM) {  // best = control_parameters_vec[best_index], :692
+        for (int p = t; p < P; p += blockDim.x) {
+            float e;
+            if (a.eps) {
+                e = a.eps[((size_t)r * N + bi) * P + p];
+            } else {
+                const float4 v = noise_group(c, a.key, nullptr, bi, p >> 2, robot);
+                const int k = p & 3;
+                e = k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w));
+            }
+            s_best[p] = __fadd_rn(a.best[(size_t)r * P + p], e);
+        }
+    } else {
+        // best + sum_i w_i eps_i = sum_i w_i par_i / sum_i w_i with w = softmin(costs), :828-836.  Each rollout block
+        // left {min_b, sum_t w, V[P]} relative to its own minimum; rescale by exp(-(min_b - min)) and merge.
+        float dpart = 0.f;
+        for (int b = t; b < a.nblk; b += blockDim.x) {
+            const float sc = __expf(-(s_sc[b] - bc));
+            s_sc[b] = sc;
+            dpart += s_sw[b] * sc;
+        }
+        const float den = block_sum(dpart, s_red);  // its barriers also publish s_sc
+        QP_TICK(2);
+        // Blocks whose minimum sits far above the global one have a scale of exactly 0 (upstream those samples
+        // contribute 0 * eps = 0): warp 0 compacts the live blocks in ascending order (deterministic summation order).
+        if (t < 32) {
+            int nl = 0;
+            for (int b0 = 0; b0 < a.nblk; b0 += 32) {
+                const int b = b0 + t;
+                const bool live = b < a.nblk && s_sc[b] != 0.f;
+                const unsigned m = __ballot_sync(0xffffffffu, live);
+                if (live) s_lb[nl + __popc(m & ((1u << t) - 1u))] = b;
+                nl += __popc(m);
+            }
+            if (t == 0) s_lb[a.nblk] = nl;
+        }
+        __syncthreads();
+        const int nlive = s_lb[a.nblk];
+        // sum_b scale_b V_b[p]: the block splits into G row groups of P/4 threads, each thread streams float4 slices of
+        // every G-th live row through L2 with 16 loads in flight; the G group sums are then added in group order.
+        const int P4 = P >> 2;
+        const int G = max(1, (int)blockDim.x / P4);
+        for (int q = t; q < G * P4; q += blockDim.x) {
+            const int g = q / P4, p4 = q - g * P4;
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 16
+            for (int k = g; k < nlive; k += G) {
+                const int b = s_lb[k];
+                const float sc = s_sc[b];
+                const float4 v = __ldcg(reinterpret_cast<const float4 *>(part + (size_t)b * stride + PART_HDR) + p4);
+                acc.x = fmaf(sc, v.x, acc.x);
+                acc.y = fmaf(sc, v.y, acc.y);
+                acc.z = fmaf(sc, v.z, acc.z);
+                acc.w = fmaf(sc, v.w, acc.w);
+            }
+            *reinterpret_cast<float4 *>(s_acc + g * P + 4 * p4) = acc;
+        }
+        __syncthreads();
+        for (int p = t; p < P; p += blockDim.x) {
+            float num = 0.f;
+            for (int g = 0; g < G; ++g) num += s_acc[g * P + p];
+            s_best[p] = num / den;
+        }
+    }
+    __syncthreads();
+    QP_TICK(3);
+    for (int p = t; p < P; p += blockDim.x) a.best_out[(size_t)r * P + p] = s_best[p];
+
+    qpmpc_result *out = a.result + r;
+    if (t == 0) {
+        out->best_cost = bc;
+        out->best_index = bi;
+        out->reserved = 0;
+        float bf;
+        if (c.ga)
+            bf = a.freqs ? a.freqs[(size_t)r * N + bi] : freq_sample(c, a.key, bi, robot, a.nominal[r], a.oswing[r]);
+        else
+            bf = (c.method == QPMPC_METHOD_CEM) ? 1.65f : 1.4f;  // centroidal_nmpc_jax.py:786,930,1083
+        out->best_freq = bf;
+        const float *state = a.state + r * 24;
+        const float *contact = a.contact + (size_t)r * 4 * c.H;
+        if (c.param == QPMPC_PARAM_ZERO_ORDER)
+            grf_and_prediction<QPMPC_PARAM_ZERO_ORDER>(c, s_best, state, contact, out);
+        else if (c.param == QPMPC_PARAM_LINEAR)
+            grf_and_prediction<QPMPC_PARAM_LINEAR>(c, s_best, state, contact, out);
+        else
+            grf_and_prediction<QPMPC_PARAM_CUBIC>(c, s_best, state, contact, out);
+        QP_TICK(4);
+#ifdef QPMPC_TIMING
+        for (int k = 1; k < 5; ++k) out->footholds[k] = (float)(tick_[k] - tick_[k - 1]);
+#endif
+    }
+
+    if (c.method != QPMPC_METHOD_CEM || a.sigma_out == nullptr) return;
+    // ---- CEM: elites = argsort(costs)[:K] (stable: ties by index), new sigma from their noise rows,
+    // centroidal_nmpc_jax.py:1075-1081 (K=10, sqrt, clip [0.2,5]) / ..._gait_adaptive.py:1115-1121 (K=200, no sqrt, [0.5,3])
+    const int K = min(c.cem_elite, N);
+    const float *costs = a.costs + (size_t)r * N;
+    float lc = -INFINITY;
+    int li = -1;
+    for (int k = 0; k < K; ++k) {
+        float mc = INFINITY;
+        int mi = 0x7fffffff;
+        for (int i = t; i < N; i += blockDim.x) {
+            const float ci = __ldcg(costs + i);
+            if (ci > lc || (ci == lc && i > li)) argmin_combine(mc, mi, ci, i);
+        }
+        block_argmin(mc, mi, s_red);
+        if (t == 0) s_sel[k] = mi;
+        lc = mc;
+        li = mi;
+    }
+    __syncthreads();
+    for (int p = t; p < P; p += blockDim.x) {
+        float mean = 0.f;
+        for (int pass = 0; pass < 2; ++pass) {
+            float acc = 0.f;
+            for (int k = 0; k < K; ++k) {
+                const int i = s_sel[k];
+                float e;
+                if (a.eps) {
+                    e = a.eps[((size_t)r * N + i) * P + p];
+                } else {
+                    const float4 v = noise_group(c, a.key, a.sigma + (size_t)r * P, i, p >> 2, robot);
+                    const int kk = p & 3;
+                    e = kk == 0 ? v.x : (kk == 1 ? v.y : (kk == 2 ? v.z : v.w));
+                }
+                acc += pass == 0 ? e : (e - mean) * (e - mean);
+            }
+            if (pass == 0) mean = acc / (float)K;
+            else {
+                float v = acc / (float)(K - 1) + 1e-8f;
+                if (c.cem_sqrt) v = sqrtf(v);
+                v = v > c.cem_hi ? c.cem_hi : v;
+                v = v < c.cem_lo ? c.cem_lo : v;
+                a.sigma_out[(size_t)r * P + p] = v;
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(FIN_THREADS_MAX) k_finalize(const __grid_constant__ DevCfg c, const FinalizeArgs a) {
+    extern __shared__ float smem[];
+    finalize_robot(c, a, blockIdx.x, smem);
+}
+
+// Arrival ticket of the fused finalize: true in the block that arrives last for its robot (all partials and costs of
+// the robot are then visible through L2); that block also re-arms the counter for the next launch on the stream.
+__device__ __forceinline__ bool last_block_of_robot(unsigned int *ticket, int nblk) {
+    __shared__ unsigned int s_ticket;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_ticket = atomicAdd(ticket, 1u);
+    __syncthreads();
+    if (s_ticket != (unsigned)(nblk - 1)) return false;
+    if (threadIdx.x == 0) *ticket = 0u;
+    __threadfence();
+    return true;
+}
+
 // ---------------------------------------------------------------- rollout kernel (throughput regime) -------
 // Shared memory layout (floats):
-//   w[T] | live[T] (int) | par[P][T+1] | best[P] | sigma[P] (cem only) | state[24] | ref[12] | timing[4] | st[8H] |
+//   w[T] | live[T] (u16) | par[P][T+1] | best[P] | sigma[P] (cem only) | state[24] | ref[12] | timing[4] | st[8H] |
 //   ref_fz[H] | basis[4H] | index[H] (int) | mgk[8] | red[64]
 // par[p][t] = best[p] + eps[t][p] is the parameter vector of thread t's rollout, one COLUMN per thread: the rollout's
 // own reads are conflict-free, and with the row stride T+1 so are the row-wise reads of the softmin-weighted sum.
 // (sigma only exists for cem_mppi: at P = 144, T = 128 leaving it out is what lets three blocks share an SM.)
 __host__ __device__ inline int rollout_smem_floats(int P, int H, int T, bool cem) {
-    return 2 * T + P * (T + 1) + (cem ? 2 : 1) * P + 24 + 12 + 4 + 8 * H + H + 4 * H + H + 8 + 64;
+    return T + T / 2 + P * (T + 1) + (cem ? 2 : 1) * P + 24 + 12 + 4 + 8 * H + H + 4 * H + H + 8 + 40;
 }
 
 // V[p] = sum_t w_t par[p][t] over the block, written to part[PART_HDR + p].  At temperature 1 with costs of 1e3..1e5
 // almost every weight underflows to exactly 0 (the reference multiplies those by eps and adds 0): the live (t, w)
 // pairs are compacted in ascending t (deterministic summation order) and only they are visited.
 template <int STRIDE>
-__device__ __forceinline__ void weighted_rows(const float *s_par, float *s_w, int *s_live, float *s_red, float w, int P,
+__device__ __forceinline__ void weighted_rows(const float *s_par, float *s_w, unsigned short *s_live, float *s_red, float w, int P,
                                               float *part) {
     const int t = threadIdx.x, T = blockDim.x, lane = t & 31, wid = t >> 5, nw = T >> 5;
     const bool live = w > 0.f;
@@ -199,7 +437,7 @@ __device__ __forceinline__ void weighted_rows(const float *s_par, float *s_w, in
     }
     if (live) {
         const int k = base + __popc(m & ((1u << lane) - 1u));
-        s_live[k] = t;
+        s_live[k] = (unsigned short)t;
         s_w[k] = w;
     }
     __syncthreads();
@@ -217,8 +455,8 @@ __global__ void __launch_bounds__(T, T == 128 ? 3 : 1) k_rollout(const __grid_co
     constexpr int STRIDE = T + 1;
     const int P = c.P, H = c.H, t = threadIdx.x;
     float *s_w = smem;
-    int *s_live = reinterpret_cast<int *>(s_w + T);
-    float *s_par = s_w + 2 * T;
+    unsigned short *s_live = reinterpret_cast<unsigned short *>(s_w + T);
+    float *s_par = s_w + T + T / 2;
     float *s_best = s_par + P * STRIDE;
     float *s_sigma = s_best + P;
     float *s_state = s_sigma + (c.method == QPMPC_METHOD_CEM ? P : 0);
@@ -321,19 +559,20 @@ __global__ void __launch_bounds__(T, T == 128 ? 3 : 1) k_rollout(const __grid_co
             part[2] = bc;
             part[3] = __int_as_float(bi);
         }
-        return;
+    } else {
+        // softmin numerators relative to the block minimum (merged exactly by finalize_robot), :828-836
+        const float w = valid ? __expf(-(cost - bc)) : 0.f;
+        const float sw = block_sum(w, s_red);
+        if (t == 0) {
+            part[0] = bc;
+            part[1] = sw;
+            part[2] = bc;
+            part[3] = __int_as_float(bi);
+        }
+        // finalize_robot turns sum_b scale_b V_b / sum_b scale_b sw_b into the updated parameters
+        weighted_rows<STRIDE>(s_par, s_w, s_live, s_red, w, P, part);
     }
-    // softmin numerators relative to the block minimum (merged exactly in k_finalize), :828-836
-    const float w = valid ? __expf(-(cost - bc)) : 0.f;
-    const float sw = block_sum(w, s_red);
-    if (t == 0) {
-        part[0] = bc;
-        part[1] = sw;
-        part[2] = bc;
-        part[3] = __int_as_float(bi);
-    }
-    // k_finalize turns sum_b scale_b V_b / sum_b scale_b sw_b into the updated parameters
-    weighted_rows<STRIDE>(s_par, s_w, s_live, s_red, w, P, part);
+    if (a.fused && last_block_of_robot(a.tickets + r, a.nblk)) finalize_robot(c, a, r, s_par);
 }
 
 // ---------------------------------------------------------------- quad rollout kernel (latency regime) ------
@@ -346,10 +585,11 @@ __global__ void __launch_bounds__(T, T == 128 ? 3 : 1) k_rollout(const __grid_co
 // first and only wave.  Runtime horizon / spline count: this is also the kernel for any non-default horizon when
 // the launch is small.
 // Shared memory (floats): w[QB] | par[P][QB+1] | best[P] | sigma[P] | state[24] | ref[12] | timing[4] | stance[4H] |
-//   ref_fz[H] | q[H] | index[H] | mgk[8] | cost[QB]
-constexpr int QB = 32;  // rollouts per 128-thread block
-__host__ __device__ inline int quad_smem_floats(int P, int H) {
-    return QB + P * (QB + 1) + 2 * P + 24 + 12 + 4 + 4 * H + 3 * H + 8 + QB;
+//   ref_fz[H] | q[H] | index[H] | mgk[8] | cost[QB] | red[64]
+// QB = rollouts per block (4 QB threads): 128 for a full-size solve (79 partials to merge at N = 10,000), 32 for
+// small N (more blocks, more SMs).
+__host__ __device__ inline int quad_smem_floats(int P, int H, int QB) {
+    return QB + P * (QB + 1) + 2 * P + 24 + 12 + 4 + 4 * H + 3 * H + 8 + QB + 64;
 }
 
 __device__ __forceinline__ float quad_sum(float v) {
@@ -358,9 +598,13 @@ __device__ __forceinline__ float quad_sum(float v) {
     return v;
 }
 
-template <int PARAM, bool GA>
+template <int PARAM, bool GA, int QB>
 __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__ DevCfg c, const RolloutArgs a) {
     extern __shared__ __align__(16) float smem[];
+#ifdef QPMPC_TIMING
+    unsigned long long g0_;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g0_));
+#endif
     constexpr int T = 4 * QB, stride = QB + 1;
     const int P = c.P, H = c.H, t = threadIdx.x;
     const int leg = t & 3, rb = t >> 2, lane = t & 31, qbase = lane & ~3;
@@ -462,6 +706,7 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
     const float rb_ = leg == 0 ? ref[1] : leg == 1 ? ref[4] : leg == 2 ? ref[7] : ref[10];
     const float rc = leg == 0 ? ref[2] : leg == 1 ? ref[5] : leg == 2 ? ref[8] : ref[11];
     const float rq = __fdividef((float)c.S, hl);  // position in chunk = step / (horizon_leg / S) - index
+    const float b1 = c.bounds[1], b2 = c.bounds[2];
     const int hs = H * stride;
     float cost = 0.f;
     float kc[3][4];
@@ -480,8 +725,7 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
             istep = max(ncnt, 0);  // a swing leg's value is multiplied by 0: any finite stand-in does
             if (PARAM != QPMPC_PARAM_ZERO_ORDER) {
                 const float stepf = (float)istep;
-                int idx = 0;
-                for (int j = 1; j <= c.S; ++j) idx += (stepf >= c.bounds[j]) ? 1 : 0;
+                const int idx = chunk_of(c, stepf, b1, b2);
                 if (idx != cur) {
                     load_chunk<PARAM, stride>(c, col, leg, idx, kc);
                     cur = idx;
@@ -575,216 +819,58 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
     if (a.costs_only) return;
     __syncthreads();
 
-    // ---- block partials: warp 0 owns the 32 costs
+    // ---- block partials: thread t < QB owns the cost of rollout t of the block
     float *part = a.partials + ((size_t)r * a.nblk + blockIdx.x) * (PART_HDR + P);
-    if (t < 32) {
-        const float ct = s_cost[t];
+    {
+        float *s_red = s_cost + QB;
         const int it = blockIdx.x * QB + t;
+        const bool own = t < QB && it < a.n;
+        const float ct = own ? s_cost[t] : INFINITY;
         float bc = ct;
-        int bi = it < a.n ? it : 0x7fffffff;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const float oc = __shfl_xor_sync(0xffffffffu, bc, o);
-            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-            argmin_combine(bc, bi, oc, oi);
-        }
-        float w = it < a.n ? __expf(-(ct - bc)) : 0.f;
-        s_w[t] = w;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) w += __shfl_xor_sync(0xffffffffu, w, o);
+        int bi = own ? it : 0x7fffffff;
+        block_argmin(bc, bi, s_red);
+        const float w = own ? __expf(-(ct - bc)) : 0.f;
+        if (t < QB) s_w[t] = w;
+        const float sw = block_sum(w, s_red);
         if (t == 0) {
             part[0] = bc;
-            part[1] = c.method == QPMPC_METHOD_RANDOM ? 0.f : w;
+            part[1] = c.method == QPMPC_METHOD_RANDOM ? 0.f : sw;
             part[2] = bc;
             part[3] = __int_as_float(bi);
         }
     }
-    if (c.method == QPMPC_METHOD_RANDOM) return;
-    __syncthreads();
-    for (int p = t; p < P; p += T) {
-        const float *row = s_par + p * stride;
-        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-#pragma unroll
-        for (int k = 0; k < QB; k += 4) {
-            const float4 w4 = *reinterpret_cast<const float4 *>(s_w + k);
-            a0 = fmaf(w4.x, row[k], a0);
-            a1 = fmaf(w4.y, row[k + 1], a1);
-            a2 = fmaf(w4.z, row[k + 2], a2);
-            a3 = fmaf(w4.w, row[k + 3], a3);
-        }
-        part[PART_HDR + p] = (a0 + a1) + (a2 + a3);
-    }
-}
-
-// ---------------------------------------------------------------- finalize kernel --------------------------
-// Shared: best_out[P] | sel (elite indices) [cem_elite] | red[64] | misc
-template <int PARAM>
-__device__ void grf_and_prediction(const DevCfg &c, const float *s_best, const float *state, const float *contact,
-                                   qpmpc_result *out) {
-    // centroidal_nmpc_jax.py:707-784: spline at (step = 0.0, horizon_leg = 1), passed-in contact_sequence[:, 0]
-    float f[4][3], st[4];
-    const int index = chunk_index(c, 0.0f);
-    const float q = chunk_tau(c, 0.0f, 1.0f, index);
-    const CubicBasis B = cubic_basis(q);
-#pragma unroll
-    for (int l = 0; l < 4; ++l) {
-        st[l] = contact[l * c.H];
-        const float *pl = s_best + l * c.np;
-        spline_eval<PARAM>(c, [&](int j) { return pl[j]; }, 0, index, q, B, f[l]);
-    }
-    const float nst = ((st[0] + st[1]) + st[2]) + st[3];
-    shape_forces(c, f, st, c.mg / nst);
-    float x[12];
-#pragma unroll
-    for (int k = 0; k < 12; ++k) x[k] = state[k];
-    srbd_step(c, x, state + 12, f, st, c.dts[0]);
-#pragma unroll
-    for (int l = 0; l < 4; ++l)
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            out->grf[3 * l + k] = f[l][k];
-            out->footholds[3 * l + k] = 0.f;
-        }
-#pragma unroll
-    for (int k = 0; k < 12; ++k) {
-        out->predicted_state[k] = x[k];
-        out->predicted_state[12 + k] = state[12 + k];
-    }
-}
-
-__global__ void __launch_bounds__(FIN_THREADS_MAX) k_finalize(const __grid_constant__ DevCfg c, const FinalizeArgs a) {
-    extern __shared__ float smem[];
-    const int P = c.P, N = c.N, t = threadIdx.x, r = blockIdx.x;
-    const int lane = t & 31, wid = t >> 5, nw = blockDim.x >> 5;
-    float *s_best = smem;
-    float *s_red = s_best + P;
-    int *s_sel = reinterpret_cast<int *>(s_red + 64);
-    float *s_sc = reinterpret_cast<float *>(s_sel + ((c.method == QPMPC_METHOD_CEM ? c.cem_elite : 0) + 8));
-    float *s_acc = s_sc + a.nblk;  // [nw][P]
-    const float *part = a.partials + (size_t)r * a.nblk * (PART_HDR + P);
-    const int stride = PART_HDR + P;
-    const uint32_t robot = (uint32_t)r;
-
-    // global minimum / first argmin over the block partials (nanargmin: lowest index among equal minima)
-    float bc = INFINITY;
-    int bi = 0x7fffffff;
-    for (int b = t; b < a.nblk; b += blockDim.x)
-        argmin_combine(bc, bi, part[(size_t)b * stride + 2], __float_as_int(part[(size_t)b * stride + 3]));
-    block_argmin(bc, bi, s_red);
-
-    if (c.method == QPMPC_METHOD_RANDOM) {  // best = control_parameters_vec[best_index], :692
-        for (int p = t; p < P; p += blockDim.x) {
-            float e;
-            if (a.eps) {
-                e = a.eps[((size_t)r * N + bi) * P + p];
-            } else {
-                const float4 v = noise_group(c, a.key, nullptr, bi, p >> 2, robot);
-                const int k = p & 3;
-                e = k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w));
-            }
-            s_best[p] = __fadd_rn(a.best[(size_t)r * P + p], e);
-        }
-    } else {
-        // best + sum_i w_i eps_i = sum_i w_i par_i / sum_i w_i with w = softmin(costs), :828-836.  Each rollout block
-        // left {min_b, sum_t w, V[P]} relative to its own minimum; rescale by exp(-(min_b - min)) and merge:
-        // warps stride over the blocks, lanes over the parameters (coalesced rows), then a cross-warp sum.
-        float dpart = 0.f;
-        for (int b = t; b < a.nblk; b += blockDim.x) {
-            const float sc = __expf(-(part[(size_t)b * stride] - bc));
-            s_sc[b] = sc;
-            dpart += part[(size_t)b * stride + 1] * sc;
-        }
-        const float den = block_sum(dpart, s_red);  // its barriers also publish s_sc
-        for (int p0 = 0; p0 < P; p0 += 32) {
-            const int p = p0 + lane;
-            float acc = 0.f;
-            if (p < P) {
-                // most blocks' minima sit far above the global one: their scale underflows to exactly 0 and their row
-                // is not even fetched (upstream those samples contribute 0 * eps = 0)
-                for (int b = wid; b < a.nblk; b += nw) {
-                    const float sc = s_sc[b];
-                    if (sc != 0.f) acc = fmaf(sc, part[(size_t)b * stride + PART_HDR + p], acc);
-                }
-                s_acc[wid * P + p] = acc;
-            }
-        }
+    if (c.method != QPMPC_METHOD_RANDOM) {
         __syncthreads();
-        for (int p = t; p < P; p += blockDim.x) {
-            float num = 0.f;
-            for (int w = 0; w < nw; ++w) num += s_acc[w * P + p];
-            s_best[p] = num / den;
-        }
-    }
-    __syncthreads();
-    for (int p = t; p < P; p += blockDim.x) a.best_out[(size_t)r * P + p] = s_best[p];
-
-    qpmpc_result *out = a.result + r;
-    if (t == 0) {
-        out->best_cost = bc;
-        out->best_index = bi;
-        out->reserved = 0;
-        float bf;
-        if (c.ga)
-            bf = a.freqs ? a.freqs[(size_t)r * N + bi] : freq_sample(c, a.key, bi, robot, a.nominal[r], a.oswing[r]);
-        else
-            bf = (c.method == QPMPC_METHOD_CEM) ? 1.65f : 1.4f;  // centroidal_nmpc_jax.py:786,930,1083
-        out->best_freq = bf;
-        const float *state = a.state + r * 24;
-        const float *contact = a.contact + (size_t)r * 4 * c.H;
-        if (c.param == QPMPC_PARAM_ZERO_ORDER)
-            grf_and_prediction<QPMPC_PARAM_ZERO_ORDER>(c, s_best, state, contact, out);
-        else if (c.param == QPMPC_PARAM_LINEAR)
-            grf_and_prediction<QPMPC_PARAM_LINEAR>(c, s_best, state, contact, out);
-        else
-            grf_and_prediction<QPMPC_PARAM_CUBIC>(c, s_best, state, contact, out);
-    }
-
-    if (c.method != QPMPC_METHOD_CEM || a.sigma_out == nullptr) return;
-    // ---- CEM: elites = argsort(costs)[:K] (stable: ties by index), new sigma from their noise rows,
-    // centroidal_nmpc_jax.py:1075-1081 (K=10, sqrt, clip [0.2,5]) / ..._gait_adaptive.py:1115-1121 (K=200, no sqrt, [0.5,3])
-    const int K = min(c.cem_elite, N);
-    const float *costs = a.costs + (size_t)r * N;
-    float lc = -INFINITY;
-    int li = -1;
-    for (int k = 0; k < K; ++k) {
-        float mc = INFINITY;
-        int mi = 0x7fffffff;
-        for (int i = t; i < N; i += blockDim.x) {
-            const float ci = costs[i];
-            if (ci > lc || (ci == lc && i > li)) argmin_combine(mc, mi, ci, i);
-        }
-        block_argmin(mc, mi, s_red);
-        if (t == 0) s_sel[k] = mi;
-        lc = mc;
-        li = mi;
-    }
-    __syncthreads();
-    for (int p = t; p < P; p += blockDim.x) {
-        float mean = 0.f;
-        for (int pass = 0; pass < 2; ++pass) {
-            float acc = 0.f;
-            for (int k = 0; k < K; ++k) {
-                const int i = s_sel[k];
-                float e;
-                if (a.eps) {
-                    e = a.eps[((size_t)r * N + i) * P + p];
-                } else {
-                    const float4 v = noise_group(c, a.key, a.sigma + (size_t)r * P, i, p >> 2, robot);
-                    const int kk = p & 3;
-                    e = kk == 0 ? v.x : (kk == 1 ? v.y : (kk == 2 ? v.z : v.w));
-                }
-                acc += pass == 0 ? e : (e - mean) * (e - mean);
+        for (int p = t; p < P; p += T) {
+            const float *row = s_par + p * stride;
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+            for (int k = 0; k < QB; k += 4) {
+                const float4 w4 = *reinterpret_cast<const float4 *>(s_w + k);
+                a0 = fmaf(w4.x, row[k], a0);
+                a1 = fmaf(w4.y, row[k + 1], a1);
+                a2 = fmaf(w4.z, row[k + 2], a2);
+                a3 = fmaf(w4.w, row[k + 3], a3);
             }
-            if (pass == 0) mean = acc / (float)K;
-            else {
-                float v = acc / (float)(K - 1) + 1e-8f;
-                if (c.cem_sqrt) v = sqrtf(v);
-                v = v > c.cem_hi ? c.cem_hi : v;
-                v = v < c.cem_lo ? c.cem_lo : v;
-                a.sigma_out[(size_t)r * P + p] = v;
-            }
+            part[PART_HDR + p] = (a0 + a1) + (a2 + a3);
         }
     }
+#ifdef QPMPC_TIMING
+    unsigned long long g1_, g2_, g3_;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g1_));
+    if (a.fused && last_block_of_robot(a.tickets + r, a.nblk)) {
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g2_));
+        finalize_robot(c, a, r, s_par);
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g3_));
+        if (t == 0) {
+            a.result[r].footholds[6] = (float)(g1_ - g0_);
+            a.result[r].footholds[7] = (float)(g2_ - g1_);
+            a.result[r].footholds[8] = (float)(g3_ - g2_);
+        }
+    }
+#else
+    if (a.fused && last_block_of_robot(a.tickets + r, a.nblk)) finalize_robot(c, a, r, s_par);
+#endif
 }
 
 // ---------------------------------------------------------------- noise dump -------------------------------
@@ -825,7 +911,7 @@ struct qpmpc_handle {
     int device;
     cudaStream_t stream;
     int num_sms;
-    rollout_fn fn128, fn32, fn_quad;
+    rollout_fn fn128, fn32, fn_quad32, fn_quad128;
     size_t max_smem;
     // single-robot staging: one pinned input block, one pinned output block
     float *h_in, *d_in;
@@ -833,6 +919,7 @@ struct qpmpc_handle {
     size_t in_floats, out_floats;
     float *d_costs;     // [max_robots * N]
     float *d_partials;  // [max_robots * nblk_max * (4 + P)]
+    unsigned int *d_tickets;  // [max_robots], zero between launches
     size_t partial_floats;
     int64_t launches;
     int profiling;                  // qpmpc_set_profiling: record events around each kernel of a solve
@@ -873,14 +960,15 @@ static rollout_fn pick_rollout(int param, int ga) {
         default: return k_rollout<QPMPC_PARAM_CUBIC, true, T>;
     }
 }
+template <int QB>
 static rollout_fn pick_quad(int param, int ga) {
     switch (param * 2 + (ga ? 1 : 0)) {
-        case 0: return k_rollout_quad<QPMPC_PARAM_ZERO_ORDER, false>;
-        case 1: return k_rollout_quad<QPMPC_PARAM_ZERO_ORDER, true>;
-        case 2: return k_rollout_quad<QPMPC_PARAM_LINEAR, false>;
-        case 3: return k_rollout_quad<QPMPC_PARAM_LINEAR, true>;
-        case 4: return k_rollout_quad<QPMPC_PARAM_CUBIC, false>;
-        default: return k_rollout_quad<QPMPC_PARAM_CUBIC, true>;
+        case 0: return k_rollout_quad<QPMPC_PARAM_ZERO_ORDER, false, QB>;
+        case 1: return k_rollout_quad<QPMPC_PARAM_ZERO_ORDER, true, QB>;
+        case 2: return k_rollout_quad<QPMPC_PARAM_LINEAR, false, QB>;
+        case 3: return k_rollout_quad<QPMPC_PARAM_LINEAR, true, QB>;
+        case 4: return k_rollout_quad<QPMPC_PARAM_CUBIC, false, QB>;
+        default: return k_rollout_quad<QPMPC_PARAM_CUBIC, true, QB>;
     }
 }
 // QPMPC_KERNEL=quad|thread pins the kernel choice (the tests exercise both kernels at every size with it)
@@ -903,11 +991,15 @@ static LaunchPlan plan_launch(const qpmpc_handle *h, int n, long long total_roll
     pl.quad = total_rollouts < subparts * 32 * 2;
     if (!strcmp(kernel_override(), "quad")) pl.quad = true;
     if (!strcmp(kernel_override(), "thread")) pl.quad = false;
-    if (pl.quad && (size_t)quad_smem_floats(d.P, d.H) * 4 > h->max_smem) pl.quad = false;
+    // rollouts per quad block: 128 keeps the number of partials the last block merges small; 32 spreads a small solve
+    int QB = n >= 4096 ? 128 : 32;
+    if (const char *q = getenv("QPMPC_QB")) QB = atoi(q) == 128 ? 128 : 32;
+    if (pl.quad && QB == 128 && (size_t)quad_smem_floats(d.P, d.H, 128) * 4 > h->max_smem) QB = 32;
+    if (pl.quad && (size_t)quad_smem_floats(d.P, d.H, QB) * 4 > h->max_smem) pl.quad = false;
     if (pl.quad) {
         pl.T = 4 * QB;
         pl.nblk = (n + QB - 1) / QB;
-        pl.smem = (size_t)quad_smem_floats(d.P, d.H) * 4;
+        pl.smem = (size_t)quad_smem_floats(d.P, d.H, QB) * 4;
     } else {
         const int T = (size_t)rollout_smem_floats(d.P, d.H, 128, d.method == QPMPC_METHOD_CEM) * 4 <= h->max_smem ? 128 : 32;
         pl.T = T;
@@ -915,6 +1007,11 @@ static LaunchPlan plan_launch(const qpmpc_handle *h, int n, long long total_roll
         pl.smem = (size_t)rollout_smem_floats(d.P, d.H, T, d.method == QPMPC_METHOD_CEM) * 4;
     }
     return pl;
+}
+
+static rollout_fn pick_fn(const qpmpc_handle *h, const LaunchPlan &pl) {
+    if (pl.quad) return pl.T == 512 ? h->fn_quad128 : h->fn_quad32;
+    return pl.T == 128 ? h->fn128 : h->fn32;
 }
 
 extern "C" const char *qpmpc_last_error(void) { return g_err.c_str(); }
@@ -981,9 +1078,17 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     }
     h->fn128 = pick_rollout<128>(d.param, d.ga);
     h->fn32 = pick_rollout<32>(d.param, d.ga);
-    h->fn_quad = pick_quad(d.param, d.ga);
+    h->fn_quad32 = pick_quad<32>(d.param, d.ga);
+    h->fn_quad128 = pick_quad<128>(d.param, d.ga);
     cudaError_t e = cudaSuccess;
-    for (rollout_fn f : {h->fn128, h->fn32, h->fn_quad})
+    size_t static_smem = 0;  // the kernels' own __shared__ variables come out of the same per-block budget
+    for (rollout_fn f : {h->fn128, h->fn32, h->fn_quad32, h->fn_quad128}) {
+        cudaFuncAttributes fa;
+        if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, (const void *)f);
+        if (e == cudaSuccess && fa.sharedSizeBytes > static_smem) static_smem = fa.sharedSizeBytes;
+    }
+    h->max_smem -= static_smem;
+    for (rollout_fn f : {h->fn128, h->fn32, h->fn_quad32, h->fn_quad128})
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute((const void *)f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_smem);
     if (e != cudaSuccess) { delete h; return fail(QPMPC_E_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e)); }
@@ -1001,7 +1106,9 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
               cudaMalloc(&h->d_in, h->in_floats * 4) == cudaSuccess &&
               cudaMalloc(&h->d_out, h->out_floats * 4) == cudaSuccess &&
               cudaMalloc(&h->d_costs, (size_t)c.max_robots * d.N * 4) == cudaSuccess &&
-              cudaMalloc(&h->d_partials, h->partial_floats * 4) == cudaSuccess;
+              cudaMalloc(&h->d_partials, h->partial_floats * 4) == cudaSuccess &&
+              cudaMalloc(&h->d_tickets, (size_t)c.max_robots * 4) == cudaSuccess &&
+              cudaMemset(h->d_tickets, 0, (size_t)c.max_robots * 4) == cudaSuccess;
     if (!ok) {
         std::string m = std::string("allocation failed: ") + cudaGetErrorString(cudaGetLastError());
         qpmpc_destroy(h);
@@ -1023,6 +1130,7 @@ extern "C" int qpmpc_destroy(qpmpc_handle *h) {
     if (h->d_out) cudaFree(h->d_out);
     if (h->d_costs) cudaFree(h->d_costs);
     if (h->d_partials) cudaFree(h->d_partials);
+    if (h->d_tickets) cudaFree(h->d_tickets);
     delete h;
     return QPMPC_OK;
 }
@@ -1038,30 +1146,35 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
     const LaunchPlan pl = plan_launch(h, N, (long long)N * R);
     const int nblk = pl.nblk;
     if ((size_t)R * nblk * (PART_HDR + P) > h->partial_floats) return fail(QPMPC_E_ARG, "internal: partial buffer too small");
-    RolloutArgs ra;
+    SolveArgs ra;
+    memset(&ra, 0, sizeof ra);
     ra.state = b.d_state; ra.reference = b.d_reference; ra.contact = b.d_contact_sequence; ra.best = b.d_best_in;
     ra.sigma = b.d_sigma_in; ra.timing = b.d_timing; ra.nominal = b.d_nominal_freq; ra.oswing = b.d_optimize_swing;
     ra.eps = b.d_eps; ra.freqs = b.d_freqs;
     ra.costs = b.d_costs ? b.d_costs : h->d_costs; ra.partials = h->d_partials;
+    ra.result = b.d_result; ra.best_out = b.d_best_out; ra.sigma_out = b.d_sigma_out; ra.tickets = h->d_tickets;
     ra.key = NoiseKey{seed, offset}; ra.n = N; ra.costs_only = 0; ra.nblk = nblk;
+    // One launch per solve: the last rollout block of each robot runs the finalize step in the shared memory its
+    // parameter columns occupied.  Falls back to the stand-alone k_finalize when that scratch is too small
+    // (huge N with tiny P) or when QPMPC_FUSED=0 asks for the two-kernel path (tests cover both).
+    const int K = d.method == QPMPC_METHOD_CEM ? d.cem_elite : 0;
+    const int scratch = pl.quad ? P * (pl.T / 4 + 1) : P * (pl.T + 1);
+    const char *fe = getenv("QPMPC_FUSED");
+    ra.fused = finalize_smem_floats(P, nblk, K, pl.T) <= scratch && !(fe && fe[0] == '0');
     if (h->profiling) CU(cudaEventRecord(h->ev[0], h->stream));
-    (pl.quad ? h->fn_quad : (pl.T == 128 ? h->fn128 : h->fn32))<<<dim3(nblk, R), pl.T, pl.smem, h->stream>>>(d, ra);
+    pick_fn(h, pl)<<<dim3(nblk, R), pl.T, pl.smem, h->stream>>>(d, ra);
     CU(cudaGetLastError());
     if (h->profiling) CU(cudaEventRecord(h->ev[1], h->stream));
-    FinalizeArgs fa;
-    fa.state = b.d_state; fa.reference = b.d_reference; fa.contact = b.d_contact_sequence; fa.best = b.d_best_in;
-    fa.sigma = b.d_sigma_in; fa.nominal = b.d_nominal_freq; fa.oswing = b.d_optimize_swing;
-    fa.eps = b.d_eps; fa.freqs = b.d_freqs; fa.costs = ra.costs; fa.partials = h->d_partials;
-    fa.result = b.d_result; fa.best_out = b.d_best_out; fa.sigma_out = b.d_sigma_out;
-    fa.key = ra.key; fa.nblk = nblk;
-    // one block per robot: 512 threads when there are many rollout blocks to merge (single robot), 128 otherwise
-    const int fin_threads = nblk > 16 ? FIN_THREADS_MAX : 128;
-    const size_t fsmem = (size_t)(P + 64 + (d.method == QPMPC_METHOD_CEM ? d.cem_elite : 0) + 8 + nblk +
-                                  (fin_threads / 32) * P) * 4;
-    k_finalize<<<R, fin_threads, fsmem, h->stream>>>(d, fa);
-    CU(cudaGetLastError());
+    h->launches += 1;
+    if (!ra.fused) {
+        // one block per robot: 512 threads when there are many rollout blocks to merge (single robot), 128 otherwise
+        const int fin_threads = nblk > 16 ? FIN_THREADS_MAX : 128;
+        const size_t fsmem = (size_t)finalize_smem_floats(P, nblk, K, fin_threads) * 4;
+        k_finalize<<<R, fin_threads, fsmem, h->stream>>>(d, ra);
+        CU(cudaGetLastError());
+        h->launches += 1;
+    }
     if (h->profiling) CU(cudaEventRecord(h->ev[2], h->stream));
-    h->launches += 2;
     return QPMPC_OK;
 }
 
@@ -1150,7 +1263,7 @@ extern "C" int qpmpc_rollout_costs(qpmpc_handle *h, const float *state, const fl
     ra.eps = d_params; ra.freqs = d_freqs; ra.costs = d_costs; ra.n = n; ra.costs_only = 1;
     const LaunchPlan pl = plan_launch(h, n, n);
     ra.nblk = pl.nblk;
-    (pl.quad ? h->fn_quad : (pl.T == 128 ? h->fn128 : h->fn32))<<<dim3(pl.nblk, 1), pl.T, pl.smem, h->stream>>>(d, ra);
+    pick_fn(h, pl)<<<dim3(pl.nblk, 1), pl.T, pl.smem, h->stream>>>(d, ra);
     CU(cudaGetLastError());
     h->launches += 1;
     CU(cudaStreamSynchronize(h->stream));

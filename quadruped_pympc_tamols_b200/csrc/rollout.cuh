@@ -137,6 +137,16 @@ __device__ __forceinline__ float4 chunk_basis(float q) {
     return make_float4(1.f - q, q, 0.f, 0.f);
 }
 
+// spline chunk of a (non-negative) step: the number of knots linspace(0, H, S+1)[1..S] at or below it
+// (centroidal_nmpc_jax.py:186-188 / 210-212).  b1, b2 = the first two knots held in registers: at the shipped
+// num_splines = 2 no constant-bank lookups remain in the step loop.
+__device__ __forceinline__ int chunk_of(const DevCfg &c, float stepf, float b1, float b2) {
+    if (c.S <= 2) return (stepf >= b1 ? 1 : 0) + ((c.S == 2 && stepf >= b2) ? 1 : 0);
+    int idx = 0;
+    for (int j = 1; j <= c.S; ++j) idx += (stepf >= c.bounds[j]) ? 1 : 0;
+    return idx;
+}
+
 struct Problem {
     float x[12], feet[12], ref[12];
 };
@@ -229,6 +239,7 @@ __device__ __forceinline__ float rollout_gait_adaptive(const DevCfg &c, const fl
     }
     Problem pb;
     load_problem(pb, s_state, s_ref);
+    const float b1 = c.bounds[1], b2 = c.bounds[2];
     float cost = 0.f;
     float k[4][3][4];
     int ncnt[4] = {-1, -1, -1, -1}, cur[4] = {-1, -1, -1, -1};  // ..._gait_adaptive.py:339
@@ -255,8 +266,7 @@ __device__ __forceinline__ float rollout_gait_adaptive(const DevCfg &c, const fl
                 f[l][2] = p[2 * hs];
             } else {
                 const float stepf = (float)step;
-                int idx = 0;
-                for (int j = 1; j <= c.S; ++j) idx += (stepf >= c.bounds[j]) ? 1 : 0;  // bounds ascend: = the last j
+                const int idx = chunk_of(c, stepf, b1, b2);
                 if (idx != cur[l]) {
                     load_chunk<PARAM, STRIDE>(c, col, l, idx, k[l]);
                     cur[l] = idx;

@@ -35,14 +35,19 @@ GAITS = {"trot": ([0.5, 1.0, 1.0, 0.5], 1.4, 0.65), "pace": ([0.8, 0.3, 0.8, 0.3
          "bound": ([0.5, 0.5, 0.0, 0.0], 1.8, 0.65)}
 
 
-@pytest.fixture(params=["auto", "quad", "thread"])
+@pytest.fixture(params=["auto", "quad", "thread", "quad-2launch", "thread-2launch"])
 def kernel(request, monkeypatch):
     """Every rollout kernel at every size: QPMPC_KERNEL pins the choice the library otherwise makes from the launch size
     (quad = 4 lanes per rollout, latency regime; thread = one thread per rollout, throughput regime)."""
-    if request.param == "auto":
+    name, _, two = request.param.partition("-")
+    if name == "auto":
         monkeypatch.delenv("QPMPC_KERNEL", raising=False)
     else:
-        monkeypatch.setenv("QPMPC_KERNEL", request.param)
+        monkeypatch.setenv("QPMPC_KERNEL", name)
+    if two:  # QPMPC_FUSED=0: rollout kernel + stand-alone k_finalize instead of the fused last-block finalize
+        monkeypatch.setenv("QPMPC_FUSED", "0")
+    else:
+        monkeypatch.delenv("QPMPC_FUSED", raising=False)
     return request.param
 
 
