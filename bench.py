@@ -288,7 +288,9 @@ def run_cuda(args):
 
 
 def run_batched(torch, _cabi, dev, local_rank, rank, world, barrier, max_over_ranks, fp32_peak, robots_total=8192, n=1024):
-    R = robots_total // world
+    from quadruped_pympc_tamols_b200.sharding import shard_bounds
+    lo, hi = shard_bounds(robots_total, world, rank)  # contiguous block of robots per rank, no collective
+    R = hi - lo
     rng = np.random.default_rng(77 + rank)
     h = _cabi.Handle(_cabi.make_config(sampling_method="mppi", parametrization="zero_order", num_parallel_computations=n,
                                        max_robots=R, device=local_rank, **ALIENGO))
@@ -305,7 +307,7 @@ def run_batched(torch, _cabi, dev, local_rank, rank, world, barrier, max_over_ra
     steps, roll = 10, []
     with torch.cuda.stream(stream):
         for it in range(3 + steps):
-            b = _cabi.QpmpcBatch(num_robots=R, d_state=d_state.data_ptr(), d_reference=d_ref.data_ptr(),
+            b = _cabi.QpmpcBatch(num_robots=R, robot_offset=lo, d_state=d_state.data_ptr(), d_reference=d_ref.data_ptr(),
                                  d_contact_sequence=d_seq.data_ptr(), d_best_in=d_best[it & 1].data_ptr(),
                                  d_result=d_res.data_ptr(), d_best_out=d_best[(it + 1) & 1].data_ptr())
             if it == 3:

@@ -109,10 +109,11 @@ int qpmpc_solve(qpmpc_handle *h, const float *state, const float *reference, con
                 const float *d_freqs, qpmpc_result *out, float *best_out, float *sigma_out, float *costs_out);
 
 /* Device-resident problem description for the batched entry points; every pointer is a DEVICE pointer
- * with `num_robots` leading rows.  Robot r draws its Philox noise from subsequence r. */
+ * with `num_robots` leading rows. */
 typedef struct qpmpc_batch {
     int32_t num_robots;
-    int32_t reserved;
+    int32_t robot_offset;            /* global id of row 0: robot r of this batch draws from Philox subsequence
+                                        robot_offset + r, so results do not depend on how robots are sharded */
     const float *d_state;            /* [R,24] */
     const float *d_reference;        /* [R,24] */
     const float *d_contact_sequence; /* [R,4,H] */

@@ -48,7 +48,7 @@ RESULT_FLOATS = C.sizeof(QpmpcResult) // 4  # 52
 
 
 class QpmpcBatch(C.Structure):
-    _fields_ = [("num_robots", C.c_int32), ("reserved", C.c_int32),
+    _fields_ = [("num_robots", C.c_int32), ("robot_offset", C.c_int32),
                 ("d_state", C.c_void_p), ("d_reference", C.c_void_p), ("d_contact_sequence", C.c_void_p),
                 ("d_best_in", C.c_void_p), ("d_sigma_in", C.c_void_p), ("d_timing", C.c_void_p),
                 ("d_nominal_freq", C.c_void_p), ("d_optimize_swing", C.c_void_p), ("d_eps", C.c_void_p),

@@ -41,6 +41,7 @@ struct SolveArgs {
     int n;            // rollouts per robot in this launch
     int costs_only;   // 1: jit_vectorized_rollout semantics (eps = parameters, no saturation, no partials)
     int nblk;         // rollout blocks per robot
+    int robot_offset; // global id of robot 0 of this launch (Philox subsequence = robot_offset + r)
     int fused;        // 1: the last rollout block of a robot runs finalize_robot itself (one launch per solve)
 };
 typedef SolveArgs RolloutArgs;
@@ -231,7 +232,7 @@ __device__ void finalize_robot(const DevCfg &c, const FinalizeArgs &a, const int
     __syncthreads();  // fused call: every thread is done with the columns this scratch overlays
     const float *part = a.partials + (size_t)r * a.nblk * (PART_HDR + P);
     const int stride = PART_HDR + P;
-    const uint32_t robot = (uint32_t)r;
+    const uint32_t robot = (uint32_t)(r + a.robot_offset);
 
     // One pass over the block headers {min_b, sum_t w, min_b, argmin}: kept in shared memory for the rescale.
     // global minimum / first argmin (nanargmin: lowest index among equal minima)
@@ -500,7 +501,7 @@ __global__ void __launch_bounds__(T, T == 128 ? 3 : 1) k_rollout(const __grid_co
     __syncthreads();
 
     // ---- this thread's parameter vector -> shared column t
-    const uint32_t robot = (uint32_t)r;
+    const uint32_t robot = (uint32_t)(r + a.robot_offset);
     if (a.eps) {
         const float *src = a.eps + ((size_t)r * a.n + (size_t)blockIdx.x * T) * P;
         const int rows = min(T, a.n - blockIdx.x * T);
@@ -649,7 +650,7 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
     __syncthreads();
 
     // ---- parameters of the block's 32 rollouts -> columns of s_par; lane `leg` draws groups leg, leg + 4, ...
-    const uint32_t robot = (uint32_t)r;
+    const uint32_t robot = (uint32_t)(r + a.robot_offset);
     if (a.eps) {
         const float *src = a.eps + ((size_t)r * a.n + (size_t)blockIdx.x * QB) * P;
         const int rows = min(QB, a.n - blockIdx.x * QB);
@@ -1153,7 +1154,7 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
     ra.eps = b.d_eps; ra.freqs = b.d_freqs;
     ra.costs = b.d_costs ? b.d_costs : h->d_costs; ra.partials = h->d_partials;
     ra.result = b.d_result; ra.best_out = b.d_best_out; ra.sigma_out = b.d_sigma_out; ra.tickets = h->d_tickets;
-    ra.key = NoiseKey{seed, offset}; ra.n = N; ra.costs_only = 0; ra.nblk = nblk;
+    ra.key = NoiseKey{seed, offset}; ra.n = N; ra.costs_only = 0; ra.nblk = nblk; ra.robot_offset = b.robot_offset;
     // One launch per solve: the last rollout block of each robot runs the finalize step in the shared memory its
     // parameter columns occupied.  Falls back to the stand-alone k_finalize when that scratch is too small
     // (huge N with tiny P) or when QPMPC_FUSED=0 asks for the two-kernel path (tests cover both).

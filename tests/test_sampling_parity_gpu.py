@@ -299,3 +299,37 @@ def test_batched_robots_match_single_solves(kernel):
         assert abs(res[r, 48] - o["best_cost"]) <= COST_RTOL * abs(o["best_cost"])
     assert not np.array_equal(costs[0, 1:], costs[1, 1:])
     h.close()
+
+
+def test_batched_results_do_not_depend_on_sharding():
+    """robot r draws from Philox subsequence robot_offset + r, so 6 robots in one launch equal
+    two launches of 3 robots (what two ranks would run) bit for bit."""
+    rng = np.random.default_rng(9)
+    mass, inertia, _, _ = ROBOTS["go2"]
+    R, n = 6, 512
+    h = _cabi.Handle(_cabi.make_config(mass=mass, inertia=np.array(inertia), sampling_method="mppi",
+                                       parametrization="cubic_spline", num_parallel_computations=n, max_robots=R))
+    P = h.P
+    probs = [synth_problem("go2", "trot", rng) for _ in range(R)]
+    d_state, d_ref = dev(np.stack([p[0] for p in probs])), dev(np.stack([p[1] for p in probs]))
+    d_seq, d_best = dev(np.stack([p[2] for p in probs])), dev(rng.normal(size=(R, P)))
+
+    def run(lo, hi):
+        k = hi - lo
+        d_res = torch.zeros((k, _cabi.RESULT_FLOATS), dtype=torch.float32, device="cuda")
+        d_bo = torch.zeros((k, P), dtype=torch.float32, device="cuda")
+        d_costs = torch.zeros((k, n), dtype=torch.float32, device="cuda")
+        b = _cabi.QpmpcBatch(num_robots=k, robot_offset=lo, d_state=d_state[lo:hi].data_ptr(),
+                             d_reference=d_ref[lo:hi].data_ptr(), d_contact_sequence=d_seq[lo:hi].data_ptr(),
+                             d_best_in=d_best[lo:hi].data_ptr(), d_result=d_res.data_ptr(), d_best_out=d_bo.data_ptr(),
+                             d_costs=d_costs.data_ptr())
+        h.solve_batched(b, 5, 2)
+        torch.cuda.synchronize()
+        return d_res.cpu().numpy(), d_bo.cpu().numpy(), d_costs.cpu().numpy()
+
+    full = run(0, R)
+    halves = [run(0, 3), run(3, 6)]
+    for k in range(3):
+        assert np.array_equal(full[k], np.concatenate([halves[0][k], halves[1][k]]))
+    assert not np.array_equal(full[2][0, 1:], full[2][3, 1:])
+    h.close()
