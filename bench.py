@@ -67,6 +67,7 @@ def dist_env():
 def cpu_solve_loop(steps, warmup, seed=0):
     """The CPU port of compute_control_mppi on the C2 workload: noise generation + 10k rollouts + update per step."""
     from oracle import srbd_oracle as so
+    so.set_threads(os.cpu_count() or 1)  # all host threads, also under torchrun (which exports OMP_NUM_THREADS=1)
     cfg = so.make_cfg(parametrization="cubic_spline", gait_adaptive=True, **GO2)
     rng = np.random.default_rng(seed)
     st, ref, seq, timing, nominal = synth_problem(rng, 0.27, (0.19, 0.13))

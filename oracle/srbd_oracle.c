@@ -441,6 +441,15 @@ void oracle_fill_noise(float *eps, int N, int P, float sigma, uint64_t seed) {
 
 int oracle_sizeof_cfg(void) { return (int)sizeof(oracle_cfg); }
 int oracle_sizeof_result(void) { return (int)sizeof(oracle_result); }
+/* torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU baseline arm asks for all host threads explicitly */
+void oracle_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int oracle_max_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();

@@ -124,6 +124,11 @@ def solve(cfg, method, state, ref, contact_seq, best, eps, timing=None, freqs=No
                 sigma=sigma if method == "cem_mppi" else None, best_index=int(res.best_index))
 
 
+def set_threads(n, fast=True):
+    """Use n OpenMP threads in the -O3 build (torchrun pins OMP_NUM_THREADS=1 per rank otherwise)."""
+    _lib(fast).oracle_set_threads(int(n))
+
+
 def max_threads(fast=True):
     return _lib(fast).oracle_max_threads()
 
