@@ -91,11 +91,11 @@ def lib():
         L.qpmpc_stream.restype = vp
         L.qpmpc_launch_count.argtypes = [vp]
         L.qpmpc_launch_count.restype = C.c_int64
-        L.qpmpc_solve.argtypes = [vp, fp, fp, fp, fp, C.c_uint64, C.c_uint64, fp, C.c_float, C.c_int32, fp, vp, vp,
-                                  C.POINTER(QpmpcResult), fp, fp, fp]
+        L.qpmpc_solve.argtypes = [vp, vp, vp, vp, vp, C.c_uint64, C.c_uint64, vp, C.c_float, C.c_int32, vp, vp, vp,
+                                  vp, vp, vp, vp]  # host pointers passed as integers (cheapest ctypes marshalling)
         L.qpmpc_solve_batched.argtypes = [vp, C.POINTER(QpmpcBatch), C.c_uint64, C.c_uint64]
-        L.qpmpc_rollout_costs.argtypes = [vp, fp, fp, fp, fp, vp, vp, C.c_int32, vp]
-        L.qpmpc_generate_noise.argtypes = [vp, C.c_uint64, C.c_uint64, C.c_int32, fp, C.c_float, C.c_int32, vp, vp]
+        L.qpmpc_rollout_costs.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp]
+        L.qpmpc_generate_noise.argtypes = [vp, C.c_uint64, C.c_uint64, C.c_int32, vp, C.c_float, C.c_int32, vp, vp]
         L.qpmpc_set_profiling.argtypes = [vp, C.c_int32]
         L.qpmpc_profile_last.argtypes = [vp, fp, fp]
         L.qpmpc_measure_fp32_peak.argtypes = [C.c_int32, fp]
@@ -154,7 +154,7 @@ def _f32(a):
 
 
 def _fp(a):
-    return a.ctypes.data_as(C.POINTER(C.c_float)) if a is not None else None
+    return a.ctypes.data if a is not None else None
 
 
 class Handle:
@@ -193,17 +193,16 @@ class Handle:
         sg = None
         if sigma_in is not None:
             sg = _f32(np.broadcast_to(np.asarray(sigma_in, np.float32), (self.P,)))
-        res = QpmpcResult()
+        res = np.empty(RESULT_FLOATS, np.float32)  # qpmpc_result as 52 packed 4-byte words
         best_out = np.empty(self.P, np.float32)
         sigma_out = np.empty(self.P, np.float32) if sg is not None else None
         costs = np.empty(self.N, np.float32) if want_costs else None
         check(lib().qpmpc_solve(self._h, _fp(st), _fp(rf), _fp(cs), _fp(bi), int(seed), int(offset), _fp(tm),
-                                float(nominal_freq), int(optimize_swing), _fp(sg), d_eps, d_freqs, C.byref(res),
-                                _fp(best_out), _fp(sigma_out), _fp(costs)))
-        return dict(grf=np.array(res.grf, np.float32), footholds=np.array(res.footholds, np.float32),
-                    predicted_state=np.array(res.predicted_state, np.float32), best=best_out,
-                    best_cost=np.float32(res.best_cost), best_freq=np.float32(res.best_freq), costs=costs,
-                    sigma=sigma_out, best_index=int(res.best_index))
+                                float(nominal_freq), int(optimize_swing), _fp(sg), d_eps, d_freqs,
+                                _fp(res), _fp(best_out), _fp(sigma_out), _fp(costs)))
+        return dict(grf=res[0:12], footholds=res[12:24], predicted_state=res[24:48], best=best_out,
+                    best_cost=res[48], best_freq=res[49], costs=costs, sigma=sigma_out,
+                    best_index=int(res[50:51].view(np.int32)[0]))
 
     def set_profiling(self, on=True):
         check(lib().qpmpc_set_profiling(self._h, int(on)))

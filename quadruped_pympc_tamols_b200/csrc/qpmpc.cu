@@ -37,6 +37,8 @@ struct SolveArgs {
     qpmpc_result *result;
     float *best_out, *sigma_out;
     unsigned int *tickets;  // [robots] arrival counters of the fused finalize (zero between launches)
+    unsigned int *done_flag;  // mapped host word the finalize step of robot 0 stores done_value to (or NULL)
+    unsigned int done_value;
     NoiseKey key;
     int n;            // rollouts per robot in this launch
     int costs_only;   // 1: jit_vectorized_rollout semantics (eps = parameters, no saturation, no partials)
@@ -340,7 +342,7 @@ __device__ void finalize_robot(const DevCfg &c, const FinalizeArgs &a, const int
 #endif
     }
 
-    if (c.method != QPMPC_METHOD_CEM || a.sigma_out == nullptr) return;
+    if (c.method == QPMPC_METHOD_CEM && a.sigma_out != nullptr) {
     // ---- CEM: elites = argsort(costs)[:K] (stable: ties by index), new sigma from their noise rows,
     // centroidal_nmpc_jax.py:1075-1081 (K=10, sqrt, clip [0.2,5]) / ..._gait_adaptive.py:1115-1121 (K=200, no sqrt, [0.5,3])
     const int K = min(c.cem_elite, N);
@@ -385,6 +387,13 @@ __device__ void finalize_robot(const DevCfg &c, const FinalizeArgs &a, const int
                 a.sigma_out[(size_t)r * P + p] = v;
             }
         }
+    }
+    }
+    // host-buffer solve: results live in mapped host memory; publish them system-wide, then raise the host's flag
+    if (a.done_flag != nullptr && r == 0) {
+        __threadfence_system();
+        __syncthreads();
+        if (t == 0) *reinterpret_cast<volatile unsigned int *>(a.done_flag) = a.done_value;
     }
 }
 
@@ -917,6 +926,8 @@ struct qpmpc_handle {
     // single-robot staging: one pinned input block, one pinned output block
     float *h_in, *d_in;
     float *h_out, *d_out;
+    float *m_io, *md_io;  // mapped (zero-copy) host block of qpmpc_solve: inputs | outputs | done flag
+    unsigned int seq;     // value the next solve stores to the done flag
     size_t in_floats, out_floats;
     float *d_costs;     // [max_robots * N]
     float *d_partials;  // [max_robots * nblk_max * (4 + P)]
@@ -1104,6 +1115,8 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
               cudaEventCreate(&h->ev[2]) == cudaSuccess &&
               cudaMallocHost(&h->h_in, h->in_floats * 4) == cudaSuccess &&
               cudaMallocHost(&h->h_out, h->out_floats * 4 + (size_t)d.N * 4) == cudaSuccess &&
+              cudaHostAlloc(&h->m_io, (h->in_floats + h->out_floats + 16) * 4, cudaHostAllocMapped) == cudaSuccess &&
+              cudaHostGetDevicePointer(&h->md_io, h->m_io, 0) == cudaSuccess &&
               cudaMalloc(&h->d_in, h->in_floats * 4) == cudaSuccess &&
               cudaMalloc(&h->d_out, h->out_floats * 4) == cudaSuccess &&
               cudaMalloc(&h->d_costs, (size_t)c.max_robots * d.N * 4) == cudaSuccess &&
@@ -1127,6 +1140,7 @@ extern "C" int qpmpc_destroy(qpmpc_handle *h) {
         if (h->ev[k]) cudaEventDestroy(h->ev[k]);
     if (h->h_in) cudaFreeHost(h->h_in);
     if (h->h_out) cudaFreeHost(h->h_out);
+    if (h->m_io) cudaFreeHost(h->m_io);
     if (h->d_in) cudaFree(h->d_in);
     if (h->d_out) cudaFree(h->d_out);
     if (h->d_costs) cudaFree(h->d_costs);
@@ -1141,7 +1155,8 @@ extern "C" void *qpmpc_stream(qpmpc_handle *h) { return h ? (void *)h->stream : 
 extern "C" int64_t qpmpc_launch_count(const qpmpc_handle *h) { return h ? h->launches : 0; }
 
 // launches k_rollout + k_finalize for `b` on the handle's stream (no synchronisation)
-static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, uint64_t offset) {
+static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, uint64_t offset,
+                        unsigned int *done_flag = nullptr, unsigned int done_value = 0) {
     const DevCfg &d = h->dc;
     const int R = b.num_robots, N = d.N, P = d.P;
     const LaunchPlan pl = plan_launch(h, N, (long long)N * R);
@@ -1155,6 +1170,7 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
     ra.costs = b.d_costs ? b.d_costs : h->d_costs; ra.partials = h->d_partials;
     ra.result = b.d_result; ra.best_out = b.d_best_out; ra.sigma_out = b.d_sigma_out; ra.tickets = h->d_tickets;
     ra.key = NoiseKey{seed, offset}; ra.n = N; ra.costs_only = 0; ra.nblk = nblk; ra.robot_offset = b.robot_offset;
+    ra.done_flag = done_flag; ra.done_value = done_value;
     // One launch per solve: the last rollout block of each robot runs the finalize step in the shared memory its
     // parameter columns occupied.  Falls back to the stand-alone k_finalize when that scratch is too small
     // (huge N with tiny P) or when QPMPC_FUSED=0 asks for the two-kernel path (tests cover both).
@@ -1205,10 +1221,21 @@ extern "C" int qpmpc_solve(qpmpc_handle *h, const float *state, const float *ref
     if (d.method == QPMPC_METHOD_CEM && !sigma_in) return fail(QPMPC_E_ARG, "cem_mppi needs sigma_in");
     if (d.ga && !timing) return fail(QPMPC_E_ARG, "gait adaptive needs timing");
     CU(cudaSetDevice(h->device));
-    // pack the inputs into one pinned block -> one H2D copy
-    float *p = h->h_in;
+    // Default I/O: the ~1 KB of inputs goes down as ONE H2D copy from pinned memory; the finalize step stores the
+    // results straight into a mapped pinned block and raises a flag there that the host spins on -- no D2H copy
+    // command and no stream-synchronise wake-up on the critical path (measured e2e p50 47 us against 55 us with
+    // H2D + D2H + cudaStreamSynchronize).  QPMPC_ZEROCOPY=0 selects that classic path; QPMPC_ZEROCOPY=1 also maps the
+    // INPUTS (every block then reads them over PCIe: 74 us, kept only as the measured negative result).
+    const char *zc = getenv("QPMPC_ZEROCOPY");
+    const bool zero_copy = !(zc && zc[0] == '0');
+    const bool mapped_in = zero_copy && zc && zc[0] == '1';  // inputs read over PCIe by the kernel (slower, kept for A/B)
     const size_t o_state = 0, o_ref = 24, o_contact = 48, o_best = o_contact + 4 * H, o_sigma = o_best + P,
                  o_timing = o_sigma + P, o_nominal = o_timing + 4, o_oswing = o_nominal + 1;
+    const size_t res_floats = sizeof(qpmpc_result) / 4;
+    float *p = mapped_in ? h->m_io : h->h_in;            // host view of the input block
+    float *din = mapped_in ? h->md_io : h->d_in;          // device view of the input block
+    float *hout = zero_copy ? h->m_io + h->in_floats : h->h_out;
+    float *dout = zero_copy ? h->md_io + h->in_floats : h->d_out;
     memcpy(p + o_state, state, 24 * 4);
     memcpy(p + o_ref, reference, 24 * 4);
     memcpy(p + o_contact, contact_sequence, (size_t)4 * H * 4);
@@ -1217,27 +1244,50 @@ extern "C" int qpmpc_solve(qpmpc_handle *h, const float *state, const float *ref
     if (timing) memcpy(p + o_timing, timing, 16); else memset(p + o_timing, 0, 16);
     p[o_nominal] = nominal_step_frequency;
     memcpy(p + o_oswing, &optimize_swing, 4);
-    CU(cudaMemcpyAsync(h->d_in, h->h_in, h->in_floats * 4, cudaMemcpyHostToDevice, h->stream));
+    if (!mapped_in) CU(cudaMemcpyAsync(h->d_in, h->h_in, h->in_floats * 4, cudaMemcpyHostToDevice, h->stream));
     qpmpc_batch b;
     memset(&b, 0, sizeof b);
     b.num_robots = 1;
-    b.d_state = h->d_in + o_state; b.d_reference = h->d_in + o_ref; b.d_contact_sequence = h->d_in + o_contact;
-    b.d_best_in = h->d_in + o_best; b.d_sigma_in = h->d_in + o_sigma; b.d_timing = h->d_in + o_timing;
-    b.d_nominal_freq = h->d_in + o_nominal; b.d_optimize_swing = reinterpret_cast<const int32_t *>(h->d_in + o_oswing);
+    b.d_state = din + o_state; b.d_reference = din + o_ref; b.d_contact_sequence = din + o_contact;
+    b.d_best_in = din + o_best; b.d_sigma_in = din + o_sigma; b.d_timing = din + o_timing;
+    b.d_nominal_freq = din + o_nominal; b.d_optimize_swing = reinterpret_cast<const int32_t *>(din + o_oswing);
     b.d_eps = d_eps; b.d_freqs = d_freqs;
-    const size_t res_floats = sizeof(qpmpc_result) / 4;
-    b.d_result = reinterpret_cast<qpmpc_result *>(h->d_out);
-    b.d_best_out = h->d_out + res_floats;
-    b.d_sigma_out = (d.method == QPMPC_METHOD_CEM) ? h->d_out + res_floats + P : nullptr;
+    b.d_result = reinterpret_cast<qpmpc_result *>(dout);
+    b.d_best_out = dout + res_floats;
+    b.d_sigma_out = (d.method == QPMPC_METHOD_CEM) ? dout + res_floats + P : nullptr;
     b.d_costs = h->d_costs;
-    int rc = launch_solve(h, b, seed, offset);
-    if (rc) return rc;
-    CU(cudaMemcpyAsync(h->h_out, h->d_out, h->out_floats * 4, cudaMemcpyDeviceToHost, h->stream));
-    if (costs_out) CU(cudaMemcpyAsync(h->h_out + h->out_floats, h->d_costs, (size_t)N * 4, cudaMemcpyDeviceToHost, h->stream));
-    CU(cudaStreamSynchronize(h->stream));
-    memcpy(out, h->h_out, sizeof(qpmpc_result));
-    memcpy(best_out, h->h_out + res_floats, (size_t)P * 4);
-    if (sigma_out && d.method == QPMPC_METHOD_CEM) memcpy(sigma_out, h->h_out + res_floats + P, (size_t)P * 4);
+    if (zero_copy) {
+        volatile unsigned int *flag = reinterpret_cast<volatile unsigned int *>(h->m_io + h->in_floats + h->out_floats);
+        const unsigned int seq = ++h->seq;
+        int rc = launch_solve(h, b, seed, offset, reinterpret_cast<unsigned int *>(h->md_io + h->in_floats + h->out_floats), seq);
+        if (rc) return rc;
+        if (costs_out) {  // 4 N bytes: a regular copy behind the kernel; its completion also implies the flag
+            CU(cudaMemcpyAsync(h->h_out + h->out_floats, h->d_costs, (size_t)N * 4, cudaMemcpyDeviceToHost, h->stream));
+            CU(cudaStreamSynchronize(h->stream));
+        } else {
+            unsigned long long spins = 0;
+            while (*flag != seq) {
+                __builtin_ia32_pause();
+                if ((++spins & 0xFFFFF) == 0) {  // ~ms: make sure the kernel is still alive rather than spin forever
+                    const cudaError_t q = cudaStreamQuery(h->stream);
+                    if (q != cudaErrorNotReady) {
+                        if (q != cudaSuccess) return fail(QPMPC_E_CUDA, std::string("solve kernel: ") + cudaGetErrorString(q));
+                        break;
+                    }
+                }
+            }
+        }
+        if (*flag != seq) return fail(QPMPC_E_CUDA, "solve finished without publishing its results");
+    } else {
+        int rc = launch_solve(h, b, seed, offset);
+        if (rc) return rc;
+        CU(cudaMemcpyAsync(h->h_out, h->d_out, h->out_floats * 4, cudaMemcpyDeviceToHost, h->stream));
+        if (costs_out) CU(cudaMemcpyAsync(h->h_out + h->out_floats, h->d_costs, (size_t)N * 4, cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+    }
+    memcpy(out, hout, sizeof(qpmpc_result));
+    memcpy(best_out, hout + res_floats, (size_t)P * 4);
+    if (sigma_out && d.method == QPMPC_METHOD_CEM) memcpy(sigma_out, hout + res_floats + P, (size_t)P * 4);
     if (costs_out) memcpy(costs_out, h->h_out + h->out_floats, (size_t)N * 4);
     return QPMPC_OK;
 }

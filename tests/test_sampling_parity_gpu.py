@@ -333,3 +333,32 @@ def test_batched_results_do_not_depend_on_sharding():
         assert np.array_equal(full[k], np.concatenate([halves[0][k], halves[1][k]]))
     assert not np.array_equal(full[2][0, 1:], full[2][3, 1:])
     h.close()
+
+
+@pytest.mark.parametrize("method,want_costs", [("mppi", False), ("cem_mppi", True), ("random_sampling", False)])
+def test_zero_copy_solve_equals_copy_path(monkeypatch, method, want_costs):
+    """qpmpc_solve's default I/O (H2D copy in, mapped host block + done flag out), the fully mapped variant and the
+    classic H2D / D2H copies: bit-identical."""
+    rng = np.random.default_rng(21)
+    mass, inertia, _, _ = ROBOTS["go2"]
+    st, ref, seq, timing, nominal = synth_problem("go2", "bound", rng)
+    outs = []
+    for zc in ("", "1", "0"):
+        monkeypatch.setenv("QPMPC_ZEROCOPY", zc)
+        h = _cabi.Handle(_cabi.make_config(mass=mass, inertia=np.array(inertia), sampling_method=method,
+                                           parametrization="cubic_spline", gait_adaptive=(method != "cem_mppi"),
+                                           num_parallel_computations=10000))
+        best = np.zeros(h.P, np.float32)
+        sig = np.full(h.P, 3.0, np.float32) if method == "cem_mppi" else None
+        for it in range(3):  # repeated calls reuse the block and bump the flag value
+            r = h.solve(st, ref, seq, best, 3, it, timing=timing, nominal_freq=nominal, optimize_swing=1, sigma_in=sig,
+                        want_costs=want_costs)
+            best = r["best"].copy()
+            if sig is not None:
+                sig = r["sigma"].copy()
+        outs.append({k: np.array(v) for k, v in r.items() if v is not None})
+        h.close()
+    for other in outs[1:]:
+        assert outs[0].keys() == other.keys()
+        for k in outs[0]:
+            assert np.array_equal(outs[0][k], other[k]), k
