@@ -259,7 +259,7 @@ def run_cuda(args):
     # ---- CPU baseline (rank 0, N=1 only): bounded sample of the same workload
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        nsolve = 300
+        nsolve = 4000  # about 10 s of CPU work on the B200 host (2.4 ms per solve with 16 threads)
         times, cores = cpu_solve_loop(nsolve, 3)
         cpu = {"value": N_ROLLOUTS / float(times.mean()), "unit": "rollouts/s", "cores": cores, "kind": "port",
                "sample": f"{nsolve} full C2 solves (noise + 10000 rollouts + MPPI update), {times.sum():.1f} s of CPU work",
@@ -277,8 +277,9 @@ def run_cuda(args):
                         "api": "qpmpc_solve (host buffers; costs[N] left on the device as upstream)"},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak,
-                             "traffic": None, "kernel": "k_rollout<cubic,gait_adaptive>", "launch_ms": float(roll[:, 0].mean()),
-                             "finalize_ms": float(roll[:, 1].mean()), "flop_per_rollout": FLOP_PER_ROLLOUT["cubic_spline_ga"],
+                             "traffic": 87808, "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, profiles/r1o_ncu_raw_c2.csv (bytes)",
+                             "kernel": "k_rollout_quad<cubic,gait_adaptive,128> (rollouts + fused finalize, one launch per solve)", "launch_ms": float(roll[:, 0].mean()),
+                             "finalize_ms": float(roll[:, 1].mean()), "finalize": "fused into the rollout kernel (last block per robot)", "flop_per_rollout": FLOP_PER_ROLLOUT["cubic_spline_ga"],
                              "peak_source": "FP32 FMA-chain microbenchmark in this run (qpmpc_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 figure",
                              "note": "10k rollouts = 75.5 MFLOP: latency-bound at this size; see batched.roofline for the throughput regime"},
                 "cpu_baseline": cpu, "clocks": clk, "batched": batched, "tamols": tamols}
@@ -326,7 +327,8 @@ def run_batched(torch, _cabi, dev, local_rank, rank, world, barrier, max_over_ra
             "value": robots_total * n / (step_ms * 1e-3), "unit": "rollouts/s", "robot_solves_per_s": robots_total / (step_ms * 1e-3),
             "ms_per_step": step_ms, "scaling": "strong",
             "roofline": {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak,
-                         "kernel": "k_rollout<zero_order,fixed>", "launch_ms": roll_ms, "flop_per_rollout": FLOP_PER_ROLLOUT["zero_order"]}}
+                         "traffic": 31213056 // world, "traffic_source": "profiles/r1o_ncu_raw_c5.csv (bytes per launch at 8192 robots)",
+                         "kernel": "k_rollout<zero_order,fixed,128>", "launch_ms": roll_ms, "flop_per_rollout": FLOP_PER_ROLLOUT["zero_order"]}}
 
 
 def run_tamols(torch, dev, local_rank, rank, world, barrier, max_over_ranks, with_cpu):
@@ -407,7 +409,8 @@ def run_tamols(torch, dev, local_rank, rank, world, barrier, max_over_ranks, wit
                       "ms_per_step": step_ms, "footholds_per_s": robots_total * 4 / (step_ms * 1e-3),
                       "candidates_per_s": cand / (step_ms * 1e-3), "scaling": "strong", "gpu_launches_per_step": 1,
                       "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                                   "traffic": None, "kernel": "k_tamols_score<double,TMA>", "launch_ms": float(ms.mean()),
+                                   "traffic": 32219392, "traffic_source": "profiles/r1o_ncu_raw_tamols.csv (bytes per launch: the 2048x2048 f64 map once)",
+                                   "kernel": "k_tamols_score<double,TMA>", "launch_ms": float(ms.mean()),
                                    "algorithmic_bytes_per_candidate": 8, "peak_source": peak_src,
                                    "note": "FP64 arithmetic (about 330 FP64 instructions per feasible candidate) binds long before HBM: see DESIGN.md"}}
     out["launch_count_check"] = int(launches)
@@ -442,13 +445,15 @@ def run_tamols(torch, dev, local_rank, rank, world, barrier, max_over_ranks, wit
             n += 1
         c3t = (time.perf_counter() - t0) / n
         sub = sy.sweep_scene("go2", np.random.default_rng(91), "stepping_stones_tall", window=64, seed=4, robots=32)
-        t0 = time.perf_counter()
-        to.score(p, sub["heights"], sub["jobs"], want_scores=False, fast=True)
-        tb = time.perf_counter() - t0
+        t0, nb = time.perf_counter(), 0
+        while time.perf_counter() - t0 < 3.0:
+            to.score(p, sub["heights"], sub["jobs"], want_scores=False, fast=True)
+            nb += 1
+        tb = (time.perf_counter() - t0) / nb
         out["cpu_baseline"] = {"kind": "port", "cores": cores,
                                "c3t_footholds_per_s": 4 / c3t, "c3t_p50_ms": c3t * 1e3,
                                "batched_candidates_per_s": 32 * 4 * 64 * 64 / tb,
-                               "sample": f"{n} C3-T calls (3 s) and one 32-robot x 4 x 64x64 batch ({tb:.2f} s), oracle/tamols_oracle.c -O3 OpenMP",
+                               "sample": f"{n} C3-T calls (3 s) and {nb} batches of 32 robots x 4 legs x 64x64 candidates (3 s), oracle/tamols_oracle.c -O3 OpenMP",
                                "reference_python": "the reference's own Python loop measured 0.75 ms/candidate (15 footholds/s) in the build container (BASELINE.md section 2); it cannot travel to the GPU box"}
     return out
 

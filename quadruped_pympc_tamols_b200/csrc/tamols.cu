@@ -18,6 +18,7 @@
 
 #include <cmath>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -46,6 +47,10 @@ struct Args {
     long long scores_stride;
     Partial *partials;
     unsigned int *tickets;
+    unsigned int *jobs_done;   // [1] counter of finished jobs (host-buffer call only, else NULL)
+    unsigned int *host_flag;   // mapped host word that receives flag_value once every job has written its result
+    unsigned int flag_value;
+    int n_jobs;
     int rows, cols, pitch, max_tiles;
 };
 
@@ -383,6 +388,13 @@ __global__ void __launch_bounds__(THREADS) k_tamols_score(const __grid_constant_
         out.vertex2[0] += a.p.constraint_box_dx;
         out.vertex2[1] += a.p.constraint_box_dy;
         a.tickets[job] = 0;  // ready for the next launch on this stream
+        if (a.host_flag != nullptr) {  // results live in mapped host memory: publish, then count this job in
+            __threadfence_system();
+            if (atomicAdd(a.jobs_done, 1u) == (unsigned)(a.n_jobs - 1)) {
+                *a.jobs_done = 0u;
+                *reinterpret_cast<volatile unsigned int *>(a.host_flag) = a.flag_value;
+            }
+        }
     }
 }
 
@@ -413,7 +425,7 @@ struct tamols_handle {
     cudaStream_t stream;
     encode_tiled_fn encode;
     int64_t launches;
-    unsigned int *d_tickets;
+    unsigned int *d_tickets;   // [max_jobs] tile arrival tickets + [1] finished-job counter
     Partial *d_partials;
     size_t partial_cap;  // in Partial elements
     // cached tensor map
@@ -423,6 +435,8 @@ struct tamols_handle {
     // staging for tamols_score_host
     char *d_stage, *h_stage;
     size_t stage_cap;
+    char *m_out, *md_out;      // mapped pinned block of tamols_score_host: results | done flag
+    unsigned int seq;
 };
 
 extern "C" const char *tamols_last_error(void) { return g_terr.c_str(); }
@@ -464,8 +478,10 @@ extern "C" int tamols_create(const tamols_params *params, int32_t device, int32_
         h->encode = (encode_tiled_fn)fn;
     cudaGetLastError();
     bool ok = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) == cudaSuccess &&
-              cudaMalloc(&h->d_tickets, (size_t)max_jobs * sizeof(unsigned int)) == cudaSuccess &&
-              cudaMemset(h->d_tickets, 0, (size_t)max_jobs * sizeof(unsigned int)) == cudaSuccess;
+              cudaMalloc(&h->d_tickets, ((size_t)max_jobs + 1) * sizeof(unsigned int)) == cudaSuccess &&
+              cudaMemset(h->d_tickets, 0, ((size_t)max_jobs + 1) * sizeof(unsigned int)) == cudaSuccess &&
+              cudaHostAlloc(&h->m_out, (size_t)max_jobs * sizeof(tamols_result) + 64, cudaHostAllocMapped) == cudaSuccess &&
+              cudaHostGetDevicePointer(&h->md_out, h->m_out, 0) == cudaSuccess;
     if (!ok) {
         std::string m = std::string("allocation failed: ") + cudaGetErrorString(cudaGetLastError());
         tamols_destroy(h);
@@ -486,6 +502,7 @@ extern "C" int tamols_destroy(tamols_handle *h) {
     if (h->d_partials) cudaFree(h->d_partials);
     if (h->d_stage) cudaFree(h->d_stage);
     if (h->h_stage) cudaFreeHost(h->h_stage);
+    if (h->m_out) cudaFreeHost(h->m_out);
     delete h;
     return TAMOLS_OK;
 }
@@ -524,7 +541,8 @@ static bool get_tensor_map(tamols_handle *h, const void *d_heights, int dtype, i
 
 static int launch_score(tamols_handle *h, const void *d_heights, int dtype, int maps, int rows, int cols, int pitch,
                         const double *d_xy, const tamols_leg_job *d_jobs, int n_jobs, int max_nr, int max_nc,
-                        tamols_result *d_results, double *d_scores, int64_t scores_stride) {
+                        tamols_result *d_results, double *d_scores, int64_t scores_stride,
+                        unsigned int *host_flag = nullptr, unsigned int flag_value = 0) {
     const int max_tiles = ((max_nr + TH - 1) / TH) * ((max_nc + TW - 1) / TW);
     const size_t need = (size_t)n_jobs * max_tiles;
     if (need > h->partial_cap) {
@@ -542,6 +560,7 @@ static int launch_score(tamols_handle *h, const void *d_heights, int dtype, int 
     a.heights = d_heights; a.xy = d_xy; a.jobs = d_jobs; a.results = d_results; a.scores = d_scores;
     a.scores_stride = scores_stride; a.partials = h->d_partials; a.tickets = h->d_tickets;
     a.rows = rows; a.cols = cols; a.pitch = pitch; a.max_tiles = max_tiles;
+    a.jobs_done = h->d_tickets + h->max_jobs; a.host_flag = host_flag; a.flag_value = flag_value; a.n_jobs = n_jobs;
     const bool tma = get_tensor_map(h, d_heights, dtype, maps, rows, cols, pitch);
     const dim3 grid(max_tiles, n_jobs);
     if (dtype == TAMOLS_F64) {
@@ -624,6 +643,35 @@ extern "C" int tamols_score_host(tamols_handle *h, const double *heights, int32_
     memcpy(hs + o_j, jobs, sz_j);
     TCU(cudaMemcpyAsync(ds, hs, o_j + sz_j, cudaMemcpyHostToDevice, h->stream));  // one H2D copy
     double *d_scores = scores ? reinterpret_cast<double *>(ds + o_s) : nullptr;
+    // Without per-candidate scores (the product call) the results go straight into a mapped pinned block and the last
+    // finished job raises a flag there that the host spins on: no D2H copy command, no stream-synchronise wake-up.
+    // With scores (tests) or TAMOLS_ZEROCOPY=0: device results + one D2H copy + cudaStreamSynchronize.
+    const char *zc = getenv("TAMOLS_ZEROCOPY");
+    const bool mapped_out = !scores && !(zc && zc[0] == '0');
+    if (mapped_out) {
+        volatile unsigned int *flag = reinterpret_cast<volatile unsigned int *>(h->m_out + (size_t)h->max_jobs * sizeof(tamols_result));
+        const unsigned int seq = ++h->seq;
+        if (int rc = launch_score(h, ds + o_h, TAMOLS_F64, num_maps, rows, cols, pitch,
+                                  xy ? reinterpret_cast<const double *>(ds + o_xy) : nullptr,
+                                  reinterpret_cast<const tamols_leg_job *>(ds + o_j), n_jobs, max_nr, max_nc,
+                                  reinterpret_cast<tamols_result *>(h->md_out), nullptr, 0,
+                                  reinterpret_cast<unsigned int *>(h->md_out + (size_t)h->max_jobs * sizeof(tamols_result)), seq))
+            return rc;
+        unsigned long long spins = 0;
+        while (*flag != seq) {
+            __builtin_ia32_pause();
+            if ((++spins & 0xFFFFF) == 0) {  // ~ms: make sure the kernel is still alive rather than spin forever
+                const cudaError_t q = cudaStreamQuery(h->stream);
+                if (q != cudaErrorNotReady) {
+                    if (q != cudaSuccess) return tfail(TAMOLS_E_CUDA, std::string("scoring kernel: ") + cudaGetErrorString(q));
+                    break;
+                }
+            }
+        }
+        if (*flag != seq) return tfail(TAMOLS_E_CUDA, "scoring finished without publishing its results");
+        memcpy(results, h->m_out, sz_r);
+        return TAMOLS_OK;
+    }
     if (int rc = launch_score(h, ds + o_h, TAMOLS_F64, num_maps, rows, cols, pitch,
                               xy ? reinterpret_cast<const double *>(ds + o_xy) : nullptr,
                               reinterpret_cast<const tamols_leg_job *>(ds + o_j), n_jobs, max_nr, max_nc,

@@ -144,3 +144,20 @@ def test_bad_arguments_fail_loudly(tc):
     with pytest.raises(tc.TamolsError, match="window"):
         h.score_host(np.zeros((1, 8, 8)), jobs)
     h.close()
+
+
+def test_host_call_mapped_results_equal_copied_results(tc, monkeypatch):
+    """tamols_score_host without scores publishes its results through a mapped block + done flag; with
+    TAMOLS_ZEROCOPY=0 (or when scores are requested) through a D2H copy: identical bytes, also on repeated calls."""
+    rng = np.random.default_rng(2)
+    scenes = [sy.robot_scene("hyqreal1", rng, "stepping_stones") for _ in range(3)]
+    p = tc.make_params(sy.tamols_params_for("hyqreal1"), "hyqreal1")
+    h = tc.Handle(p, max_jobs=4)
+    for s in scenes:
+        monkeypatch.delenv("TAMOLS_ZEROCOPY", raising=False)
+        a, _ = h.score_host(s["heights"], s["jobs"], xy=s["xy"])
+        b, _ = h.score_host(s["heights"], s["jobs"], xy=s["xy"], want_scores=True)
+        monkeypatch.setenv("TAMOLS_ZEROCOPY", "0")
+        c, _ = h.score_host(s["heights"], s["jobs"], xy=s["xy"])
+        assert a.tobytes() == b.tobytes() == c.tobytes()
+    h.close()
