@@ -27,9 +27,12 @@
 
 namespace tamols {
 
-constexpr int TW = 32, TH = 8, HALO = 4;
-constexpr int BW = TW + 2 * HALO, BH = TH + 2 * HALO;  // 40 x 16 cells staged per tile
-constexpr int THREADS = TW * TH;
+// A block of 256 threads scores a TW x TH tile of candidates: TH = 32 (4 cells per thread in the gate pass, 4x fewer
+// blocks, partials and tickets) when the launch has enough tiles to fill the GPU, TH = 8 (one cell per thread) for a
+// few legs, where latency matters and the extra blocks spread over more SMs.
+constexpr int TW = 32, HALO = 4;
+constexpr int BW = TW + 2 * HALO;  // 40 cells per staged row; staged rows = TH + 2 * HALO
+constexpr int THREADS = 256;
 
 struct Partial {
     double score;
@@ -59,7 +62,7 @@ struct Ctx {
     double ox, oy, rax, ray, cax, cay;  // grid
     double arx, ary, acx, acy;          // axes / |axis|^2: grid coordinate = d . a
     int map, r0, c0, nr, nc, flags;
-    int br, bc;                          // map coordinates of the staged box's first cell
+    int br, bc, bh;                      // map coordinates of the staged box's first cell, staged rows
     long long map_base;                  // map * rows * pitch
     int pitch;
 };
@@ -75,7 +78,7 @@ __device__ __forceinline__ double lookup(const Args &a, const Ctx &c, const HT *
     ic = min(max(ic, c.c0), c.c0 + c.nc - 1);
     const int lr = ir - c.br, lc = ic - c.bc;
     HT h;
-    if ((unsigned)lr < (unsigned)BH && (unsigned)lc < (unsigned)BW)
+    if ((unsigned)lr < (unsigned)c.bh && (unsigned)lc < (unsigned)BW)
         h = s_box[lr * BW + lc];
     else
         h = __ldg(static_cast<const HT *>(a.heights) + c.map_base + (long long)ir * c.pitch + ic);
@@ -93,27 +96,33 @@ __device__ __forceinline__ void candidate_xy(const Args &a, const Ctx &c, int R,
     }
 }
 
-// candidate construction (:188-196) + _compute_tamols_score (:261-373) for map cell (R, C)
+// candidate construction (:188-196) for map cell (R, C) and _check_kinematic_feasibility (:375-395), the cheap first
+// gate of _compute_tamols_score (:287-290): most cells of a window fail it (they lie outside the leg's reach)
 template <typename HT>
-__device__ double score_candidate(const Args &a, const Ctx &c, const tamols_leg_job &j, const HT *s_box, int R, int C,
-                                  double cand[3]) {
+__device__ __forceinline__ bool candidate_reachable(const Args &a, const Ctx &c, const tamols_leg_job &j, const HT *s_box,
+                                                    int R, int C, double cand[3]) {
     const tamols_params &p = a.p;
     candidate_xy(a, c, R, C, cand[0], cand[1]);
     cand[2] = lookup(a, c, s_box, cand[0], cand[1]) + p.foot_clearance;
-    const double inf = __longlong_as_double(0x7ff0000000000000LL);
-    // _check_kinematic_feasibility (:375-395)
-    {
-        double d0 = cand[0] - j.hip[0], d1 = cand[1] - j.hip[1], d2 = cand[2] - j.hip[2];
-        const double dist_td = sqrt((d0 * d0 + d1 * d1) + d2 * d2);
-        if (!(p.l_min <= dist_td && dist_td <= p.l_max)) return inf;
-        if (c.flags & TAMOLS_FLAG_HAS_VELOCITY) {
-            d0 = cand[0] - (j.hip[0] + j.vel[0] * p.stance_duration);
-            d1 = cand[1] - (j.hip[1] + j.vel[1] * p.stance_duration);
-            d2 = cand[2] - (j.hip[2] + j.vel[2] * p.stance_duration);
-            const double dist_lo = sqrt((d0 * d0 + d1 * d1) + d2 * d2);
-            if (!(p.l_min <= dist_lo && dist_lo <= p.l_max)) return inf;
-        }
+    double d0 = cand[0] - j.hip[0], d1 = cand[1] - j.hip[1], d2 = cand[2] - j.hip[2];
+    const double dist_td = sqrt((d0 * d0 + d1 * d1) + d2 * d2);
+    if (!(p.l_min <= dist_td && dist_td <= p.l_max)) return false;
+    if (c.flags & TAMOLS_FLAG_HAS_VELOCITY) {
+        d0 = cand[0] - (j.hip[0] + j.vel[0] * p.stance_duration);
+        d1 = cand[1] - (j.hip[1] + j.vel[1] * p.stance_duration);
+        d2 = cand[2] - (j.hip[2] + j.vel[2] * p.stance_duration);
+        const double dist_lo = sqrt((d0 * d0 + d1 * d1) + d2 * d2);
+        if (!(p.l_min <= dist_lo && dist_lo <= p.l_max)) return false;
     }
+    return true;
+}
+
+// the rest of _compute_tamols_score (:291-373) for a reachable candidate
+template <typename HT>
+__device__ double score_reachable(const Args &a, const Ctx &c, const tamols_leg_job &j, const HT *s_box,
+                                  const double cand[3]) {
+    const tamols_params &p = a.p;
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
     // _check_leg_collision (:397-420)
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
@@ -242,23 +251,42 @@ __device__ __forceinline__ void argmin_combine(double &s, int &i, double os, int
 }
 
 // ---------------------------------------------------------------- the kernel ---------------------------------
-template <typename HT, bool USE_TMA>
+struct GridInv {
+    double arx, ary, acx, acy;
+};
+
+template <typename HT, bool USE_TMA, int TH>
 __global__ void __launch_bounds__(THREADS) k_tamols_score(const __grid_constant__ CUtensorMap tmap, const Args a) {
+    constexpr int BH = TH + 2 * HALO, CPT = TW * TH / THREADS;
     __shared__ __align__(128) HT s_box[BH * BW];
     __shared__ __align__(8) uint64_t s_bar;
+    __shared__ __align__(8) tamols_leg_job s_job;  // the job record, read once from global memory
+    __shared__ GridInv s_inv;
+    __shared__ unsigned short s_list[TW * TH];     // tile-local indices of the reachable candidates
+    __shared__ int s_nlist;
     __shared__ double s_rs[THREADS / 32];
     __shared__ int s_ri[THREADS / 32], s_rn[THREADS / 32];
     __shared__ unsigned int s_ticket;
 
     const int job = blockIdx.y, t = threadIdx.x;
-    const tamols_leg_job &j = a.jobs[job];
-    Ctx c;
-    c.map = j.map; c.r0 = j.r0; c.c0 = j.c0; c.nr = j.nr; c.nc = j.nc; c.flags = j.flags;
-    const int tiles_c = (c.nc + TW - 1) / TW, tiles_r = (c.nr + TH - 1) / TH;
+    // window shape first (two words): blocks beyond this job's own tile count leave at once
+    const int nr_ = a.jobs[job].nr, nc_ = a.jobs[job].nc;
+    const int tiles_c = (nc_ + TW - 1) / TW, tiles_r = (nr_ + TH - 1) / TH;
     const int ntiles = tiles_c * tiles_r;
     if ((int)blockIdx.x >= ntiles) return;
+    {   // the 136-byte job record -> shared memory, 34 lanes; lane 0 then derives the inverse grid axes once per block
+        static_assert(sizeof(tamols_leg_job) % 4 == 0, "job record is copied word-wise");
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(a.jobs + job);
+        if (t < (int)(sizeof(tamols_leg_job) / 4)) reinterpret_cast<uint32_t *>(&s_job)[t] = __ldg(src + t);
+        if (t == 0) s_nlist = 0;
+    }
+    __syncthreads();
+    const tamols_leg_job &j = s_job;
+    Ctx c;
+    c.map = j.map; c.r0 = j.r0; c.c0 = j.c0; c.nr = j.nr; c.nc = j.nc; c.flags = j.flags;
     const int tile_r = blockIdx.x / tiles_c, tile_c = blockIdx.x % tiles_c;
     c.br = c.r0 + tile_r * TH - HALO;
+    c.bh = BH;
     // TMA needs the box to start on a 16-byte boundary of the row (measured on B200: an odd f64 column raises
     // 'illegal instruction'), so the left halo is HALO .. HALO + 16/sizeof(HT) - 1 cells
     c.bc = (c.c0 + tile_c * TW - HALO) & ~(int)(16 / sizeof(HT) - 1);
@@ -282,27 +310,52 @@ __global__ void __launch_bounds__(THREADS) k_tamols_score(const __grid_constant_
     // ---- per-job constants while the copy is in flight
     c.ox = j.origin[0]; c.oy = j.origin[1];
     c.rax = j.row_axis[0]; c.ray = j.row_axis[1]; c.cax = j.col_axis[0]; c.cay = j.col_axis[1];
-    {
+    if (t == 32) {
         const double r2 = c.rax * c.rax + c.ray * c.ray, c2 = c.cax * c.cax + c.cay * c.cay;
-        c.arx = c.rax / r2; c.ary = c.ray / r2; c.acx = c.cax / c2; c.acy = c.cay / c2;
+        s_inv.arx = c.rax / r2; s_inv.ary = c.ray / r2; s_inv.acx = c.cax / c2; s_inv.acy = c.cay / c2;
     }
-    __syncthreads();  // s_bar initialised (TMA) / s_box written (plain)
+    __syncthreads();  // s_bar initialised (TMA) / s_box written (plain) / s_inv written
+    c.arx = s_inv.arx; c.ary = s_inv.ary; c.acx = s_inv.acx; c.acy = s_inv.acy;
     if (USE_TMA) mbar_wait(&s_bar, 0);
 
-    // ---- one candidate per thread
-    const int r = tile_r * TH + t / TW, q = tile_c * TW + t % TW;
-    const bool valid = r < c.nr && q < c.nc;
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
-    double s = inf;
-    int idx = 0x7fffffff;
-    if (valid) {
-        double cand[3];
-        s = score_candidate<HT>(a, c, j, s_box, c.r0 + r, c.c0 + q, cand);
-        idx = r * c.nc + q;
-        if (a.scores) a.scores[(long long)job * a.scores_stride + idx] = s;
-        if (!(s < inf)) s = inf;  // NaN is never selected by the reference's `score < best_score`
+    // ---- pass 1: every cell of the tile through the reachability gate; survivors are compacted into s_list so that
+    // pass 2 (collision line, edge, roughness, ...; ~10x the work) runs on full warps instead of a ragged annulus.
+    // The compaction order is arbitrary; the result is not: the reduction below is a lexicographic (score, index) min.
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) {
+        const int e = k * THREADS + t;
+        const int r = tile_r * TH + e / TW, q = tile_c * TW + e % TW;
+        bool reach = false;
+        if (r < c.nr && q < c.nc) {
+            double cand[3];
+            reach = candidate_reachable<HT>(a, c, j, s_box, c.r0 + r, c.c0 + q, cand);
+            if (!reach && a.scores) a.scores[(long long)job * a.scores_stride + r * c.nc + q] = inf;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, reach);
+        int base = 0;
+        if ((t & 31) == 0 && m) base = atomicAdd(&s_nlist, __popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (reach) s_list[base + __popc(m & ((1u << (t & 31)) - 1u))] = (unsigned short)e;
     }
-    int nfin = (valid && s < inf) ? 1 : 0;
+    __syncthreads();
+    // ---- pass 2: full score of the reachable candidates
+    double s = inf;
+    int idx = 0x7fffffff, nfin = 0;
+    const int nlist = s_nlist;
+    for (int i = t; i < nlist; i += THREADS) {
+        const int e = s_list[i];
+        const int r = tile_r * TH + e / TW, q = tile_c * TW + e % TW;
+        double cand[3];
+        candidate_reachable<HT>(a, c, j, s_box, c.r0 + r, c.c0 + q, cand);
+        double sc = score_reachable<HT>(a, c, j, s_box, cand);
+        const int ci = r * c.nc + q;
+        if (a.scores) a.scores[(long long)job * a.scores_stride + ci] = sc;
+        if (sc < inf) {  // NaN is never selected by the reference's `score < best_score`
+            ++nfin;
+            argmin_combine(s, idx, sc, ci);
+        }
+    }
 
     // ---- block reduction: lexicographic (score, index) minimum = first minimum in row-major order
 #pragma unroll
@@ -370,7 +423,7 @@ __global__ void __launch_bounds__(THREADS) k_tamols_score(const __grid_constant_
         if (s < inf) {
             out.best_index = idx;
             Ctx g = c;
-            g.br = -0x40000000;  // no staged box for this lookup: read the map through L2
+            g.bh = 0;            // no staged box for this lookup: read the map through L2
             g.bc = -0x40000000;
             candidate_xy(a, g, c.r0 + idx / c.nc, c.c0 + idx % c.nc, xyz[0], xyz[1]);
             xyz[2] = lookup<HT>(a, g, s_box, xyz[0], xyz[1]) + a.p.foot_clearance;
@@ -421,7 +474,7 @@ typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32
 
 struct tamols_handle {
     tamols_params p;
-    int device, max_jobs;
+    int device, max_jobs, num_sms;
     cudaStream_t stream;
     encode_tiled_fn encode;
     int64_t launches;
@@ -431,7 +484,7 @@ struct tamols_handle {
     // cached tensor map
     CUtensorMap tmap;
     const void *tm_ptr;
-    int tm_dtype, tm_maps, tm_rows, tm_cols, tm_pitch;
+    int tm_dtype, tm_maps, tm_rows, tm_cols, tm_pitch, tm_th;
     // staging for tamols_score_host
     char *d_stage, *h_stage;
     size_t stage_cap;
@@ -471,6 +524,7 @@ extern "C" int tamols_create(const tamols_params *params, int32_t device, int32_
     h->p = *params;
     h->device = device;
     h->max_jobs = max_jobs;
+    h->num_sms = prop.multiProcessorCount;
     void *fn = nullptr;
     cudaDriverEntryPointQueryResult qres;
     if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess &&
@@ -514,17 +568,18 @@ extern "C" int tamols_set_params(tamols_handle *h, const tamols_params *params) 
     return TAMOLS_OK;
 }
 
-// builds (or reuses) the 3-D tensor map [maps][rows][cols] with an BW x BH x 1 box; returns false when TMA cannot
+// builds (or reuses) the 3-D tensor map [maps][rows][cols] with a BW x (TH + 2 HALO) x 1 box; returns false when TMA cannot
 // describe this buffer (pitch or base not 16-byte aligned, driver entry point missing) -> plain-load kernel
-static bool get_tensor_map(tamols_handle *h, const void *d_heights, int dtype, int maps, int rows, int cols, int pitch) {
+static bool get_tensor_map(tamols_handle *h, const void *d_heights, int dtype, int maps, int rows, int cols, int pitch,
+                           int th) {
     const size_t es = dtype == TAMOLS_F64 ? 8 : 4;
     if (!h->encode || ((uintptr_t)d_heights & 15) || ((size_t)pitch * es) % 16) return false;
     if (h->tm_ptr == d_heights && h->tm_dtype == dtype && h->tm_maps == maps && h->tm_rows == rows &&
-        h->tm_cols == cols && h->tm_pitch == pitch)
+        h->tm_cols == cols && h->tm_pitch == pitch && h->tm_th == th)
         return true;
     const cuuint64_t gdim[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)maps};
     const cuuint64_t gstride[2] = {(cuuint64_t)pitch * es, (cuuint64_t)pitch * es * (cuuint64_t)rows};
-    const cuuint32_t box[3] = {BW, BH, 1};
+    const cuuint32_t box[3] = {BW, (cuuint32_t)(th + 2 * HALO), 1};
     const cuuint32_t estr[3] = {1, 1, 1};
     // CU_TENSOR_MAP_DATA_TYPE_FLOAT64 / FLOAT32: the copy is bit-exact for either
     const CUresult r = h->encode(&h->tmap, dtype == TAMOLS_F64 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
@@ -535,7 +590,7 @@ static bool get_tensor_map(tamols_handle *h, const void *d_heights, int dtype, i
         h->tm_ptr = nullptr;
         return false;
     }
-    h->tm_ptr = d_heights; h->tm_dtype = dtype; h->tm_maps = maps; h->tm_rows = rows; h->tm_cols = cols; h->tm_pitch = pitch;
+    h->tm_ptr = d_heights; h->tm_dtype = dtype; h->tm_maps = maps; h->tm_rows = rows; h->tm_cols = cols; h->tm_pitch = pitch; h->tm_th = th;
     return true;
 }
 
@@ -543,7 +598,11 @@ static int launch_score(tamols_handle *h, const void *d_heights, int dtype, int 
                         const double *d_xy, const tamols_leg_job *d_jobs, int n_jobs, int max_nr, int max_nc,
                         tamols_result *d_results, double *d_scores, int64_t scores_stride,
                         unsigned int *host_flag = nullptr, unsigned int flag_value = 0) {
-    const int max_tiles = ((max_nr + TH - 1) / TH) * ((max_nc + TW - 1) / TW);
+    // tile height: 32-row tiles once they alone give every SM a block, else 8-row tiles (latency regime)
+    const long long tiles32 = (long long)n_jobs * ((max_nr + 31) / 32) * ((max_nc + TW - 1) / TW);
+    int th = tiles32 >= (long long)h->num_sms ? 32 : 8;
+    if (const char *e = getenv("TAMOLS_TILE_ROWS")) th = atoi(e) == 32 ? 32 : 8;
+    const int max_tiles = ((max_nr + th - 1) / th) * ((max_nc + TW - 1) / TW);
     const size_t need = (size_t)n_jobs * max_tiles;
     if (need > h->partial_cap) {
         if (h->d_partials) {
@@ -561,15 +620,17 @@ static int launch_score(tamols_handle *h, const void *d_heights, int dtype, int 
     a.scores_stride = scores_stride; a.partials = h->d_partials; a.tickets = h->d_tickets;
     a.rows = rows; a.cols = cols; a.pitch = pitch; a.max_tiles = max_tiles;
     a.jobs_done = h->d_tickets + h->max_jobs; a.host_flag = host_flag; a.flag_value = flag_value; a.n_jobs = n_jobs;
-    const bool tma = get_tensor_map(h, d_heights, dtype, maps, rows, cols, pitch);
+    const bool tma = get_tensor_map(h, d_heights, dtype, maps, rows, cols, pitch, th);
     const dim3 grid(max_tiles, n_jobs);
+#define TAMOLS_LAUNCH(HT, TMA, TH_) k_tamols_score<HT, TMA, TH_><<<grid, THREADS, 0, h->stream>>>(h->tmap, a)
     if (dtype == TAMOLS_F64) {
-        if (tma) k_tamols_score<double, true><<<grid, THREADS, 0, h->stream>>>(h->tmap, a);
-        else k_tamols_score<double, false><<<grid, THREADS, 0, h->stream>>>(h->tmap, a);
+        if (th == 32) { if (tma) TAMOLS_LAUNCH(double, true, 32); else TAMOLS_LAUNCH(double, false, 32); }
+        else { if (tma) TAMOLS_LAUNCH(double, true, 8); else TAMOLS_LAUNCH(double, false, 8); }
     } else {
-        if (tma) k_tamols_score<float, true><<<grid, THREADS, 0, h->stream>>>(h->tmap, a);
-        else k_tamols_score<float, false><<<grid, THREADS, 0, h->stream>>>(h->tmap, a);
+        if (th == 32) { if (tma) TAMOLS_LAUNCH(float, true, 32); else TAMOLS_LAUNCH(float, false, 32); }
+        else { if (tma) TAMOLS_LAUNCH(float, true, 8); else TAMOLS_LAUNCH(float, false, 8); }
     }
+#undef TAMOLS_LAUNCH
     TCU(cudaGetLastError());
     h->launches += 1;
     return TAMOLS_OK;

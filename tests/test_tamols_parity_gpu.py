@@ -16,6 +16,16 @@ from tests.util import check_tamols_against_reference, load_tamols_fixture, tamo
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(params=["auto", "8", "32"], autouse=True)
+def tile_rows(request, monkeypatch):
+    """Both tile shapes of k_tamols_score at every size (the library otherwise picks by launch size)."""
+    if request.param == "auto":
+        monkeypatch.delenv("TAMOLS_TILE_ROWS", raising=False)
+    else:
+        monkeypatch.setenv("TAMOLS_TILE_ROWS", request.param)
+    return request.param
+
+
 @pytest.fixture(scope="module")
 def tc():
     import torch
