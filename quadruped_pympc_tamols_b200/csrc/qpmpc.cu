@@ -45,9 +45,33 @@ struct SolveArgs {
     int nblk;         // rollout blocks per robot
     int robot_offset; // global id of robot 0 of this launch (Philox subsequence = robot_offset + r)
     int fused;        // 1: the last rollout block of a robot runs finalize_robot itself (one launch per solve)
+    int inline_in;    // 1: the eight input pointers above hold BYTE OFFSETS into the kernel's InlineIn parameter
 };
 typedef SolveArgs RolloutArgs;
 typedef SolveArgs FinalizeArgs;
+
+// qpmpc_solve's ~1 KB of inputs (state | reference | contact | best | sigma | timing | nominal | oswing) ride in the
+// kernel parameter block instead of a separate H2D copy: one command on the stream, no copy-engine -> compute
+// dependency in front of the kernel.  Batched launches pass device pointers and ignore this block.
+constexpr int INLINE_FLOATS = 608;
+struct InlineIn {
+    float v[INLINE_FLOATS];
+};
+__device__ __forceinline__ SolveArgs resolve_inputs(const SolveArgs &a_, const InlineIn &in) {
+    SolveArgs a = a_;
+    if (a.inline_in) {
+        const char *base = reinterpret_cast<const char *>(in.v);
+        a.state = reinterpret_cast<const float *>(base + reinterpret_cast<size_t>(a_.state));
+        a.reference = reinterpret_cast<const float *>(base + reinterpret_cast<size_t>(a_.reference));
+        a.contact = reinterpret_cast<const float *>(base + reinterpret_cast<size_t>(a_.contact));
+        a.best = reinterpret_cast<const float *>(base + reinterpret_cast<size_t>(a_.best));
+        a.sigma = reinterpret_cast<const float *>(base + reinterpret_cast<size_t>(a_.sigma));
+        a.timing = reinterpret_cast<const float *>(base + reinterpret_cast<size_t>(a_.timing));
+        a.nominal = reinterpret_cast<const float *>(base + reinterpret_cast<size_t>(a_.nominal));
+        a.oswing = reinterpret_cast<const int32_t *>(base + reinterpret_cast<size_t>(a_.oswing));
+    }
+    return a;
+}
 
 // ---------------------------------------------------------------- noise ------------------------------------
 // additional_random_parameters[i, 4g..4g+3] (sigma applied) for robot `robot`:
@@ -397,7 +421,9 @@ __device__ void finalize_robot(const DevCfg &c, const FinalizeArgs &a, const int
     }
 }
 
-__global__ void __launch_bounds__(FIN_THREADS_MAX) k_finalize(const __grid_constant__ DevCfg c, const FinalizeArgs a) {
+__global__ void __launch_bounds__(FIN_THREADS_MAX) k_finalize(const __grid_constant__ DevCfg c, const FinalizeArgs a_,
+                                                              const __grid_constant__ InlineIn in) {
+    const FinalizeArgs a = resolve_inputs(a_, in);
     extern __shared__ float smem[];
     finalize_robot(c, a, blockIdx.x, smem);
 }
@@ -460,7 +486,9 @@ __device__ __forceinline__ void weighted_rows(const float *s_par, float *s_w, un
 }
 
 template <int PARAM, bool GA, int T>
-__global__ void __launch_bounds__(T, T == 128 ? 3 : 1) k_rollout(const __grid_constant__ DevCfg c, const RolloutArgs a) {
+__global__ void __launch_bounds__(T, T == 128 ? 3 : 1) k_rollout(const __grid_constant__ DevCfg c, const RolloutArgs a_,
+                                                                  const __grid_constant__ InlineIn in) {
+    const RolloutArgs a = resolve_inputs(a_, in);
     extern __shared__ __align__(16) float smem[];
     constexpr int STRIDE = T + 1;
     const int P = c.P, H = c.H, t = threadIdx.x;
@@ -582,7 +610,7 @@ __global__ void __launch_bounds__(T, T == 128 ? 3 : 1) k_rollout(const __grid_co
         // finalize_robot turns sum_b scale_b V_b / sum_b scale_b sw_b into the updated parameters
         weighted_rows<STRIDE>(s_par, s_w, s_live, s_red, w, P, part);
     }
-    if (a.fused && last_block_of_robot(a.tickets + r, a.nblk)) finalize_robot(c, a, r, s_par);
+    if (a.fused && last_block_of_robot(a.tickets + r, a.nblk)) finalize_robot(c, resolve_inputs(a_, in), r, s_par);
 }
 
 // ---------------------------------------------------------------- quad rollout kernel (latency regime) ------
@@ -609,7 +637,9 @@ __device__ __forceinline__ float quad_sum(float v) {
 }
 
 template <int PARAM, bool GA, int QB>
-__global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__ DevCfg c, const RolloutArgs a) {
+__global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__ DevCfg c, const RolloutArgs a_,
+                                                       const __grid_constant__ InlineIn in) {
+    const RolloutArgs a = resolve_inputs(a_, in);
     extern __shared__ __align__(16) float smem[];
 #ifdef QPMPC_TIMING
     unsigned long long g0_;
@@ -870,7 +900,7 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g1_));
     if (a.fused && last_block_of_robot(a.tickets + r, a.nblk)) {
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g2_));
-        finalize_robot(c, a, r, s_par);
+        finalize_robot(c, resolve_inputs(a_, in), r, s_par);
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g3_));
         if (t == 0) {
             a.result[r].footholds[6] = (float)(g1_ - g0_);
@@ -879,7 +909,7 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
         }
     }
 #else
-    if (a.fused && last_block_of_robot(a.tickets + r, a.nblk)) finalize_robot(c, a, r, s_par);
+    if (a.fused && last_block_of_robot(a.tickets + r, a.nblk)) finalize_robot(c, resolve_inputs(a_, in), r, s_par);
 #endif
 }
 
@@ -913,7 +943,7 @@ static int fail(int code, const std::string &msg) {
             return fail(QPMPC_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));               \
     } while (0)
 
-typedef void (*rollout_fn)(const qp::DevCfg, const qp::RolloutArgs);
+typedef void (*rollout_fn)(const qp::DevCfg, const qp::RolloutArgs, const qp::InlineIn);
 
 struct qpmpc_handle {
     qpmpc_config cfg;
@@ -921,7 +951,7 @@ struct qpmpc_handle {
     int device;
     cudaStream_t stream;
     int num_sms;
-    rollout_fn fn128, fn32, fn_quad32, fn_quad128;
+    rollout_fn fn128, fn32, fn_quad32, fn_quad72, fn_quad128;
     size_t max_smem;
     // single-robot staging: one pinned input block, one pinned output block
     float *h_in, *d_in;
@@ -1004,8 +1034,10 @@ static LaunchPlan plan_launch(const qpmpc_handle *h, int n, long long total_roll
     if (!strcmp(kernel_override(), "quad")) pl.quad = true;
     if (!strcmp(kernel_override(), "thread")) pl.quad = false;
     // rollouts per quad block: 128 keeps the number of partials the last block merges small; 32 spreads a small solve
-    int QB = n >= 4096 ? 128 : 32;
-    if (const char *q = getenv("QPMPC_QB")) QB = atoi(q) == 128 ? 128 : 32;
+    // (72 x 4 threads = 9 warps: N = 10,000 becomes 139 blocks, one per SM in a single wave)
+    int QB = n < 4096 ? 32 : ((n + 71) / 72 <= h->num_sms ? 72 : 128);
+    if (const char *q = getenv("QPMPC_QB")) QB = atoi(q) == 128 ? 128 : atoi(q) == 72 ? 72 : 32;
+    if (pl.quad && QB == 72 && (size_t)quad_smem_floats(d.P, d.H, 72) * 4 > h->max_smem) QB = 32;
     if (pl.quad && QB == 128 && (size_t)quad_smem_floats(d.P, d.H, 128) * 4 > h->max_smem) QB = 32;
     if (pl.quad && (size_t)quad_smem_floats(d.P, d.H, QB) * 4 > h->max_smem) pl.quad = false;
     if (pl.quad) {
@@ -1022,7 +1054,7 @@ static LaunchPlan plan_launch(const qpmpc_handle *h, int n, long long total_roll
 }
 
 static rollout_fn pick_fn(const qpmpc_handle *h, const LaunchPlan &pl) {
-    if (pl.quad) return pl.T == 512 ? h->fn_quad128 : h->fn_quad32;
+    if (pl.quad) return pl.T == 512 ? h->fn_quad128 : pl.T == 288 ? h->fn_quad72 : h->fn_quad32;
     return pl.T == 128 ? h->fn128 : h->fn32;
 }
 
@@ -1091,16 +1123,17 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     h->fn128 = pick_rollout<128>(d.param, d.ga);
     h->fn32 = pick_rollout<32>(d.param, d.ga);
     h->fn_quad32 = pick_quad<32>(d.param, d.ga);
+    h->fn_quad72 = pick_quad<72>(d.param, d.ga);
     h->fn_quad128 = pick_quad<128>(d.param, d.ga);
     cudaError_t e = cudaSuccess;
     size_t static_smem = 0;  // the kernels' own __shared__ variables come out of the same per-block budget
-    for (rollout_fn f : {h->fn128, h->fn32, h->fn_quad32, h->fn_quad128}) {
+    for (rollout_fn f : {h->fn128, h->fn32, h->fn_quad32, h->fn_quad72, h->fn_quad128}) {
         cudaFuncAttributes fa;
         if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, (const void *)f);
         if (e == cudaSuccess && fa.sharedSizeBytes > static_smem) static_smem = fa.sharedSizeBytes;
     }
     h->max_smem -= static_smem;
-    for (rollout_fn f : {h->fn128, h->fn32, h->fn_quad32, h->fn_quad128})
+    for (rollout_fn f : {h->fn128, h->fn32, h->fn_quad32, h->fn_quad72, h->fn_quad128})
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute((const void *)f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_smem);
     if (e != cudaSuccess) { delete h; return fail(QPMPC_E_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e)); }
@@ -1155,8 +1188,11 @@ extern "C" void *qpmpc_stream(qpmpc_handle *h) { return h ? (void *)h->stream : 
 extern "C" int64_t qpmpc_launch_count(const qpmpc_handle *h) { return h ? h->launches : 0; }
 
 // launches k_rollout + k_finalize for `b` on the handle's stream (no synchronisation)
+static const InlineIn g_no_inline = {};
+
 static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, uint64_t offset,
-                        unsigned int *done_flag = nullptr, unsigned int done_value = 0) {
+                        unsigned int *done_flag = nullptr, unsigned int done_value = 0,
+                        const InlineIn *inl = nullptr) {
     const DevCfg &d = h->dc;
     const int R = b.num_robots, N = d.N, P = d.P;
     const LaunchPlan pl = plan_launch(h, N, (long long)N * R);
@@ -1171,6 +1207,8 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
     ra.result = b.d_result; ra.best_out = b.d_best_out; ra.sigma_out = b.d_sigma_out; ra.tickets = h->d_tickets;
     ra.key = NoiseKey{seed, offset}; ra.n = N; ra.costs_only = 0; ra.nblk = nblk; ra.robot_offset = b.robot_offset;
     ra.done_flag = done_flag; ra.done_value = done_value;
+    ra.inline_in = inl ? 1 : 0;  // the caller then filled the input pointers of `b` with byte offsets
+    const InlineIn &in = inl ? *inl : g_no_inline;
     // One launch per solve: the last rollout block of each robot runs the finalize step in the shared memory its
     // parameter columns occupied.  Falls back to the stand-alone k_finalize when that scratch is too small
     // (huge N with tiny P) or when QPMPC_FUSED=0 asks for the two-kernel path (tests cover both).
@@ -1179,7 +1217,7 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
     const char *fe = getenv("QPMPC_FUSED");
     ra.fused = finalize_smem_floats(P, nblk, K, pl.T) <= scratch && !(fe && fe[0] == '0');
     if (h->profiling) CU(cudaEventRecord(h->ev[0], h->stream));
-    pick_fn(h, pl)<<<dim3(nblk, R), pl.T, pl.smem, h->stream>>>(d, ra);
+    pick_fn(h, pl)<<<dim3(nblk, R), pl.T, pl.smem, h->stream>>>(d, ra, in);
     CU(cudaGetLastError());
     if (h->profiling) CU(cudaEventRecord(h->ev[1], h->stream));
     h->launches += 1;
@@ -1187,7 +1225,7 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
         // one block per robot: 512 threads when there are many rollout blocks to merge (single robot), 128 otherwise
         const int fin_threads = nblk > 16 ? FIN_THREADS_MAX : 128;
         const size_t fsmem = (size_t)finalize_smem_floats(P, nblk, K, fin_threads) * 4;
-        k_finalize<<<R, fin_threads, fsmem, h->stream>>>(d, ra);
+        k_finalize<<<R, fin_threads, fsmem, h->stream>>>(d, ra, in);
         CU(cudaGetLastError());
         h->launches += 1;
     }
@@ -1221,19 +1259,26 @@ extern "C" int qpmpc_solve(qpmpc_handle *h, const float *state, const float *ref
     if (d.method == QPMPC_METHOD_CEM && !sigma_in) return fail(QPMPC_E_ARG, "cem_mppi needs sigma_in");
     if (d.ga && !timing) return fail(QPMPC_E_ARG, "gait adaptive needs timing");
     CU(cudaSetDevice(h->device));
-    // Default I/O: the ~1 KB of inputs goes down as ONE H2D copy from pinned memory; the finalize step stores the
-    // results straight into a mapped pinned block and raises a flag there that the host spins on -- no D2H copy
-    // command and no stream-synchronise wake-up on the critical path (measured e2e p50 47 us against 55 us with
-    // H2D + D2H + cudaStreamSynchronize).  QPMPC_ZEROCOPY=0 selects that classic path; QPMPC_ZEROCOPY=1 also maps the
-    // INPUTS (every block then reads them over PCIe: 74 us, kept only as the measured negative result).
+    // Default I/O: the ~1 KB of inputs rides in the kernel's parameter block (InlineIn) and the finalize step stores the
+    // results straight into a mapped pinned block and raises a flag there that the host spins on -- ONE command on
+    // the stream, no copy commands and no stream-synchronise wake-up on the critical path.
+    //   QPMPC_INPUTS=copy    one H2D copy from pinned memory in front of the kernel (also used when the inputs do not
+    //                        fit the parameter block);   QPMPC_INPUTS=mapped   the kernel reads the inputs over PCIe
+    //                        (every block does: slowest, kept as the measured negative result)
+    //   QPMPC_ZEROCOPY=0     classic H2D + kernel + D2H + cudaStreamSynchronize
     const char *zc = getenv("QPMPC_ZEROCOPY");
+    const char *im = getenv("QPMPC_INPUTS");
     const bool zero_copy = !(zc && zc[0] == '0');
-    const bool mapped_in = zero_copy && zc && zc[0] == '1';  // inputs read over PCIe by the kernel (slower, kept for A/B)
+    const bool mapped_in = zero_copy && ((zc && zc[0] == '1') || (im && !strcmp(im, "mapped")));
+    const bool inline_in = !mapped_in && h->in_floats <= (size_t)INLINE_FLOATS && !(im && !strcmp(im, "copy")) &&
+                           !(zc && zc[0] == '0');
     const size_t o_state = 0, o_ref = 24, o_contact = 48, o_best = o_contact + 4 * H, o_sigma = o_best + P,
                  o_timing = o_sigma + P, o_nominal = o_timing + 4, o_oswing = o_nominal + 1;
     const size_t res_floats = sizeof(qpmpc_result) / 4;
-    float *p = mapped_in ? h->m_io : h->h_in;            // host view of the input block
-    float *din = mapped_in ? h->md_io : h->d_in;          // device view of the input block
+    InlineIn inl;
+    float *p = inline_in ? inl.v : mapped_in ? h->m_io : h->h_in;  // host view of the input block
+    // device view of the input block (byte offsets into the parameter block when the inputs ride inline)
+    float *din = inline_in ? static_cast<float *>(nullptr) : mapped_in ? h->md_io : h->d_in;
     float *hout = zero_copy ? h->m_io + h->in_floats : h->h_out;
     float *dout = zero_copy ? h->md_io + h->in_floats : h->d_out;
     memcpy(p + o_state, state, 24 * 4);
@@ -1244,7 +1289,8 @@ extern "C" int qpmpc_solve(qpmpc_handle *h, const float *state, const float *ref
     if (timing) memcpy(p + o_timing, timing, 16); else memset(p + o_timing, 0, 16);
     p[o_nominal] = nominal_step_frequency;
     memcpy(p + o_oswing, &optimize_swing, 4);
-    if (!mapped_in) CU(cudaMemcpyAsync(h->d_in, h->h_in, h->in_floats * 4, cudaMemcpyHostToDevice, h->stream));
+    if (!mapped_in && !inline_in)
+        CU(cudaMemcpyAsync(h->d_in, h->h_in, h->in_floats * 4, cudaMemcpyHostToDevice, h->stream));
     qpmpc_batch b;
     memset(&b, 0, sizeof b);
     b.num_robots = 1;
@@ -1259,7 +1305,8 @@ extern "C" int qpmpc_solve(qpmpc_handle *h, const float *state, const float *ref
     if (zero_copy) {
         volatile unsigned int *flag = reinterpret_cast<volatile unsigned int *>(h->m_io + h->in_floats + h->out_floats);
         const unsigned int seq = ++h->seq;
-        int rc = launch_solve(h, b, seed, offset, reinterpret_cast<unsigned int *>(h->md_io + h->in_floats + h->out_floats), seq);
+        int rc = launch_solve(h, b, seed, offset, reinterpret_cast<unsigned int *>(h->md_io + h->in_floats + h->out_floats), seq,
+                              inline_in ? &inl : nullptr);
         if (rc) return rc;
         if (costs_out) {  // 4 N bytes: a regular copy behind the kernel; its completion also implies the flag
             CU(cudaMemcpyAsync(h->h_out + h->out_floats, h->d_costs, (size_t)N * 4, cudaMemcpyDeviceToHost, h->stream));
@@ -1301,20 +1348,26 @@ extern "C" int qpmpc_rollout_costs(qpmpc_handle *h, const float *state, const fl
     if (d.ga && (!timing || !d_freqs)) return fail(QPMPC_E_ARG, "gait adaptive needs timing and d_freqs");
     CU(cudaSetDevice(h->device));
     const int H = d.H, P = d.P;
-    float *p = h->h_in;
+    const bool inline_in = h->in_floats <= (size_t)INLINE_FLOATS;
+    InlineIn inl;
+    float *p = inline_in ? inl.v : h->h_in;
+    float *din = inline_in ? static_cast<float *>(nullptr) : h->d_in;
     memcpy(p, state, 24 * 4);
     memcpy(p + 24, reference, 24 * 4);
     memcpy(p + 48, contact_sequence, (size_t)4 * H * 4);
     const size_t o_timing = 48 + 4 * H + 2 * P;
     if (timing) memcpy(p + o_timing, timing, 16); else memset(p + o_timing, 0, 16);
-    CU(cudaMemcpyAsync(h->d_in, h->h_in, h->in_floats * 4, cudaMemcpyHostToDevice, h->stream));
+    if (!inline_in) CU(cudaMemcpyAsync(h->d_in, h->h_in, h->in_floats * 4, cudaMemcpyHostToDevice, h->stream));
     RolloutArgs ra;
     memset(&ra, 0, sizeof ra);
-    ra.state = h->d_in; ra.reference = h->d_in + 24; ra.contact = h->d_in + 48; ra.timing = h->d_in + o_timing;
+    ra.state = din; ra.reference = din + 24; ra.contact = din + 48; ra.timing = din + o_timing;
+    ra.best = din + 48 + 4 * H; ra.sigma = din + 48 + 4 * H + P;  // unused in costs-only mode; kept inside the block
+    ra.nominal = din + o_timing + 4; ra.oswing = reinterpret_cast<const int32_t *>(din + o_timing + 5);
+    ra.inline_in = inline_in ? 1 : 0;
     ra.eps = d_params; ra.freqs = d_freqs; ra.costs = d_costs; ra.n = n; ra.costs_only = 1;
     const LaunchPlan pl = plan_launch(h, n, n);
     ra.nblk = pl.nblk;
-    pick_fn(h, pl)<<<dim3(pl.nblk, 1), pl.T, pl.smem, h->stream>>>(d, ra);
+    pick_fn(h, pl)<<<dim3(pl.nblk, 1), pl.T, pl.smem, h->stream>>>(d, ra, inline_in ? inl : g_no_inline);
     CU(cudaGetLastError());
     h->launches += 1;
     CU(cudaStreamSynchronize(h->stream));
