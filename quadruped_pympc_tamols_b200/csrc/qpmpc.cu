@@ -37,8 +37,11 @@ struct SolveArgs {
     qpmpc_result *result;
     float *best_out, *sigma_out;
     unsigned int *tickets;  // [robots] arrival counters of the fused finalize (zero between launches)
-    unsigned int *done_flag;  // mapped host word the finalize step of robot 0 stores done_value to (or NULL)
-    unsigned int done_value;
+    // host-buffer solve (one robot): mapped host block the finalize step stores {word, ll_seq} pairs into, 8 bytes
+    // per store (result record | best_out | sigma_out).  Every pair carries its own arrival flag, so no system-wide
+    // fence and no separate done flag are needed: the host waits until each pair shows the current sequence number.
+    uint2 *ll_out;
+    unsigned int ll_seq;
     NoiseKey key;
     int n;            // rollouts per robot in this launch
     int costs_only;   // 1: jit_vectorized_rollout semantics (eps = parameters, no saturation, no partials)
@@ -130,6 +133,31 @@ __device__ __forceinline__ float4 noise_group_row(const RowNoise &rn, const Nois
     if (rn.mode == 0) return z;
     return make_float4(__fmul_rn(z.x, sigma_vec[4 * g]), __fmul_rn(z.y, sigma_vec[4 * g + 1]),
                        __fmul_rn(z.z, sigma_vec[4 * g + 2]), __fmul_rn(z.w, sigma_vec[4 * g + 3]));
+}
+
+// groups ga and gb of the same row under ONE control flow, so that the two Philox blocks and the two Box-Muller
+// chains interleave (same values as two noise_group_row calls)
+__device__ __forceinline__ void noise_group_row2(const RowNoise &rn, const NoiseKey &nk, const float *sigma_vec, int ga,
+                                                 int gb, uint32_t robot, float4 &ea, float4 &eb) {
+    ea = eb = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (rn.mode == 3) return;
+    const uint4 xa = draw(nk, rn.stream, ga, rn.sample, robot);
+    const uint4 xb = draw(nk, rn.stream, gb, rn.sample, robot);
+    if (rn.mode == 1) {
+        const float a = rn.k, w = __fmul_rn(2.0f, a);
+        ea = make_float4(__fmaf_rn(u01_half_open(xa.x), w, -a), __fmaf_rn(u01_half_open(xa.y), w, -a),
+                         __fmaf_rn(u01_half_open(xa.z), w, -a), __fmaf_rn(u01_half_open(xa.w), w, -a));
+        eb = make_float4(__fmaf_rn(u01_half_open(xb.x), w, -a), __fmaf_rn(u01_half_open(xb.y), w, -a),
+                         __fmaf_rn(u01_half_open(xb.z), w, -a), __fmaf_rn(u01_half_open(xb.w), w, -a));
+        return;
+    }
+    ea = normal4_scaled(xa, rn.k);
+    eb = normal4_scaled(xb, rn.k);
+    if (rn.mode == 0) return;
+    ea = make_float4(__fmul_rn(ea.x, sigma_vec[4 * ga]), __fmul_rn(ea.y, sigma_vec[4 * ga + 1]),
+                     __fmul_rn(ea.z, sigma_vec[4 * ga + 2]), __fmul_rn(ea.w, sigma_vec[4 * ga + 3]));
+    eb = make_float4(__fmul_rn(eb.x, sigma_vec[4 * gb]), __fmul_rn(eb.y, sigma_vec[4 * gb + 1]),
+                     __fmul_rn(eb.z, sigma_vec[4 * gb + 2]), __fmul_rn(eb.w, sigma_vec[4 * gb + 3]));
 }
 
 __device__ __forceinline__ float4 noise_group(const DevCfg &c, const NoiseKey &nk, const float *sigma_vec, int i,
@@ -232,7 +260,7 @@ __device__ void grf_and_prediction(const DevCfg &c, const float *s_best, const f
 // Partials and costs were written by other blocks: they are read through L2 (ld.global.cg).
 __host__ __device__ inline int finalize_smem_floats(int P, int nblk, int cem_elite, int threads) {
     const int G = threads / (P / 4) > 1 ? threads / (P / 4) : 1;
-    return G * P + P + 64 + 3 * nblk + 1 + cem_elite + 8;
+    return G * P + P + 64 + 3 * nblk + 1 + cem_elite + (int)(sizeof(qpmpc_result) / 4) + 8;
 }
 
 #ifdef QPMPC_TIMING
@@ -246,7 +274,7 @@ __device__ void finalize_robot(const DevCfg &c, const FinalizeArgs &a, const int
     unsigned long long tick_[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 #endif
     QP_TICK(0);
-    // scratch: acc[G][P] | best[P] | red[64] | sc[nblk] | sw[nblk] | lb[nblk + 1] | sel[cem_elite]
+    // scratch: acc[G][P] | best[P] | red[64] | sc[nblk] | sw[nblk] | lb[nblk + 1] | sel[cem_elite] | result record
     const int G_ = max(1, (int)blockDim.x / (P >> 2));
     float *s_acc = smem;
     float *s_best = s_acc + G_ * P;
@@ -255,6 +283,7 @@ __device__ void finalize_robot(const DevCfg &c, const FinalizeArgs &a, const int
     float *s_sw = s_sc + a.nblk;
     int *s_lb = reinterpret_cast<int *>(s_sw + a.nblk);
     int *s_sel = s_lb + a.nblk + 1;
+    qpmpc_result *s_res = reinterpret_cast<qpmpc_result *>(s_sel + (c.method == QPMPC_METHOD_CEM ? c.cem_elite : 0));
     __syncthreads();  // fused call: every thread is done with the columns this scratch overlays
     const float *part = a.partials + (size_t)r * a.nblk * (PART_HDR + P);
     const int stride = PART_HDR + P;
@@ -318,15 +347,29 @@ __device__ void finalize_robot(const DevCfg &c, const FinalizeArgs &a, const int
         for (int q = t; q < G * P4; q += blockDim.x) {
             const int g = q / P4, p4 = q - g * P4;
             float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 16
-            for (int k = g; k < nlive; k += G) {
-                const int b = s_lb[k];
-                const float sc = s_sc[b];
-                const float4 v = __ldcg(reinterpret_cast<const float4 *>(part + (size_t)b * stride + PART_HDR) + p4);
-                acc.x = fmaf(sc, v.x, acc.x);
-                acc.y = fmaf(sc, v.y, acc.y);
-                acc.z = fmaf(sc, v.z, acc.z);
-                acc.w = fmaf(sc, v.w, acc.w);
+            // fixed batches of MB predicated loads: a short row list must not fall into a one-load-at-a-time
+            // remainder loop (12 rows per group at 139 blocks = 12 serial L2 round trips, 4.5 us, before this)
+            constexpr int MB = 12;
+            for (int k0 = g; k0 < nlive; k0 += MB * G) {
+                float4 v[MB];
+                float sc[MB];
+#pragma unroll
+                for (int j = 0; j < MB; ++j) {
+                    const int k = k0 + j * G;
+                    const bool ok = k < nlive;
+                    const int b = s_lb[ok ? k : 0];
+                    sc[j] = ok ? s_sc[b] : 0.f;
+                    v[j] = __ldcg(reinterpret_cast<const float4 *>(part + (size_t)b * stride + PART_HDR) + p4);
+                }
+#pragma unroll
+                for (int j = 0; j < MB; ++j) {  // ascending row order within the group, as before
+                    if (k0 + j * G < nlive) {
+                        acc.x = fmaf(sc[j], v[j].x, acc.x);
+                        acc.y = fmaf(sc[j], v[j].y, acc.y);
+                        acc.z = fmaf(sc[j], v[j].z, acc.z);
+                        acc.w = fmaf(sc[j], v[j].w, acc.w);
+                    }
+                }
             }
             *reinterpret_cast<float4 *>(s_acc + g * P + 4 * p4) = acc;
         }
@@ -337,33 +380,56 @@ __device__ void finalize_robot(const DevCfg &c, const FinalizeArgs &a, const int
             s_best[p] = num / den;
         }
     }
-    __syncthreads();
-    QP_TICK(3);
-    for (int p = t; p < P; p += blockDim.x) a.best_out[(size_t)r * P + p] = s_best[p];
-
-    qpmpc_result *out = a.result + r;
-    if (t == 0) {
-        out->best_cost = bc;
-        out->best_index = bi;
-        out->reserved = 0;
+    // best rollout's step frequency: one lane of the last warp, off thread 0's critical path
+    if (t == (int)blockDim.x - 1) {
         float bf;
         if (c.ga)
             bf = a.freqs ? a.freqs[(size_t)r * N + bi] : freq_sample(c, a.key, bi, robot, a.nominal[r], a.oswing[r]);
         else
             bf = (c.method == QPMPC_METHOD_CEM) ? 1.65f : 1.4f;  // centroidal_nmpc_jax.py:786,930,1083
-        out->best_freq = bf;
+        s_res->best_freq = bf;
+    }
+    __syncthreads();
+    QP_TICK(3);
+    constexpr int RW = (int)(sizeof(qpmpc_result) / 4);
+    const bool ll = a.ll_out != nullptr && r == 0;
+    auto ll_store = [&](int k, float v) {
+        uint2 w = make_uint2(__float_as_uint(v), a.ll_seq);
+        asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(a.ll_out + k), "r"(w.x), "r"(w.y) : "memory");
+    };
+    for (int p = t; p < P; p += blockDim.x) {
+        if (ll) ll_store(RW + p, s_best[p]);
+        else a.best_out[(size_t)r * P + p] = s_best[p];
+    }
+
+    // first GRFs and one-step prediction from the new mean: thread 0 fills a shared-memory copy of the result
+    // record, then one warp-wide store moves it out (the record may live in mapped host memory: two 128-byte
+    // bursts instead of fifty 4-byte stores from one thread)
+    if (t == 0) {
+        s_res->best_cost = bc;
+        s_res->best_index = bi;
+        s_res->reserved = 0;
         const float *state = a.state + r * 24;
         const float *contact = a.contact + (size_t)r * 4 * c.H;
         if (c.param == QPMPC_PARAM_ZERO_ORDER)
-            grf_and_prediction<QPMPC_PARAM_ZERO_ORDER>(c, s_best, state, contact, out);
+            grf_and_prediction<QPMPC_PARAM_ZERO_ORDER>(c, s_best, state, contact, s_res);
         else if (c.param == QPMPC_PARAM_LINEAR)
-            grf_and_prediction<QPMPC_PARAM_LINEAR>(c, s_best, state, contact, out);
+            grf_and_prediction<QPMPC_PARAM_LINEAR>(c, s_best, state, contact, s_res);
         else
-            grf_and_prediction<QPMPC_PARAM_CUBIC>(c, s_best, state, contact, out);
+            grf_and_prediction<QPMPC_PARAM_CUBIC>(c, s_best, state, contact, s_res);
         QP_TICK(4);
 #ifdef QPMPC_TIMING
-        for (int k = 1; k < 5; ++k) out->footholds[k] = (float)(tick_[k] - tick_[k - 1]);
+        for (int k = 1; k < 5; ++k) s_res->footholds[k] = (float)(tick_[k] - tick_[k - 1]);
 #endif
+    }
+    __syncthreads();
+    {
+        float *dst = reinterpret_cast<float *>(a.result + r);
+        for (int k = t; k < RW; k += blockDim.x) {
+            const float v = reinterpret_cast<const float *>(s_res)[k];
+            if (ll) ll_store(k, v);
+            else dst[k] = v;
+        }
     }
 
     if (c.method == QPMPC_METHOD_CEM && a.sigma_out != nullptr) {
@@ -408,16 +474,11 @@ __device__ void finalize_robot(const DevCfg &c, const FinalizeArgs &a, const int
                 if (c.cem_sqrt) v = sqrtf(v);
                 v = v > c.cem_hi ? c.cem_hi : v;
                 v = v < c.cem_lo ? c.cem_lo : v;
-                a.sigma_out[(size_t)r * P + p] = v;
+                if (ll) ll_store(RW + P + p, v);
+                else a.sigma_out[(size_t)r * P + p] = v;
             }
         }
     }
-    }
-    // host-buffer solve: results live in mapped host memory; publish them system-wide, then raise the host's flag
-    if (a.done_flag != nullptr && r == 0) {
-        __threadfence_system();
-        __syncthreads();
-        if (t == 0) *reinterpret_cast<volatile unsigned int *>(a.done_flag) = a.done_value;
     }
 }
 
@@ -687,6 +748,10 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
         if (t >= 96 && t < 100) s_timing[t - 96] = a.timing[r * 4 + t - 96];
     }
     __syncthreads();
+#ifdef QPMPC_TIMING
+    unsigned long long gs_, gn_, gl_;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gs_));
+#endif
 
     // ---- parameters of the block's 32 rollouts -> columns of s_par; lane `leg` draws groups leg, leg + 4, ...
     const uint32_t robot = (uint32_t)(r + a.robot_offset);
@@ -700,22 +765,37 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
         __syncthreads();
     } else {
         const RowNoise rn = row_noise(c, valid ? i : 0);
-        for (int g = leg; g < P / 4; g += 4) {
+        // two groups per trip: their Philox rounds and Box-Muller SFU chains are independent and interleave
+        const int G4 = P / 4;
+        for (int g = leg; g < G4; g += 8) {
+            const int g2 = g + 4;
+            const bool two = g2 < G4;
             float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
-            float4 b = e;
+            float4 e2 = e, b = e, b2 = e;
             if (valid) {
-                e = noise_group_row(rn, a.key, s_sigma, g, robot);
+                noise_group_row2(rn, a.key, s_sigma, g, two ? g2 : g, robot, e, e2);
                 b = *reinterpret_cast<const float4 *>(s_best + 4 * g);
+                b2 = *reinterpret_cast<const float4 *>(s_best + 4 * (two ? g2 : g));
             }
             float *dst = s_par + (4 * g) * stride + rb;
             dst[0] = b.x + e.x;
             dst[stride] = b.y + e.y;
             dst[2 * stride] = b.z + e.z;
             dst[3 * stride] = b.w + e.w;
+            if (two) {
+                dst += 16 * stride;
+                dst[0] = b2.x + e2.x;
+                dst[stride] = b2.y + e2.y;
+                dst[2 * stride] = b2.z + e2.z;
+                dst[3 * stride] = b2.w + e2.w;
+            }
         }
         __syncwarp();
     }
 
+#ifdef QPMPC_TIMING
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gn_));
+#endif
     // ---- rollout: lane = leg
     float x[12], ref[12];
 #pragma unroll
@@ -843,6 +923,9 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
         cost += (eb * qb) * eb;
         cost += (ec * qc) * ec;
     }
+#ifdef QPMPC_TIMING
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gl_));
+#endif
     cost = quad_sum(cost);
     if (GA) {
         const float df = freq - 1.3f;
@@ -906,6 +989,9 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
             a.result[r].footholds[6] = (float)(g1_ - g0_);
             a.result[r].footholds[7] = (float)(g2_ - g1_);
             a.result[r].footholds[8] = (float)(g3_ - g2_);
+            a.result[r].footholds[9] = (float)(gs_ - g0_);
+            a.result[r].footholds[10] = (float)(gn_ - gs_);
+            a.result[r].footholds[11] = (float)(gl_ - gn_);
         }
     }
 #else
@@ -956,7 +1042,7 @@ struct qpmpc_handle {
     // single-robot staging: one pinned input block, one pinned output block
     float *h_in, *d_in;
     float *h_out, *d_out;
-    float *m_io, *md_io;  // mapped (zero-copy) host block of qpmpc_solve: inputs | outputs | done flag
+    float *m_io, *md_io;  // mapped (zero-copy) host block of qpmpc_solve: inputs | {word, seq} output pairs
     unsigned int seq;     // value the next solve stores to the done flag
     size_t in_floats, out_floats;
     float *d_costs;     // [max_robots * N]
@@ -1148,7 +1234,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
               cudaEventCreate(&h->ev[2]) == cudaSuccess &&
               cudaMallocHost(&h->h_in, h->in_floats * 4) == cudaSuccess &&
               cudaMallocHost(&h->h_out, h->out_floats * 4 + (size_t)d.N * 4) == cudaSuccess &&
-              cudaHostAlloc(&h->m_io, (h->in_floats + h->out_floats + 16) * 4, cudaHostAllocMapped) == cudaSuccess &&
+              cudaHostAlloc(&h->m_io, (h->in_floats + 2 * h->out_floats + 16) * 4, cudaHostAllocMapped) == cudaSuccess &&
               cudaHostGetDevicePointer(&h->md_io, h->m_io, 0) == cudaSuccess &&
               cudaMalloc(&h->d_in, h->in_floats * 4) == cudaSuccess &&
               cudaMalloc(&h->d_out, h->out_floats * 4) == cudaSuccess &&
@@ -1161,6 +1247,8 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
         qpmpc_destroy(h);
         return fail(QPMPC_E_CUDA, m);
     }
+    memset(h->m_io, 0, (h->in_floats + 2 * h->out_floats + 16) * 4);  // sequence number 0 = nothing published yet
+    h->seq = 0;
     *out = h;
     return QPMPC_OK;
 }
@@ -1191,7 +1279,7 @@ extern "C" int64_t qpmpc_launch_count(const qpmpc_handle *h) { return h ? h->lau
 static const InlineIn g_no_inline = {};
 
 static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, uint64_t offset,
-                        unsigned int *done_flag = nullptr, unsigned int done_value = 0,
+                        uint2 *ll_out = nullptr, unsigned int ll_seq = 0,
                         const InlineIn *inl = nullptr) {
     const DevCfg &d = h->dc;
     const int R = b.num_robots, N = d.N, P = d.P;
@@ -1206,7 +1294,7 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
     ra.costs = b.d_costs ? b.d_costs : h->d_costs; ra.partials = h->d_partials;
     ra.result = b.d_result; ra.best_out = b.d_best_out; ra.sigma_out = b.d_sigma_out; ra.tickets = h->d_tickets;
     ra.key = NoiseKey{seed, offset}; ra.n = N; ra.costs_only = 0; ra.nblk = nblk; ra.robot_offset = b.robot_offset;
-    ra.done_flag = done_flag; ra.done_value = done_value;
+    ra.ll_out = ll_out; ra.ll_seq = ll_seq;
     ra.inline_in = inl ? 1 : 0;  // the caller then filled the input pointers of `b` with byte offsets
     const InlineIn &in = inl ? *inl : g_no_inline;
     // One launch per solve: the last rollout block of each robot runs the finalize step in the shared memory its
@@ -1279,8 +1367,9 @@ extern "C" int qpmpc_solve(qpmpc_handle *h, const float *state, const float *ref
     float *p = inline_in ? inl.v : mapped_in ? h->m_io : h->h_in;  // host view of the input block
     // device view of the input block (byte offsets into the parameter block when the inputs ride inline)
     float *din = inline_in ? static_cast<float *>(nullptr) : mapped_in ? h->md_io : h->d_in;
-    float *hout = zero_copy ? h->m_io + h->in_floats : h->h_out;
-    float *dout = zero_copy ? h->md_io + h->in_floats : h->d_out;
+    const size_t ll_off = (h->in_floats + 3) & ~(size_t)3;  // 16-byte aligned start of the output pairs
+    float *hout = h->h_out;
+    float *dout = h->d_out;  // unused by the kernel when the outputs go out as pairs
     memcpy(p + o_state, state, 24 * 4);
     memcpy(p + o_ref, reference, 24 * 4);
     memcpy(p + o_contact, contact_sequence, (size_t)4 * H * 4);
@@ -1303,28 +1392,32 @@ extern "C" int qpmpc_solve(qpmpc_handle *h, const float *state, const float *ref
     b.d_sigma_out = (d.method == QPMPC_METHOD_CEM) ? dout + res_floats + P : nullptr;
     b.d_costs = h->d_costs;
     if (zero_copy) {
-        volatile unsigned int *flag = reinterpret_cast<volatile unsigned int *>(h->m_io + h->in_floats + h->out_floats);
-        const unsigned int seq = ++h->seq;
-        int rc = launch_solve(h, b, seed, offset, reinterpret_cast<unsigned int *>(h->md_io + h->in_floats + h->out_floats), seq,
-                              inline_in ? &inl : nullptr);
+        volatile unsigned long long *pairs = reinterpret_cast<volatile unsigned long long *>(h->m_io + ll_off);
+        unsigned int seq = ++h->seq;
+        if (seq == 0) seq = ++h->seq;  // the block starts zeroed: 0 never names a solve
+        int rc = launch_solve(h, b, seed, offset, reinterpret_cast<uint2 *>(h->md_io + ll_off), seq, inline_in ? &inl : nullptr);
         if (rc) return rc;
-        if (costs_out) {  // 4 N bytes: a regular copy behind the kernel; its completion also implies the flag
+        if (costs_out) {  // 4 N bytes: a regular copy behind the kernel; its completion implies the pairs too
             CU(cudaMemcpyAsync(h->h_out + h->out_floats, h->d_costs, (size_t)N * 4, cudaMemcpyDeviceToHost, h->stream));
             CU(cudaStreamSynchronize(h->stream));
-        } else {
-            unsigned long long spins = 0;
-            while (*flag != seq) {
+        }
+        // wait for every {word, seq} pair of this solve and unpack the words
+        const size_t words = res_floats + P + (d.method == QPMPC_METHOD_CEM ? P : 0);
+        uint32_t *dst = reinterpret_cast<uint32_t *>(hout);
+        unsigned long long spins = 0;
+        for (size_t k = 0; k < words; ++k) {
+            unsigned long long v;
+            while ((unsigned int)((v = pairs[k]) >> 32) != seq) {
                 __builtin_ia32_pause();
                 if ((++spins & 0xFFFFF) == 0) {  // ~ms: make sure the kernel is still alive rather than spin forever
                     const cudaError_t q = cudaStreamQuery(h->stream);
-                    if (q != cudaErrorNotReady) {
-                        if (q != cudaSuccess) return fail(QPMPC_E_CUDA, std::string("solve kernel: ") + cudaGetErrorString(q));
-                        break;
-                    }
+                    if (q != cudaErrorNotReady && (unsigned int)(pairs[k] >> 32) != seq)
+                        return fail(QPMPC_E_CUDA, q != cudaSuccess ? std::string("solve kernel: ") + cudaGetErrorString(q)
+                                                                   : std::string("solve finished without publishing its results"));
                 }
             }
+            dst[k] = (uint32_t)v;
         }
-        if (*flag != seq) return fail(QPMPC_E_CUDA, "solve finished without publishing its results");
     } else {
         int rc = launch_solve(h, b, seed, offset);
         if (rc) return rc;
