@@ -611,18 +611,35 @@ __global__ void __launch_bounds__(T, T == 128 ? 3 : 1) k_rollout(const __grid_co
     } else {
         const RowNoise rn = row_noise(c, valid ? i : 0);
         float *dst = s_par + t;
-#pragma unroll 2
-        for (int g = 0; g < P / 4; ++g) {
-            float4 e = make_float4(0.f, 0.f, 0.f, 0.f), b = e;  // tail block: zero columns keep everything finite
-            if (valid) {
-                e = noise_group_row(rn, a.key, s_sigma, g, robot);
-                b = *reinterpret_cast<const float4 *>(s_best + 4 * g);
+        const int G4 = P / 4;
+        if (!valid) {  // tail block: zero columns keep everything finite
+            for (int p = 0; p < P; ++p) dst[p * STRIDE] = 0.f;
+        } else {
+            // two groups per trip under one control flow: the two Philox blocks and Box-Muller chains interleave
+            int g = 0;
+            for (; g + 1 < G4; g += 2) {
+                float4 e, e2;
+                noise_group_row2(rn, a.key, s_sigma, g, g + 1, robot, e, e2);
+                const float4 b = *reinterpret_cast<const float4 *>(s_best + 4 * g);
+                const float4 b2 = *reinterpret_cast<const float4 *>(s_best + 4 * g + 4);
+                dst[0] = b.x + e.x;
+                dst[STRIDE] = b.y + e.y;
+                dst[2 * STRIDE] = b.z + e.z;
+                dst[3 * STRIDE] = b.w + e.w;
+                dst[4 * STRIDE] = b2.x + e2.x;
+                dst[5 * STRIDE] = b2.y + e2.y;
+                dst[6 * STRIDE] = b2.z + e2.z;
+                dst[7 * STRIDE] = b2.w + e2.w;
+                dst += 8 * STRIDE;
             }
-            dst[0] = b.x + e.x;
-            dst[STRIDE] = b.y + e.y;
-            dst[2 * STRIDE] = b.z + e.z;
-            dst[3 * STRIDE] = b.w + e.w;
-            dst += 4 * STRIDE;
+            if (g < G4) {
+                const float4 e = noise_group_row(rn, a.key, s_sigma, g, robot);
+                const float4 b = *reinterpret_cast<const float4 *>(s_best + 4 * g);
+                dst[0] = b.x + e.x;
+                dst[STRIDE] = b.y + e.y;
+                dst[2 * STRIDE] = b.z + e.z;
+                dst[3 * STRIDE] = b.w + e.w;
+            }
         }
     }
 
