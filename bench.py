@@ -6,8 +6,10 @@ step-frequency adaptation, 10,000 rollouts over a 12-step horizon.  One "step" =
 
   value        rollouts/s with the inputs resident in HBM (qpmpc_solve_batched on device tensors), device-timed
                per step with CUDA events on the handle's stream; L2 is flushed between timed steps.
-  e2e          the same metric through the reference-facing call qpmpc_solve with HOST buffers: H2D copy of the
-               inputs, both kernels, D2H copy of the result, stream sync -- wall clock per call; p50 latency reported.
+  e2e          the same metric through the reference-facing call qpmpc_solve with HOST buffers, wall clock per call:
+               the inputs (1176 B) go host -> device inside the launch (kernel parameter block), the one kernel runs,
+               and its finalize step stores the results device -> host into mapped pinned memory as {word, sequence}
+               pairs the host waits on (QPMPC_ZEROCOPY=0: H2D copy + kernel + D2H copy + stream sync); p50 reported.
   roofline     k_rollout against the FP32 CUDA-core peak measured in this run (no tensor cores: nothing on this path
                is a dense contraction); algorithmic FLOPs per rollout from SURVEY.md 8(d).
   cpu_baseline the CPU oracle port (-O3, OpenMP over rollouts, all host threads) on the same workload.
@@ -230,7 +232,7 @@ def run_cuda(args):
     flop = FLOP_PER_ROLLOUT["cubic_spline_ga"] * N_ROLLOUTS
     ach = flop / (roll[:, 0].mean() * 1e-3) / 1e12
 
-    # ---- end to end through the host-buffer C ABI call (H2D + kernels + D2H + sync), wall clock
+    # ---- end to end through the host-buffer C ABI call (inputs down, one kernel, results back up), wall clock
     best = np.zeros(P, np.float32)
     e2e = []
     for it in range(W + K):
@@ -244,7 +246,7 @@ def run_cuda(args):
     e2e_total = max_over_ranks(float(e2e.sum()))
     e2e_value = N_ROLLOUTS * K * world / e2e_total
     in_bytes = 4 * (24 + 24 + 4 * 12 + 2 * P + 4 + 2)
-    out_bytes = 4 * (_cabi.RESULT_FLOATS + 2 * P)
+    out_bytes = 8 * (_cabi.RESULT_FLOATS + P)  # result record + best_out, each 4-byte word paired with its sequence number
 
     # ---- batched robots C5 (sharded by robot, no collective): extra information, not the headline
     batched = None
@@ -274,11 +276,12 @@ def run_cuda(args):
                            "multi_gpu": "one independent robot instance per rank, no collective on the control path"},
                 "e2e": {"value": e2e_value, "unit": "rollouts/s", "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": out_bytes,
                         "p50_latency_ms": float(np.median(e2e) * 1e3), "p99_latency_ms": float(np.percentile(e2e, 99) * 1e3),
-                        "api": "qpmpc_solve (host buffers; costs[N] left on the device as upstream)"},
+                        "api": "qpmpc_solve (host buffers; costs[N] left on the device as upstream)",
+                        "transfers": "inputs in the kernel parameter block (host -> device with the launch); results stored by the kernel into mapped pinned host memory as {word, sequence} pairs"},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak,
-                             "traffic": 87808, "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, profiles/r1o_ncu_raw_c2.csv (bytes)",
-                             "kernel": "k_rollout_quad<cubic,gait_adaptive,128> (rollouts + fused finalize, one launch per solve)", "launch_ms": float(roll[:, 0].mean()),
+                             "traffic": 88832, "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, profiles/r2a_ncu_raw_c2.csv (bytes)",
+                             "kernel": "k_rollout_quad<cubic,gait_adaptive,72> (139 blocks x 288 threads; rollouts + fused finalize, one launch per solve)", "launch_ms": float(roll[:, 0].mean()),
                              "finalize_ms": float(roll[:, 1].mean()), "finalize": "fused into the rollout kernel (last block per robot)", "flop_per_rollout": FLOP_PER_ROLLOUT["cubic_spline_ga"],
                              "peak_source": "FP32 FMA-chain microbenchmark in this run (qpmpc_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 figure",
                              "note": "10k rollouts = 75.5 MFLOP: latency-bound at this size; see batched.roofline for the throughput regime"},
@@ -327,7 +330,7 @@ def run_batched(torch, _cabi, dev, local_rank, rank, world, barrier, max_over_ra
             "value": robots_total * n / (step_ms * 1e-3), "unit": "rollouts/s", "robot_solves_per_s": robots_total / (step_ms * 1e-3),
             "ms_per_step": step_ms, "scaling": "strong",
             "roofline": {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak,
-                         "traffic": 31213056 // world, "traffic_source": "profiles/r1o_ncu_raw_c5.csv (bytes per launch at 8192 robots)",
+                         "traffic": 31847680 // world, "traffic_source": "profiles/r2a_ncu_raw_c5.csv (dram read + write bytes per launch at 8192 robots)",
                          "kernel": "k_rollout<zero_order,fixed,128>", "launch_ms": roll_ms, "flop_per_rollout": FLOP_PER_ROLLOUT["zero_order"]}}
 
 
@@ -409,8 +412,8 @@ def run_tamols(torch, dev, local_rank, rank, world, barrier, max_over_ranks, wit
                       "ms_per_step": step_ms, "footholds_per_s": robots_total * 4 / (step_ms * 1e-3),
                       "candidates_per_s": cand / (step_ms * 1e-3), "scaling": "strong", "gpu_launches_per_step": 1,
                       "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                                   "traffic": 32219392, "traffic_source": "profiles/r1o_ncu_raw_tamols.csv (bytes per launch: the 2048x2048 f64 map once)",
-                                   "kernel": "k_tamols_score<double,TMA>", "launch_ms": float(ms.mean()),
+                                   "traffic": 32270080, "traffic_source": "profiles/r2a_ncu_raw_tamols.csv (dram read + write bytes per launch: the 2048x2048 f64 map once)",
+                                   "kernel": "k_tamols_score<double,TMA,32-row tiles>", "launch_ms": float(ms.mean()),
                                    "algorithmic_bytes_per_candidate": 8, "peak_source": peak_src,
                                    "note": "FP64 arithmetic (about 330 FP64 instructions per feasible candidate) binds long before HBM: see DESIGN.md"}}
     out["launch_count_check"] = int(launches)

@@ -256,7 +256,7 @@ struct GridInv {
 };
 
 template <typename HT, bool USE_TMA, int TH>
-__global__ void __launch_bounds__(THREADS) k_tamols_score(const __grid_constant__ CUtensorMap tmap, const Args a) {
+__global__ void __launch_bounds__(THREADS, TH == 32 ? 4 : 2) k_tamols_score(const __grid_constant__ CUtensorMap tmap, const Args a) {
     constexpr int BH = TH + 2 * HALO, CPT = TW * TH / THREADS;
     __shared__ __align__(128) HT s_box[BH * BW];
     __shared__ __align__(8) uint64_t s_bar;
