@@ -50,9 +50,9 @@ struct Args {
     long long scores_stride;
     Partial *partials;
     unsigned int *tickets;
-    unsigned int *jobs_done;   // [1] counter of finished jobs (host-buffer call only, else NULL)
-    unsigned int *host_flag;   // mapped host word that receives flag_value once every job has written its result
-    unsigned int flag_value;
+    unsigned int *jobs_done;   // unused (kept for layout)
+    unsigned int *host_flag;   // host-buffer call: mapped host block of {word, flag_value} pairs, 22 per job (else NULL)
+    unsigned int flag_value;   // sequence number of this call
     int n_jobs;
     int rows, cols, pitch, max_tiles;
 };
@@ -416,7 +416,9 @@ __global__ void __launch_bounds__(THREADS, TH == 32 ? 4 : 2) k_tamols_score(cons
             argmin_combine(s, idx, s_rs[w], s_ri[w]);
             nfin += s_rn[w];
         }
-        tamols_result &out = a.results[job];
+        // host-buffer call: the record is built locally and leaves as {word, sequence} pairs (below)
+        tamols_result local;
+        tamols_result &out = a.host_flag != nullptr ? local : a.results[job];
         out.num_finite = nfin;
         out.best_score = s;
         double xyz[3] = {0.0, 0.0, 0.0};
@@ -441,12 +443,15 @@ __global__ void __launch_bounds__(THREADS, TH == 32 ? 4 : 2) k_tamols_score(cons
         out.vertex2[0] += a.p.constraint_box_dx;
         out.vertex2[1] += a.p.constraint_box_dy;
         a.tickets[job] = 0;  // ready for the next launch on this stream
-        if (a.host_flag != nullptr) {  // results live in mapped host memory: publish, then count this job in
-            __threadfence_system();
-            if (atomicAdd(a.jobs_done, 1u) == (unsigned)(a.n_jobs - 1)) {
-                *a.jobs_done = 0u;
-                *reinterpret_cast<volatile unsigned int *>(a.host_flag) = a.flag_value;
-            }
+        if (a.host_flag != nullptr) {
+            // Results go to mapped host memory as 8-byte {word, sequence} stores: every pair carries its own arrival
+            // flag, so neither a system-wide fence nor a job counter is needed; the host waits for each pair.
+            constexpr int RW = (int)(sizeof(tamols_result) / 4);
+            const uint32_t *w = reinterpret_cast<const uint32_t *>(&local);
+            uint2 *dst = reinterpret_cast<uint2 *>(a.host_flag) + (size_t)job * RW;
+#pragma unroll
+            for (int k = 0; k < RW; ++k)
+                asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(dst + k), "r"(w[k]), "r"(a.flag_value) : "memory");
         }
     }
 }
@@ -488,7 +493,7 @@ struct tamols_handle {
     // staging for tamols_score_host
     char *d_stage, *h_stage;
     size_t stage_cap;
-    char *m_out, *md_out;      // mapped pinned block of tamols_score_host: results | done flag
+    char *m_out, *md_out;      // mapped pinned block of tamols_score_host: {word, sequence} pairs of the results
     unsigned int seq;
 };
 
@@ -534,13 +539,15 @@ extern "C" int tamols_create(const tamols_params *params, int32_t device, int32_
     bool ok = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) == cudaSuccess &&
               cudaMalloc(&h->d_tickets, ((size_t)max_jobs + 1) * sizeof(unsigned int)) == cudaSuccess &&
               cudaMemset(h->d_tickets, 0, ((size_t)max_jobs + 1) * sizeof(unsigned int)) == cudaSuccess &&
-              cudaHostAlloc(&h->m_out, (size_t)max_jobs * sizeof(tamols_result) + 64, cudaHostAllocMapped) == cudaSuccess &&
+              cudaHostAlloc(&h->m_out, 2 * (size_t)max_jobs * sizeof(tamols_result) + 64, cudaHostAllocMapped) == cudaSuccess &&
               cudaHostGetDevicePointer(&h->md_out, h->m_out, 0) == cudaSuccess;
     if (!ok) {
         std::string m = std::string("allocation failed: ") + cudaGetErrorString(cudaGetLastError());
         tamols_destroy(h);
         return tfail(TAMOLS_E_CUDA, m);
     }
+    memset(h->m_out, 0, 2 * (size_t)max_jobs * sizeof(tamols_result) + 64);  // sequence 0 = nothing published yet
+    h->seq = 0;
     *out = h;
     return TAMOLS_OK;
 }
@@ -710,28 +717,33 @@ extern "C" int tamols_score_host(tamols_handle *h, const double *heights, int32_
     const char *zc = getenv("TAMOLS_ZEROCOPY");
     const bool mapped_out = !scores && !(zc && zc[0] == '0');
     if (mapped_out) {
-        volatile unsigned int *flag = reinterpret_cast<volatile unsigned int *>(h->m_out + (size_t)h->max_jobs * sizeof(tamols_result));
-        const unsigned int seq = ++h->seq;
+        volatile unsigned long long *pairs = reinterpret_cast<volatile unsigned long long *>(h->m_out);
+        unsigned int seq = ++h->seq;
+        if (seq == 0) seq = ++h->seq;  // the block starts zeroed: 0 never names a call
         if (int rc = launch_score(h, ds + o_h, TAMOLS_F64, num_maps, rows, cols, pitch,
                                   xy ? reinterpret_cast<const double *>(ds + o_xy) : nullptr,
                                   reinterpret_cast<const tamols_leg_job *>(ds + o_j), n_jobs, max_nr, max_nc,
-                                  reinterpret_cast<tamols_result *>(h->md_out), nullptr, 0,
-                                  reinterpret_cast<unsigned int *>(h->md_out + (size_t)h->max_jobs * sizeof(tamols_result)), seq))
+                                  reinterpret_cast<tamols_result *>(ds + o_r), nullptr, 0,
+                                  reinterpret_cast<unsigned int *>(h->md_out), seq))
             return rc;
+        const size_t words = (size_t)n_jobs * (sizeof(tamols_result) / 4);
+        uint32_t *dst = reinterpret_cast<uint32_t *>(results);
         unsigned long long spins = 0;
-        while (*flag != seq) {
-            __builtin_ia32_pause();
-            if ((++spins & 0xFFFFF) == 0) {  // ~ms: make sure the kernel is still alive rather than spin forever
-                const cudaError_t q = cudaStreamQuery(h->stream);
-                if (q != cudaErrorNotReady) {
-                    if (q != cudaSuccess) return tfail(TAMOLS_E_CUDA, std::string("scoring kernel: ") + cudaGetErrorString(q));
-                    break;
+        for (size_t k = 0; k < words; ++k) {
+            unsigned long long v;
+            while ((unsigned int)((v = pairs[k]) >> 32) != seq) {
+                __builtin_ia32_pause();
+                if ((++spins & 0xFFFFF) == 0) {  // ~ms: make sure the kernel is still alive rather than spin forever
+                    const cudaError_t q = cudaStreamQuery(h->stream);
+                    if (q != cudaErrorNotReady && (unsigned int)(pairs[k] >> 32) != seq)
+                        return tfail(TAMOLS_E_CUDA, q != cudaSuccess ? std::string("scoring kernel: ") + cudaGetErrorString(q)
+                                                                     : std::string("scoring finished without publishing its results"));
                 }
             }
+            dst[k] = (uint32_t)v;
         }
-        if (*flag != seq) return tfail(TAMOLS_E_CUDA, "scoring finished without publishing its results");
-        memcpy(results, h->m_out, sz_r);
         return TAMOLS_OK;
+
     }
     if (int rc = launch_score(h, ds + o_h, TAMOLS_F64, num_maps, rows, cols, pitch,
                               xy ? reinterpret_cast<const double *>(ds + o_xy) : nullptr,
