@@ -219,42 +219,61 @@ __device__ __forceinline__ float block_sum(float v, float *s_red) {
     return s;
 }
 
-// ---------------------------------------------------------------- finalize kernel --------------------------
-// Shared: best_out[P] | sel (elite indices) [cem_elite] | red[64] | misc
-template <int PARAM>
-__device__ void grf_and_prediction(const DevCfg &c, const float *s_best, const float *state, const float *contact,
-                                   qpmpc_result *out) {
-    // centroidal_nmpc_jax.py:707-784: spline at (step = 0.0, horizon_leg = 1), passed-in contact_sequence[:, 0]
-    float f[4][3], st[4];
-    const int index = chunk_index(c, 0.0f);
-    const float q = chunk_tau(c, 0.0f, 1.0f, index);
-    const CubicBasis B = cubic_basis(q);
-#pragma unroll
-    for (int l = 0; l < 4; ++l) {
-        st[l] = contact[l * c.H];
-        const float *pl = s_best + l * c.np;
-        spline_eval<PARAM>(c, [&](int j) { return pl[j]; }, 0, index, q, B, f[l]);
-    }
-    const float nst = ((st[0] + st[1]) + st[2]) + st[3];
-    shape_forces(c, f, st, c.mg / nst);
-    float x[12];
-#pragma unroll
-    for (int k = 0; k < 12; ++k) x[k] = state[k];
-    srbd_step(c, x, state + 12, f, st, c.dts[0]);
-#pragma unroll
-    for (int l = 0; l < 4; ++l)
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            out->grf[3 * l + k] = f[l][k];
-            out->footholds[3 * l + k] = 0.f;
-        }
-#pragma unroll
-    for (int k = 0; k < 12; ++k) {
-        out->predicted_state[k] = x[k];
-        out->predicted_state[12 + k] = state[12 + k];
-    }
+// One SRBD step of ONE rollout shared by the four lanes of a quad (lane = leg): the lane shapes its own leg's force
+// (in place: f becomes the ground reaction force), the quad sums force and torque with two shuffle stages, lanes
+// 0..2 evaluate sin/cos of roll, pitch, yaw and hand them round, and every lane integrates the same body state.
+// Must be called by all 32 lanes of the warp.  Used by k_rollout_quad and by the fused finalize's one-step prediction.
+__device__ __forceinline__ float quad_sum(float v) {
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    return v;
+}
+__device__ __forceinline__ void quad_leg_step(const DevCfg &c, float f[3], float st, float ref_fz, float footx,
+                                              float footy, float footz, float x[12], float dt, int leg, int qbase) {
+    shape_leg(c, f, st, st * (1.0f / 3.0f), ref_fz);
+    // this leg's share of the net force and of the torque about the centre of mass, summed over the quad
+    const float fzs = f[2] * st;
+    const float rx = footx - x[0], ry = footy - x[1], rz = footz - x[2];
+    const float lx = quad_sum(f[0]), ly = quad_sum(f[1]), lz = quad_sum(fzs);
+    const float tx = quad_sum(ry * fzs - rz * f[1]);
+    const float ty = quad_sum(rz * f[0] - rx * fzs);
+    const float tz = quad_sum(rx * f[1] - ry * f[0]);
+    // lanes 0, 1, 2 of the quad evaluate sin/cos of roll, pitch, yaw and hand them round
+    const float ang = leg == 0 ? x[6] : (leg == 1 ? x[7] : x[8]);
+    float sa, ca;
+    sincosf(ang, &sa, &ca);
+    const float sr = __shfl_sync(0xffffffffu, sa, qbase), cr = __shfl_sync(0xffffffffu, ca, qbase);
+    const float sp = __shfl_sync(0xffffffffu, sa, qbase + 1), cp = __shfl_sync(0xffffffffu, ca, qbase + 1);
+    const float sy = __shfl_sync(0xffffffffu, sa, qbase + 2), cy = __shfl_sync(0xffffffffu, ca, qbase + 2);
+    const float wx = x[9], wy = x[10], wz = x[11];
+    const float yaw_rate = __fdividef(sr * wy + cr * wz, cp);
+    const float pitch_rate = cr * wy - sr * wz;
+    const float roll_rate = wx + sp * yaw_rate;
+    const float bx = cp * cy * tx + cp * sy * ty - sp * tz;
+    const float by = (sr * sp * cy - cr * sy) * tx + (sr * sp * sy + cr * cy) * ty + sr * cp * tz;
+    const float bz = (cr * sp * cy + sr * sy) * tx + (cr * sp * sy - sr * cy) * ty + cr * cp * tz;
+    const float Iwx = c.I[0] * wx + c.I[1] * wy + c.I[2] * wz;
+    const float Iwy = c.I[3] * wx + c.I[4] * wy + c.I[5] * wz;
+    const float Iwz = c.I[6] * wx + c.I[7] * wy + c.I[8] * wz;
+    const float gx = bx - (wy * Iwz - wz * Iwy);
+    const float gy = by - (wz * Iwx - wx * Iwz);
+    const float gz = bz - (wx * Iwy - wy * Iwx);
+    x[0] += x[3] * dt;
+    x[1] += x[4] * dt;
+    x[2] += x[5] * dt;
+    x[3] += (c.inv_mass * lx) * dt;
+    x[4] += (c.inv_mass * ly) * dt;
+    x[5] += (c.inv_mass * lz - 9.81f) * dt;
+    x[6] += roll_rate * dt;
+    x[7] += pitch_rate * dt;
+    x[8] += yaw_rate * dt;
+    x[9] += (c.Iinv[0] * gx + c.Iinv[1] * gy + c.Iinv[2] * gz) * dt;
+    x[10] += (c.Iinv[3] * gx + c.Iinv[4] * gy + c.Iinv[5] * gz) * dt;
+    x[11] += (c.Iinv[6] * gx + c.Iinv[7] * gy + c.Iinv[8] * gz) * dt;
 }
 
+// ---------------------------------------------------------------- finalize kernel --------------------------
+// Shared: best_out[P] | sel (elite indices) [cem_elite] | red[64] | misc
 // Finalize step of robot r, run by ALL threads of one block (any multiple of 32): either the last rollout block of
 // the robot (fused, scratch = that block's parameter columns, no longer needed) or the stand-alone k_finalize.
 // Partials and costs were written by other blocks: they are read through L2 (ld.global.cg).
@@ -289,17 +308,75 @@ __device__ void finalize_robot(const DevCfg &c, const FinalizeArgs &a, const int
     const int stride = PART_HDR + P;
     const uint32_t robot = (uint32_t)(r + a.robot_offset);
 
-    // One pass over the block headers {min_b, sum_t w, min_b, argmin}: kept in shared memory for the rescale.
-    // global minimum / first argmin (nanargmin: lowest index among equal minima)
-    float bc = INFINITY;
-    int bi = 0x7fffffff;
-    for (int b = t; b < a.nblk; b += blockDim.x) {
-        const float4 hd = __ldcg(reinterpret_cast<const float4 *>(part + (size_t)b * stride));
-        s_sc[b] = hd.x;
-        s_sw[b] = hd.y;
-        argmin_combine(bc, bi, hd.z, __float_as_int(hd.w));
+    // Warp 0 alone walks the block headers {min_b, sum_t w, min_b, argmin} (all loads of a lane in flight at once, one
+    // L2 round trip), finds the global minimum / first argmin (nanargmin: lowest index among equal minima), rescales
+    // each block by exp(-(min_b - min)) (online softmax: each rollout block left {min_b, sum_t w, V[P]} relative to
+    // its own minimum; best + sum_i w_i eps_i = sum_i w_i par_i / sum_i w_i with w = softmin(costs), :828-836), sums
+    // the denominators and compacts the live blocks -- shuffles only, ONE block barrier at the end.  Blocks whose
+    // minimum sits far above the global one have a scale of exactly 0 (upstream those samples contribute 0 * eps):
+    // they are skipped; the live ones are kept in ascending order (deterministic summation order).
+    float *s_hdr = s_red;  // [0] min, [1] argmin, [2] denominator, [3] live count
+    float *s_pre = s_red + 8;  // state[24] | contact_sequence[:, 0] (4): staged now, used by the prediction step below
+    if (t >= 32 && t < 56) s_pre[t - 32] = a.state[r * 24 + t - 32];
+    if (t >= 56 && t < 60) s_pre[t - 32] = a.contact[(size_t)r * 4 * c.H + (t - 56) * c.H];
+    if (blockDim.x < 64 && t < 28)  // 32-thread blocks: the one warp does it
+        s_pre[t] = t < 24 ? a.state[r * 24 + t] : a.contact[(size_t)r * 4 * c.H + (t - 24) * c.H];
+    if (t < 32) {
+        float bc = INFINITY;
+        int bi = 0x7fffffff;
+        constexpr int HB = 8;  // headers per lane and trip, all in flight before the first shared-memory store
+        for (int b0 = t; b0 < a.nblk; b0 += 32 * HB) {
+            float4 hd[HB];
+#pragma unroll
+            for (int j = 0; j < HB; ++j) {
+                const int b = b0 + 32 * j;
+                hd[j] = __ldcg(reinterpret_cast<const float4 *>(part + (size_t)(b < a.nblk ? b : 0) * stride));
+            }
+#pragma unroll
+            for (int j = 0; j < HB; ++j) {
+                const int b = b0 + 32 * j;
+                if (b < a.nblk) {
+                    s_sc[b] = hd[j].x;
+                    s_sw[b] = hd[j].y;
+                    argmin_combine(bc, bi, hd[j].z, __float_as_int(hd[j].w));
+                }
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float oc = __shfl_xor_sync(0xffffffffu, bc, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            argmin_combine(bc, bi, oc, oi);
+        }
+        float dpart = 0.f;
+        int nl = 0;
+        if (c.method != QPMPC_METHOD_RANDOM) {
+            for (int b0 = 0; b0 < a.nblk; b0 += 32) {
+                const int b = b0 + t;
+                float sc = 0.f;
+                if (b < a.nblk) {
+                    sc = __expf(-(s_sc[b] - bc));
+                    s_sc[b] = sc;
+                    dpart += s_sw[b] * sc;
+                }
+                const bool live = sc != 0.f;
+                const unsigned m = __ballot_sync(0xffffffffu, live);
+                if (live) s_lb[nl + __popc(m & ((1u << t) - 1u))] = b;
+                nl += __popc(m);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) dpart += __shfl_xor_sync(0xffffffffu, dpart, o);
+        }
+        if (t == 0) {
+            s_hdr[0] = bc;
+            s_hdr[1] = __int_as_float(bi);
+            s_hdr[2] = dpart;
+            s_hdr[3] = __int_as_float(nl);
+        }
     }
-    block_argmin(bc, bi, s_red);
+    __syncthreads();
+    const float bc = s_hdr[0];
+    const int bi = __float_as_int(s_hdr[1]);
     QP_TICK(1);
 
     if (c.method == QPMPC_METHOD_RANDOM) {  // best = control_parameters_vec[best_index], :692
@@ -315,31 +392,9 @@ __device__ void finalize_robot(const DevCfg &c, const FinalizeArgs &a, const int
             s_best[p] = __fadd_rn(a.best[(size_t)r * P + p], e);
         }
     } else {
-        // best + sum_i w_i eps_i = sum_i w_i par_i / sum_i w_i with w = softmin(costs), :828-836.  Each rollout block
-        // left {min_b, sum_t w, V[P]} relative to its own minimum; rescale by exp(-(min_b - min)) and merge.
-        float dpart = 0.f;
-        for (int b = t; b < a.nblk; b += blockDim.x) {
-            const float sc = __expf(-(s_sc[b] - bc));
-            s_sc[b] = sc;
-            dpart += s_sw[b] * sc;
-        }
-        const float den = block_sum(dpart, s_red);  // its barriers also publish s_sc
+        const float den = s_hdr[2];
         QP_TICK(2);
-        // Blocks whose minimum sits far above the global one have a scale of exactly 0 (upstream those samples
-        // contribute 0 * eps = 0): warp 0 compacts the live blocks in ascending order (deterministic summation order).
-        if (t < 32) {
-            int nl = 0;
-            for (int b0 = 0; b0 < a.nblk; b0 += 32) {
-                const int b = b0 + t;
-                const bool live = b < a.nblk && s_sc[b] != 0.f;
-                const unsigned m = __ballot_sync(0xffffffffu, live);
-                if (live) s_lb[nl + __popc(m & ((1u << t) - 1u))] = b;
-                nl += __popc(m);
-            }
-            if (t == 0) s_lb[a.nblk] = nl;
-        }
-        __syncthreads();
-        const int nlive = s_lb[a.nblk];
+        const int nlive = __float_as_int(s_hdr[3]);
         // sum_b scale_b V_b[p]: the block splits into G row groups of P/4 threads, each thread streams float4 slices of
         // every G-th live row through L2 with 16 loads in flight; the G group sums are then added in group order.
         const int P4 = P >> 2;
@@ -402,24 +457,50 @@ __device__ void finalize_robot(const DevCfg &c, const FinalizeArgs &a, const int
         else a.best_out[(size_t)r * P + p] = s_best[p];
     }
 
-    // first GRFs and one-step prediction from the new mean: thread 0 fills a shared-memory copy of the result
-    // record, then one warp-wide store moves it out (the record may live in mapped host memory: two 128-byte
-    // bursts instead of fifty 4-byte stores from one thread)
-    if (t == 0) {
-        s_res->best_cost = bc;
-        s_res->best_index = bi;
-        s_res->reserved = 0;
-        const float *state = a.state + r * 24;
-        const float *contact = a.contact + (size_t)r * 4 * c.H;
+    // first GRFs and one-step prediction from the new mean (centroidal_nmpc_jax.py:707-784: spline at step 0.0 with
+    // horizon_leg = 1, the passed-in contact_sequence[:, 0]): warp 0 runs it as one quad step, lane = leg (the eight
+    // quads of the warp compute the same thing; quad 0 writes).  The record is assembled in shared memory, then one
+    // warp-wide store moves it out (it may live in mapped host memory: two 128-byte bursts).
+    if (t < 32) {
+        const int leg = t & 3, qbase = t & 28;
+        const float *state = s_pre;
+        const float st = s_pre[24 + leg];
+        const float nst = quad_sum(st);
+        const int index = chunk_index(c, 0.0f);
+        const float q = chunk_tau(c, 0.0f, 1.0f, index);
+        const CubicBasis B = cubic_basis(q);
+        const float *pl = s_best + leg * c.np;
+        float f[3];
         if (c.param == QPMPC_PARAM_ZERO_ORDER)
-            grf_and_prediction<QPMPC_PARAM_ZERO_ORDER>(c, s_best, state, contact, s_res);
+            spline_eval<QPMPC_PARAM_ZERO_ORDER>(c, [&](int j) { return pl[j]; }, 0, index, q, B, f);
         else if (c.param == QPMPC_PARAM_LINEAR)
-            grf_and_prediction<QPMPC_PARAM_LINEAR>(c, s_best, state, contact, s_res);
+            spline_eval<QPMPC_PARAM_LINEAR>(c, [&](int j) { return pl[j]; }, 0, index, q, B, f);
         else
-            grf_and_prediction<QPMPC_PARAM_CUBIC>(c, s_best, state, contact, s_res);
+            spline_eval<QPMPC_PARAM_CUBIC>(c, [&](int j) { return pl[j]; }, 0, index, q, B, f);
+        float x[12];
+#pragma unroll
+        for (int k = 0; k < 12; ++k) x[k] = state[k];
+        quad_leg_step(c, f, st, c.mg / nst, state[12 + 3 * leg], state[13 + 3 * leg], state[14 + 3 * leg], x, c.dts[0],
+                      leg, qbase);
+        if (t < 4) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                s_res->grf[3 * leg + k] = f[k];
+                s_res->footholds[3 * leg + k] = 0.f;
+                s_res->predicted_state[3 * leg + k] = leg == 0 ? x[k] : leg == 1 ? x[3 + k] : leg == 2 ? x[6 + k] : x[9 + k];
+                s_res->predicted_state[12 + 3 * leg + k] = state[12 + 3 * leg + k];
+            }
+        }
+        if (t == 0) {
+            s_res->best_cost = bc;
+            s_res->best_index = bi;
+            s_res->reserved = 0;
+        }
         QP_TICK(4);
 #ifdef QPMPC_TIMING
-        for (int k = 1; k < 5; ++k) s_res->footholds[k] = (float)(tick_[k] - tick_[k - 1]);
+        __syncwarp();
+        if (t == 0)
+            for (int k = 1; k < 5; ++k) s_res->footholds[k] = (float)(tick_[k] - tick_[k - 1]);
 #endif
     }
     __syncthreads();
@@ -708,12 +789,6 @@ __host__ __device__ inline int quad_smem_floats(int P, int H, int QB) {
     return QB + P * (QB + 1) + 2 * P + 24 + 12 + 4 + 4 * H + 3 * H + 8 + QB + 64;
 }
 
-__device__ __forceinline__ float quad_sum(float v) {
-    v += __shfl_xor_sync(0xffffffffu, v, 1);
-    v += __shfl_xor_sync(0xffffffffu, v, 2);
-    return v;
-}
-
 template <int PARAM, bool GA, int QB>
 __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__ DevCfg c, const RolloutArgs a_,
                                                        const __grid_constant__ InlineIn in) {
@@ -891,47 +966,7 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
         } else {
             eval_chunk<PARAM>(kc, B, f);
         }
-        shape_leg(c, f, st, st * (1.0f / 3.0f), ref_fz);
-        // this leg's share of the net force and of the torque about the centre of mass, summed over the quad
-        const float fzs = f[2] * st;
-        const float rx = footx - x[0], ry = footy - x[1], rz = footz - x[2];
-        const float lx = quad_sum(f[0]), ly = quad_sum(f[1]), lz = quad_sum(fzs);
-        const float tx = quad_sum(ry * fzs - rz * f[1]);
-        const float ty = quad_sum(rz * f[0] - rx * fzs);
-        const float tz = quad_sum(rx * f[1] - ry * f[0]);
-        // lanes 0, 1, 2 of the quad evaluate sin/cos of roll, pitch, yaw and hand them round
-        const float ang = leg == 0 ? x[6] : (leg == 1 ? x[7] : x[8]);
-        float sa, ca;
-        sincosf(ang, &sa, &ca);
-        const float sr = __shfl_sync(0xffffffffu, sa, qbase), cr = __shfl_sync(0xffffffffu, ca, qbase);
-        const float sp = __shfl_sync(0xffffffffu, sa, qbase + 1), cp = __shfl_sync(0xffffffffu, ca, qbase + 1);
-        const float sy = __shfl_sync(0xffffffffu, sa, qbase + 2), cy = __shfl_sync(0xffffffffu, ca, qbase + 2);
-        const float wx = x[9], wy = x[10], wz = x[11];
-        const float yaw_rate = __fdividef(sr * wy + cr * wz, cp);
-        const float pitch_rate = cr * wy - sr * wz;
-        const float roll_rate = wx + sp * yaw_rate;
-        const float bx = cp * cy * tx + cp * sy * ty - sp * tz;
-        const float by = (sr * sp * cy - cr * sy) * tx + (sr * sp * sy + cr * cy) * ty + sr * cp * tz;
-        const float bz = (cr * sp * cy + sr * sy) * tx + (cr * sp * sy - sr * cy) * ty + cr * cp * tz;
-        const float Iwx = c.I[0] * wx + c.I[1] * wy + c.I[2] * wz;
-        const float Iwy = c.I[3] * wx + c.I[4] * wy + c.I[5] * wz;
-        const float Iwz = c.I[6] * wx + c.I[7] * wy + c.I[8] * wz;
-        const float gx = bx - (wy * Iwz - wz * Iwy);
-        const float gy = by - (wz * Iwx - wx * Iwz);
-        const float gz = bz - (wx * Iwy - wy * Iwx);
-        const float dt = c.dts[n];
-        x[0] += x[3] * dt;
-        x[1] += x[4] * dt;
-        x[2] += x[5] * dt;
-        x[3] += (c.inv_mass * lx) * dt;
-        x[4] += (c.inv_mass * ly) * dt;
-        x[5] += (c.inv_mass * lz - 9.81f) * dt;
-        x[6] += roll_rate * dt;
-        x[7] += pitch_rate * dt;
-        x[8] += yaw_rate * dt;
-        x[9] += (c.Iinv[0] * gx + c.Iinv[1] * gy + c.Iinv[2] * gz) * dt;
-        x[10] += (c.Iinv[3] * gx + c.Iinv[4] * gy + c.Iinv[5] * gz) * dt;
-        x[11] += (c.Iinv[6] * gx + c.Iinv[7] * gy + c.Iinv[8] * gz) * dt;
+        quad_leg_step(c, f, st, ref_fz, footx, footy, footz, x, c.dts[n], leg, qbase);
         // stage cost: lane `leg` owns the terms of states 3 leg .. 3 leg + 2
         const float ea = (leg == 0 ? x[0] : leg == 1 ? x[3] : leg == 2 ? x[6] : x[9]) - ra;
         const float eb = (leg == 0 ? x[1] : leg == 1 ? x[4] : leg == 2 ? x[7] : x[10]) - rb_;
