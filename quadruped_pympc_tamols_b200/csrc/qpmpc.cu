@@ -1,13 +1,18 @@
 // qpmpc.cu -- sampling-MPC solve for sm_100a behind the C ABI of include/qpmpc.h.
 //
-// One solve = two launches on the handle's stream:
-//   k_rollout   grid (ceil(N/T), robots): thread = one rollout.  Draws its noise row with Philox into a
-//               shared-memory column (or copies a reference-supplied row), integrates the SRBD over the horizon,
-//               saturates the cost, then the block reduces {min cost, argmin, sum exp(-(c - min_b)),
-//               sum exp(-(c - min_b)) * eps[P]} from the noise still resident in shared memory.
-//   k_finalize  grid (robots): merges the per-block partials with an online-softmax rescale, applies the
+// One solve = ONE launch on the handle's stream:
+//   k_rollout       grid (ceil(N/128), robots): thread = one rollout (throughput regime, batched robots).
+//   k_rollout_quad  grid (ceil(N/QB), robots): four lanes = one rollout, lane = leg (latency regime, one robot).
+//               Either kernel draws its noise rows with Philox into shared-memory columns (or copies reference-
+//               supplied rows), integrates the SRBD over the horizon, saturates the cost, and the block reduces
+//               {min cost, argmin, sum exp(-(c - min_b)), sum exp(-(c - min_b)) * par[P]} from the parameters still
+//               resident in shared memory.  The block that arrives LAST for its robot (arrival ticket) then runs
+//   finalize_robot  in the same launch: merges the per-block partials with an online-softmax rescale, applies the
 //               random-sampling / MPPI / CEM-MPPI update, evaluates the first-step GRF and the one-step
-//               prediction, and (CEM) selects the elites and their per-parameter spread.
+//               prediction, and (CEM) selects the elites and their per-parameter spread.  k_finalize (grid
+//               (robots)) runs the same function as a second launch when the scratch does not fit or QPMPC_FUSED=0.
+// qpmpc_solve (host buffers) sends its inputs in the kernel parameter block and receives the results as
+// {word, sequence} pairs in mapped pinned memory: one stream command per solve, no copies, no synchronise.
 // Reference semantics: quadruped_pympc/controllers/sampling/centroidal_nmpc_jax.py:629-1094 and
 // centroidal_nmpc_jax_gait_adaptive.py:634-1131 (see include/qpmpc.h for the entry-point map).
 // No CPU fallback: every entry point fails with QPMPC_E_NODEVICE / QPMPC_E_CUDA when the GPU path cannot run.

@@ -1,4 +1,4 @@
-// Device-side single-rigid-body rollout: force parametrisations, force shaping, SRBD dynamics, stage cost.
+// Device-side single-rigid-body rollout: controller constants, spline chunk indexing and the generic spline evaluation.
 // From-scratch CUDA restatement of the math of (paths relative to /root/reference/quadruped_pympc):
 //   controllers/sampling/centroidal_model_jax.py:93-174            fd + explicit Euler
 //   controllers/sampling/centroidal_nmpc_jax.py:181-268            zero-order / linear / cubic parametrisations
@@ -6,9 +6,9 @@
 //   controllers/sampling/centroidal_nmpc_jax.py:316-496            compute_rollout (given contact sequence)
 //   controllers/sampling/centroidal_nmpc_jax_gait_adaptive.py:326-501  compute_rollout (per-sample gait)
 //   helpers/periodic_gait_generator_jax.py:68-89,136-151           trot clock -> contact sequence
-// The building blocks in the reference's operation order (generic spline evaluation, force shaping, one SRBD step,
-// stage cost); k_finalize uses them for the first-step GRF and the one-step prediction, rollout.cuh builds the hot
-// loops on the same formulas.
+// DevCfg, the chunk index / position rules and the generic spline evaluation in the reference's operation order (the
+// fused finalize uses it for the first-step GRF); rollout.cuh builds the hot loops (hoisted chunk coefficients, force
+// shaping, body step, stage cost) on the same formulas, qpmpc.cu holds the quad step.
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -92,92 +92,6 @@ __device__ __forceinline__ void spline_eval(const DevCfg &c, Par par, int istep,
     }
 }
 
-// Gravity compensation, contact mask with the 30/10 x,y scale, then the box + friction-pyramid selects
-// (centroidal_nmpc_jax.py:376-409 and 270-314).  The selects keep the BOUND when the comparison is false, so a
-// NaN force (zero legs in stance: mg/0 * 0) collapses to the bound exactly as upstream.
-__device__ __forceinline__ void shape_forces(const DevCfg &c, float f[4][3], const float st[4], float ref_fz) {
-#pragma unroll
-    for (int l = 0; l < 4; ++l) {
-        float fz = (ref_fz + f[l][2]) * st[l];
-        float fx = f[l][0] * st[l] * (1.0f / 3.0f);
-        float fy = f[l][1] * st[l] * (1.0f / 3.0f);
-        fz = fz > c.fzmin ? fz : c.fzmin;
-        fz = fz < c.fzmax ? fz : c.fzmax;
-        const float lim = c.mu * fz;
-        fx = fx > -lim ? fx : -lim;
-        fx = fx < lim ? fx : lim;
-        fy = fy > -lim ? fy : -lim;
-        fy = fy < lim ? fy : lim;
-        f[l][0] = fx;
-        f[l][1] = fy;
-        f[l][2] = fz;
-    }
-}
-
-// x[0:12] += fd(x, f, stance) * dt  (centroidal_model_jax.py:93-174).  The Euler-rate map is the closed form of
-// inv(conj_euler_rates) @ w (upstream inverts the 3x3 with a general adjugate; det = cos(pitch), so both go
-// non-finite at pitch = +-90 deg and the cost saturates to 1e6 either way).
-__device__ __forceinline__ void srbd_step(const DevCfg &c, float x[12], const float *feet /*[12]*/,
-                                          const float f[4][3], const float st[4], float dt) {
-    float tx = 0.f, ty = 0.f, tz = 0.f, lx = 0.f, ly = 0.f, lz = 0.f;
-#pragma unroll
-    for (int l = 0; l < 4; ++l) {
-        const float fx = f[l][0] * st[l], fy = f[l][1] * st[l], fz = f[l][2] * st[l];
-        lx += fx;
-        ly += fy;
-        lz += fz;
-        const float rx = feet[3 * l] - x[0], ry = feet[3 * l + 1] - x[1], rz = feet[3 * l + 2] - x[2];
-        tx += ry * fz - rz * fy;
-        ty += rz * fx - rx * fz;
-        tz += rx * fy - ry * fx;
-    }
-    float sr, cr, sp, cp, sy, cy;
-    sincosf(x[6], &sr, &cr);
-    sincosf(x[7], &sp, &cp);
-    sincosf(x[8], &sy, &cy);
-    const float wx = x[9], wy = x[10], wz = x[11];
-    // euler rates
-    const float yaw_rate = (sr * wy + cr * wz) / cp;
-    const float pitch_rate = cr * wy - sr * wz;
-    const float roll_rate = wx + sp * yaw_rate;
-    // b_R_w @ tau
-    const float bx = cp * cy * tx + cp * sy * ty - sp * tz;
-    const float by = (sr * sp * cy - cr * sy) * tx + (sr * sp * sy + cr * cy) * ty + sr * cp * tz;
-    const float bz = (cr * sp * cy + sr * sy) * tx + (cr * sp * sy - sr * cy) * ty + cr * cp * tz;
-    // w x (I w)
-    const float Iwx = c.I[0] * wx + c.I[1] * wy + c.I[2] * wz;
-    const float Iwy = c.I[3] * wx + c.I[4] * wy + c.I[5] * wz;
-    const float Iwz = c.I[6] * wx + c.I[7] * wy + c.I[8] * wz;
-    const float gx = bx - (wy * Iwz - wz * Iwy);
-    const float gy = by - (wz * Iwx - wx * Iwz);
-    const float gz = bz - (wx * Iwy - wy * Iwx);
-    const float ax = c.Iinv[0] * gx + c.Iinv[1] * gy + c.Iinv[2] * gz;
-    const float ay = c.Iinv[3] * gx + c.Iinv[4] * gy + c.Iinv[5] * gz;
-    const float az = c.Iinv[6] * gx + c.Iinv[7] * gy + c.Iinv[8] * gz;
-    // explicit Euler, all derivatives from the OLD state
-    x[0] += x[3] * dt;
-    x[1] += x[4] * dt;
-    x[2] += x[5] * dt;
-    x[3] += (c.inv_mass * lx) * dt;
-    x[4] += (c.inv_mass * ly) * dt;
-    x[5] += (c.inv_mass * lz - 9.81f) * dt;
-    x[6] += roll_rate * dt;
-    x[7] += pitch_rate * dt;
-    x[8] += yaw_rate * dt;
-    x[9] += ax * dt;
-    x[10] += ay * dt;
-    x[11] += az * dt;
-}
-
-// (x+ - ref)^T Q (x+ - ref) with the diagonal Q of centroidal_nmpc_jax.py:118-130 (feet weights are zero).
-__device__ __forceinline__ float stage_cost(const DevCfg &c, const float x[12], const float *ref) {
-    float acc = 0.f;
-#pragma unroll
-    for (int k = 0; k < 12; ++k) {
-        const float e = x[k] - ref[k];
-        acc += (e * c.q[k]) * e;
-    }
-    return acc;
-}
+// Force shaping (shape_leg), the body step and the stage cost live in rollout.cuh / qpmpc.cu (quad_leg_step).
 
 }  // namespace qp

@@ -50,7 +50,6 @@ struct Args {
     long long scores_stride;
     Partial *partials;
     unsigned int *tickets;
-    unsigned int *jobs_done;   // unused (kept for layout)
     unsigned int *host_flag;   // host-buffer call: mapped host block of {word, flag_value} pairs, 22 per job (else NULL)
     unsigned int flag_value;   // sequence number of this call
     int n_jobs;
@@ -626,7 +625,7 @@ static int launch_score(tamols_handle *h, const void *d_heights, int dtype, int 
     a.heights = d_heights; a.xy = d_xy; a.jobs = d_jobs; a.results = d_results; a.scores = d_scores;
     a.scores_stride = scores_stride; a.partials = h->d_partials; a.tickets = h->d_tickets;
     a.rows = rows; a.cols = cols; a.pitch = pitch; a.max_tiles = max_tiles;
-    a.jobs_done = h->d_tickets + h->max_jobs; a.host_flag = host_flag; a.flag_value = flag_value; a.n_jobs = n_jobs;
+    a.host_flag = host_flag; a.flag_value = flag_value; a.n_jobs = n_jobs;
     const bool tma = get_tensor_map(h, d_heights, dtype, maps, rows, cols, pitch, th);
     const dim3 grid(max_tiles, n_jobs);
 #define TAMOLS_LAUNCH(HT, TMA, TH_) k_tamols_score<HT, TMA, TH_><<<grid, THREADS, 0, h->stream>>>(h->tmap, a)

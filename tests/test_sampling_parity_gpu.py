@@ -337,20 +337,21 @@ def test_batched_results_do_not_depend_on_sharding():
 
 @pytest.mark.parametrize("method,want_costs", [("mppi", False), ("cem_mppi", True), ("random_sampling", False)])
 def test_zero_copy_solve_equals_copy_path(monkeypatch, method, want_costs):
-    """qpmpc_solve's default I/O (H2D copy in, mapped host block + done flag out), the fully mapped variant and the
-    classic H2D / D2H copies: bit-identical."""
+    """qpmpc_solve's default I/O (inputs in the kernel parameter block, results as {word, sequence} pairs in a mapped
+    host block), inputs by H2D copy, inputs mapped, and the classic H2D / D2H copies + sync: bit-identical."""
     rng = np.random.default_rng(21)
     mass, inertia, _, _ = ROBOTS["go2"]
     st, ref, seq, timing, nominal = synth_problem("go2", "bound", rng)
     outs = []
-    for zc in ("", "1", "0"):
+    for zc, inputs in (("", ""), ("", "copy"), ("", "mapped"), ("0", "")):
         monkeypatch.setenv("QPMPC_ZEROCOPY", zc)
+        monkeypatch.setenv("QPMPC_INPUTS", inputs)
         h = _cabi.Handle(_cabi.make_config(mass=mass, inertia=np.array(inertia), sampling_method=method,
                                            parametrization="cubic_spline", gait_adaptive=(method != "cem_mppi"),
                                            num_parallel_computations=10000))
         best = np.zeros(h.P, np.float32)
         sig = np.full(h.P, 3.0, np.float32) if method == "cem_mppi" else None
-        for it in range(3):  # repeated calls reuse the block and bump the flag value
+        for it in range(3):  # repeated calls reuse the block and bump the sequence number
             r = h.solve(st, ref, seq, best, 3, it, timing=timing, nominal_freq=nominal, optimize_swing=1, sigma_in=sig,
                         want_costs=want_costs)
             best = r["best"].copy()
@@ -362,3 +363,29 @@ def test_zero_copy_solve_equals_copy_path(monkeypatch, method, want_costs):
         assert outs[0].keys() == other.keys()
         for k in outs[0]:
             assert np.array_equal(outs[0][k], other[k]), k
+
+
+@pytest.mark.parametrize("method", ["mppi", "random_sampling"])
+def test_quad_block_sizes_agree(monkeypatch, method):
+    """The three quad-kernel block sizes (32, 72, 128 rollouts per block) split the same 10,000 rollouts differently:
+    costs, argmin and best cost are bit-identical, the MPPI mean agrees to summation-order round-off."""
+    rng = np.random.default_rng(5)
+    mass, inertia, _, _ = ROBOTS["go2"]
+    st, ref, seq, timing, nominal = synth_problem("go2", "trot", rng)
+    outs = []
+    for qb in ("32", "72", "128"):
+        monkeypatch.setenv("QPMPC_KERNEL", "quad")
+        monkeypatch.setenv("QPMPC_QB", qb)
+        h = _cabi.Handle(_cabi.make_config(mass=mass, inertia=np.array(inertia), sampling_method=method,
+                                           parametrization="linear_spline", gait_adaptive=True,
+                                           num_parallel_computations=10000))
+        outs.append(h.solve(st, ref, seq, np.zeros(h.P, np.float32), 9, 4, timing=timing, nominal_freq=nominal,
+                            optimize_swing=1))
+        h.close()
+    for o in outs[1:]:
+        assert np.array_equal(outs[0]["costs"], o["costs"])
+        assert outs[0]["best_index"] == o["best_index"] and outs[0]["best_cost"] == o["best_cost"]
+        if method == "random_sampling":
+            assert np.array_equal(outs[0]["best"], o["best"])
+        else:
+            assert np.max(np.abs(outs[0]["best"] - o["best"])) <= 1e-5 * max(1.0, float(np.max(np.abs(o["best"]))))
