@@ -101,12 +101,28 @@ int64_t qpmpc_launch_count(const qpmpc_handle *h);
  * d_eps [N,P] / d_freqs [N]: optional DEVICE buffers holding reference-supplied noise
  * (additional_random_parameters with sigma applied, step_frequencies_vec); NULL = in-kernel Philox.
  * Outputs: *out, best_out[P], sigma_out[P] (cem only, may be NULL), costs_out[N] (may be NULL).
- * One H2D copy, the kernels, one D2H copy (two when costs_out != NULL), then a stream synchronise.
+ * One launch: the inputs ride in the kernel parameter block, the results return through mapped pinned memory
+ * (QPMPC_ZEROCOPY=0: H2D copy, kernel, D2H copy, stream synchronise).  Returns when the results are complete.
  */
 int qpmpc_solve(qpmpc_handle *h, const float *state, const float *reference, const float *contact_sequence,
                 const float *best_in, uint64_t seed, uint64_t offset, const float *timing,
                 float nominal_step_frequency, int32_t optimize_swing, const float *sigma_in, const float *d_eps,
                 const float *d_freqs, qpmpc_result *out, float *best_out, float *sigma_out, float *costs_out);
+
+/* `iterations` chained solves without a host round trip: the sampling branch of
+ * SRBDControllerInterface.compute_control (interfaces/srbd_controller_interface.py:123-170), whose loop
+ *   for iter_sampling in range(num_sampling_iterations): controller.with_newkey(); ... = jitted_compute_control(...)
+ * feeds each iteration's best_control_parameters (and, for cem_mppi, its new sigma) to the next one.
+ * Iteration i draws its noise with the key (seed, first_offset + i), reads the mean (and sigma) the previous
+ * iteration left ON THE DEVICE, and only the last iteration's outputs travel back: `iterations` kernel launches
+ * back to back on the handle's stream, one wait.  Arguments and outputs as qpmpc_solve (outputs = those of the last
+ * iteration; costs_out = its costs).  Reference-supplied noise buffers are not supported here (Philox only).
+ */
+int qpmpc_solve_iterated(qpmpc_handle *h, const float *state, const float *reference, const float *contact_sequence,
+                         const float *best_in, uint64_t seed, uint64_t first_offset, int32_t iterations,
+                         const float *timing, float nominal_step_frequency, int32_t optimize_swing,
+                         const float *sigma_in, qpmpc_result *out, float *best_out, float *sigma_out,
+                         float *costs_out);
 
 /* Device-resident problem description for the batched entry points; every pointer is a DEVICE pointer
  * with `num_robots` leading rows. */

@@ -57,7 +57,7 @@ class QpmpcBatch(C.Structure):
 
 
 EXPORTS = ["qpmpc_create", "qpmpc_destroy", "qpmpc_num_params", "qpmpc_last_error", "qpmpc_version", "qpmpc_stream",
-           "qpmpc_launch_count", "qpmpc_solve", "qpmpc_solve_batched", "qpmpc_rollout_costs", "qpmpc_generate_noise", "qpmpc_set_profiling", "qpmpc_profile_last",
+           "qpmpc_launch_count", "qpmpc_solve", "qpmpc_solve_iterated", "qpmpc_solve_batched", "qpmpc_rollout_costs", "qpmpc_generate_noise", "qpmpc_set_profiling", "qpmpc_profile_last",
            "qpmpc_measure_fp32_peak"]
 
 
@@ -93,6 +93,8 @@ def lib():
         L.qpmpc_launch_count.restype = C.c_int64
         L.qpmpc_solve.argtypes = [vp, vp, vp, vp, vp, C.c_uint64, C.c_uint64, vp, C.c_float, C.c_int32, vp, vp, vp,
                                   vp, vp, vp, vp]  # host pointers passed as integers (cheapest ctypes marshalling)
+        L.qpmpc_solve_iterated.argtypes = [vp, vp, vp, vp, vp, C.c_uint64, C.c_uint64, C.c_int32, vp, C.c_float, C.c_int32,
+                                           vp, vp, vp, vp, vp]
         L.qpmpc_solve_batched.argtypes = [vp, C.POINTER(QpmpcBatch), C.c_uint64, C.c_uint64]
         L.qpmpc_rollout_costs.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp]
         L.qpmpc_generate_noise.argtypes = [vp, C.c_uint64, C.c_uint64, C.c_int32, vp, C.c_float, C.c_int32, vp, vp]
@@ -184,8 +186,10 @@ class Handle:
         return lib().qpmpc_launch_count(self._h)
 
     def solve(self, state, reference, contact_sequence, best_in, seed, offset, timing=None, nominal_freq=0.0,
-              optimize_swing=0, sigma_in=None, d_eps=None, d_freqs=None, want_costs=True):
-        """One jitted_compute_control call; host numpy in, dict of host numpy out."""
+              optimize_swing=0, sigma_in=None, d_eps=None, d_freqs=None, want_costs=True, iterations=1):
+        """One jitted_compute_control call; host numpy in, dict of host numpy out.  iterations > 1: that many chained
+        solves on the device (keys (seed, offset), (seed, offset + 1), ...; mean and sigma carried on the device,
+        srbd_controller_interface.py:131-170), outputs of the last one."""
         st, rf, cs, bi = _f32(state).reshape(24), _f32(reference).reshape(24), _f32(contact_sequence), _f32(best_in)
         if cs.size != 4 * self.H or bi.size != self.P:
             raise QpmpcError(f"contact_sequence must be [4,{self.H}] and best [{self.P}]")
@@ -197,9 +201,16 @@ class Handle:
         best_out = np.empty(self.P, np.float32)
         sigma_out = np.empty(self.P, np.float32) if sg is not None else None
         costs = np.empty(self.N, np.float32) if want_costs else None
-        check(lib().qpmpc_solve(self._h, _fp(st), _fp(rf), _fp(cs), _fp(bi), int(seed), int(offset), _fp(tm),
-                                float(nominal_freq), int(optimize_swing), _fp(sg), d_eps, d_freqs,
-                                _fp(res), _fp(best_out), _fp(sigma_out), _fp(costs)))
+        if iterations == 1:
+            check(lib().qpmpc_solve(self._h, _fp(st), _fp(rf), _fp(cs), _fp(bi), int(seed), int(offset), _fp(tm),
+                                    float(nominal_freq), int(optimize_swing), _fp(sg), d_eps, d_freqs,
+                                    _fp(res), _fp(best_out), _fp(sigma_out), _fp(costs)))
+        else:
+            if d_eps is not None or d_freqs is not None:
+                raise QpmpcError("chained iterations draw their own noise (no d_eps / d_freqs)")
+            check(lib().qpmpc_solve_iterated(self._h, _fp(st), _fp(rf), _fp(cs), _fp(bi), int(seed), int(offset),
+                                             int(iterations), _fp(tm), float(nominal_freq), int(optimize_swing), _fp(sg),
+                                             _fp(res), _fp(best_out), _fp(sigma_out), _fp(costs)))
         return dict(grf=res[0:12], footholds=res[12:24], predicted_state=res[24:48], best=best_out,
                     best_cost=res[48], best_freq=res[49], costs=costs, sigma=sigma_out,
                     best_index=int(res[50:51].view(np.int32)[0]))

@@ -225,6 +225,31 @@ class Sampling_MPC:
         return (r["grf"], r["footholds"], r["predicted_state"], r["best"], r["best_cost"], r["best_freq"], r["costs"],
                 r["sigma"])
 
+    def compute_control_iterated(self, state, reference, contact_sequence, timing=None, nominal_step_frequency=0.0,
+                                 optimize_swing=0, sigma0=None, iterations=None):
+        """The whole `for iter_sampling in range(num_sampling_iterations)` loop of
+        SRBDControllerInterface.compute_control (interfaces/srbd_controller_interface.py:131-170) as ONE call: every
+        iteration advances the key (with_newkey), starts from the previous iteration's mean and, for cem_mppi, from
+        its sigma (iteration 0 from `sigma0` = mpc_params['sigma_cem_mppi'], :134-135) -- chained on the device, no
+        host round trip in between.  Updates best_control_parameters, master_key and sigma_cem_mppi exactly as the
+        loop would and returns the last iteration's tuple (7 entries, 8 with the new sigma for cem_mppi)."""
+        K = int(self.num_sampling_iterations if iterations is None else iterations)
+        cem = self.sampling_method == "cem_mppi"
+        if cem and sigma0 is None:
+            sigma0 = self._config.mpc_params["sigma_cem_mppi"]
+        sigma = np.broadcast_to(np.asarray(sigma0, np.float32), (self.num_control_parameters,)) if cem else None
+        key = np.asarray(self.master_key, dtype=np.uint64).reshape(-1)
+        r = self._handle.solve(state, reference, contact_sequence, self.best_control_parameters, int(key[0]),
+                               int(key[-1]) + 1, timing=self._timing(timing), nominal_freq=float(nominal_step_frequency),
+                               optimize_swing=int(optimize_swing), sigma_in=sigma, want_costs=True, iterations=K)
+        self.master_key = np.array([key[0], key[-1] + np.uint64(K)], dtype=np.uint64)  # K times with_newkey
+        self.best_control_parameters = r["best"]
+        out = (r["grf"], r["footholds"], r["predicted_state"], r["best"], r["best_cost"], r["best_freq"], r["costs"])
+        if cem:
+            self.sigma_cem_mppi = r["sigma"]
+            out = out + (r["sigma"],)
+        return out
+
     def _timing(self, timing):
         return None  # the fixed-gait controller ignores timing / nominal frequency / optimize_swing (:629-639)
 

@@ -53,7 +53,8 @@ struct SolveArgs {
     int nblk;         // rollout blocks per robot
     int robot_offset; // global id of robot 0 of this launch (Philox subsequence = robot_offset + r)
     int fused;        // 1: the last rollout block of a robot runs finalize_robot itself (one launch per solve)
-    int inline_in;    // 1: the eight input pointers above hold BYTE OFFSETS into the kernel's InlineIn parameter
+    int inline_in;    // bit 0: state / reference / contact / timing / nominal / oswing, bit 1: best, bit 2: sigma hold
+                      // BYTE OFFSETS into the kernel's InlineIn parameter instead of device addresses
 };
 typedef SolveArgs RolloutArgs;
 typedef SolveArgs FinalizeArgs;
@@ -67,17 +68,17 @@ struct InlineIn {
 };
 __device__ __forceinline__ SolveArgs resolve_inputs(const SolveArgs &a_, const InlineIn &in) {
     SolveArgs a = a_;
-    if (a.inline_in) {
-        const char *base = reinterpret_cast<const char *>(in.v);
+    const char *base = reinterpret_cast<const char *>(in.v);
+    if (a.inline_in & 1) {
         a.state = reinterpret_cast<const float *>(base + reinterpret_cast<size_t>(a_.state));
         a.reference = reinterpret_cast<const float *>(base + reinterpret_cast<size_t>(a_.reference));
         a.contact = reinterpret_cast<const float *>(base + reinterpret_cast<size_t>(a_.contact));
-        a.best = reinterpret_cast<const float *>(base + reinterpret_cast<size_t>(a_.best));
-        a.sigma = reinterpret_cast<const float *>(base + reinterpret_cast<size_t>(a_.sigma));
         a.timing = reinterpret_cast<const float *>(base + reinterpret_cast<size_t>(a_.timing));
         a.nominal = reinterpret_cast<const float *>(base + reinterpret_cast<size_t>(a_.nominal));
         a.oswing = reinterpret_cast<const int32_t *>(base + reinterpret_cast<size_t>(a_.oswing));
     }
+    if (a.inline_in & 2) a.best = reinterpret_cast<const float *>(base + reinterpret_cast<size_t>(a_.best));
+    if (a.inline_in & 4) a.sigma = reinterpret_cast<const float *>(base + reinterpret_cast<size_t>(a_.sigma));
     return a;
 }
 
@@ -1099,6 +1100,7 @@ struct qpmpc_handle {
     // single-robot staging: one pinned input block, one pinned output block
     float *h_in, *d_in;
     float *h_out, *d_out;
+    float *d_iter;        // [2][2P]: mean | sigma carried between chained iterations (qpmpc_solve_iterated)
     float *m_io, *md_io;  // mapped (zero-copy) host block of qpmpc_solve: inputs | {word, seq} output pairs
     unsigned int seq;     // value the next solve stores to the done flag
     size_t in_floats, out_floats;
@@ -1295,6 +1297,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
               cudaHostGetDevicePointer(&h->md_io, h->m_io, 0) == cudaSuccess &&
               cudaMalloc(&h->d_in, h->in_floats * 4) == cudaSuccess &&
               cudaMalloc(&h->d_out, h->out_floats * 4) == cudaSuccess &&
+              cudaMalloc(&h->d_iter, (size_t)4 * P * 4) == cudaSuccess &&
               cudaMalloc(&h->d_costs, (size_t)c.max_robots * d.N * 4) == cudaSuccess &&
               cudaMalloc(&h->d_partials, h->partial_floats * 4) == cudaSuccess &&
               cudaMalloc(&h->d_tickets, (size_t)c.max_robots * 4) == cudaSuccess &&
@@ -1321,6 +1324,7 @@ extern "C" int qpmpc_destroy(qpmpc_handle *h) {
     if (h->m_io) cudaFreeHost(h->m_io);
     if (h->d_in) cudaFree(h->d_in);
     if (h->d_out) cudaFree(h->d_out);
+    if (h->d_iter) cudaFree(h->d_iter);
     if (h->d_costs) cudaFree(h->d_costs);
     if (h->d_partials) cudaFree(h->d_partials);
     if (h->d_tickets) cudaFree(h->d_tickets);
@@ -1337,7 +1341,7 @@ static const InlineIn g_no_inline = {};
 
 static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, uint64_t offset,
                         uint2 *ll_out = nullptr, unsigned int ll_seq = 0,
-                        const InlineIn *inl = nullptr) {
+                        const InlineIn *inl = nullptr, int inline_mask = 7) {
     const DevCfg &d = h->dc;
     const int R = b.num_robots, N = d.N, P = d.P;
     const LaunchPlan pl = plan_launch(h, N, (long long)N * R);
@@ -1352,7 +1356,7 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
     ra.result = b.d_result; ra.best_out = b.d_best_out; ra.sigma_out = b.d_sigma_out; ra.tickets = h->d_tickets;
     ra.key = NoiseKey{seed, offset}; ra.n = N; ra.costs_only = 0; ra.nblk = nblk; ra.robot_offset = b.robot_offset;
     ra.ll_out = ll_out; ra.ll_seq = ll_seq;
-    ra.inline_in = inl ? 1 : 0;  // the caller then filled the input pointers of `b` with byte offsets
+    ra.inline_in = inl ? inline_mask : 0;  // the caller then filled those input pointers of `b` with byte offsets
     const InlineIn &in = inl ? *inl : g_no_inline;
     // One launch per solve: the last rollout block of each robot runs the finalize step in the shared memory its
     // parameter columns occupied.  Falls back to the stand-alone k_finalize when that scratch is too small
@@ -1392,17 +1396,20 @@ extern "C" int qpmpc_solve_batched(qpmpc_handle *h, const qpmpc_batch *batch, ui
     return launch_solve(h, b, seed, offset);
 }
 
-extern "C" int qpmpc_solve(qpmpc_handle *h, const float *state, const float *reference, const float *contact_sequence,
-                           const float *best_in, uint64_t seed, uint64_t offset, const float *timing,
-                           float nominal_step_frequency, int32_t optimize_swing, const float *sigma_in,
-                           const float *d_eps, const float *d_freqs, qpmpc_result *out, float *best_out,
-                           float *sigma_out, float *costs_out) {
+// qpmpc_solve and qpmpc_solve_iterated: `iterations` launches back to back, one wait.  Iteration i reads the mean (and
+// sigma) iteration i - 1 left in h->d_iter[(i - 1) & 1]; only the last one publishes to the host.
+static int solve_impl(qpmpc_handle *h, const float *state, const float *reference, const float *contact_sequence,
+                      const float *best_in, uint64_t seed, uint64_t offset, int iterations, const float *timing,
+                      float nominal_step_frequency, int32_t optimize_swing, const float *sigma_in, const float *d_eps,
+                      const float *d_freqs, qpmpc_result *out, float *best_out, float *sigma_out, float *costs_out) {
     if (!h || !state || !reference || !contact_sequence || !best_in || !out || !best_out)
         return fail(QPMPC_E_ARG, "null argument");
     const DevCfg &d = h->dc;
     const int H = d.H, P = d.P, N = d.N;
     if (d.method == QPMPC_METHOD_CEM && !sigma_in) return fail(QPMPC_E_ARG, "cem_mppi needs sigma_in");
     if (d.ga && !timing) return fail(QPMPC_E_ARG, "gait adaptive needs timing");
+    if (iterations < 1) return fail(QPMPC_E_ARG, "iterations must be >= 1");
+    if (iterations > 1 && (d_eps || d_freqs)) return fail(QPMPC_E_ARG, "chained iterations draw their own noise");
     CU(cudaSetDevice(h->device));
     // Default I/O: the ~1 KB of inputs rides in the kernel's parameter block (InlineIn) and the finalize step stores the
     // results straight into a mapped pinned block and raises a flag there that the host spins on -- ONE command on
@@ -1448,11 +1455,26 @@ extern "C" int qpmpc_solve(qpmpc_handle *h, const float *state, const float *ref
     b.d_best_out = dout + res_floats;
     b.d_sigma_out = (d.method == QPMPC_METHOD_CEM) ? dout + res_floats + P : nullptr;
     b.d_costs = h->d_costs;
+    // iterations 0 .. K-2: outputs stay on the device (ping-pong mean / sigma blocks, scratch result record)
+    for (int it = 0; it + 1 < iterations; ++it) {
+        qpmpc_batch bi = b;
+        float *io = h->d_iter + (size_t)(it & 1) * 2 * P;
+        bi.d_best_out = io;
+        bi.d_sigma_out = (d.method == QPMPC_METHOD_CEM) ? io + P : nullptr;
+        bi.d_result = reinterpret_cast<qpmpc_result *>(h->d_out);
+        int rc = launch_solve(h, bi, seed, offset + (uint64_t)it, nullptr, 0, inline_in ? &inl : nullptr, it == 0 ? 7 : 1);
+        if (rc) return rc;
+        b.d_best_in = io;  // the next iteration starts from this mean (and sigma): device addresses from now on
+        b.d_sigma_in = io + P;
+    }
+    const int last_mask = iterations > 1 ? 1 : 7;
+    const uint64_t last_offset = offset + (uint64_t)(iterations - 1);
     if (zero_copy) {
         volatile unsigned long long *pairs = reinterpret_cast<volatile unsigned long long *>(h->m_io + ll_off);
         unsigned int seq = ++h->seq;
         if (seq == 0) seq = ++h->seq;  // the block starts zeroed: 0 never names a solve
-        int rc = launch_solve(h, b, seed, offset, reinterpret_cast<uint2 *>(h->md_io + ll_off), seq, inline_in ? &inl : nullptr);
+        int rc = launch_solve(h, b, seed, last_offset, reinterpret_cast<uint2 *>(h->md_io + ll_off), seq, inline_in ? &inl : nullptr,
+                              last_mask);
         if (rc) return rc;
         if (costs_out) {  // 4 N bytes: a regular copy behind the kernel; its completion implies the pairs too
             CU(cudaMemcpyAsync(h->h_out + h->out_floats, h->d_costs, (size_t)N * 4, cudaMemcpyDeviceToHost, h->stream));
@@ -1476,7 +1498,7 @@ extern "C" int qpmpc_solve(qpmpc_handle *h, const float *state, const float *ref
             dst[k] = (uint32_t)v;
         }
     } else {
-        int rc = launch_solve(h, b, seed, offset);
+        int rc = launch_solve(h, b, seed, last_offset, nullptr, 0, inline_in ? &inl : nullptr, last_mask);
         if (rc) return rc;
         CU(cudaMemcpyAsync(h->h_out, h->d_out, h->out_floats * 4, cudaMemcpyDeviceToHost, h->stream));
         if (costs_out) CU(cudaMemcpyAsync(h->h_out + h->out_floats, h->d_costs, (size_t)N * 4, cudaMemcpyDeviceToHost, h->stream));
@@ -1487,6 +1509,25 @@ extern "C" int qpmpc_solve(qpmpc_handle *h, const float *state, const float *ref
     if (sigma_out && d.method == QPMPC_METHOD_CEM) memcpy(sigma_out, hout + res_floats + P, (size_t)P * 4);
     if (costs_out) memcpy(costs_out, h->h_out + h->out_floats, (size_t)N * 4);
     return QPMPC_OK;
+}
+
+extern "C" int qpmpc_solve(qpmpc_handle *h, const float *state, const float *reference, const float *contact_sequence,
+                           const float *best_in, uint64_t seed, uint64_t offset, const float *timing,
+                           float nominal_step_frequency, int32_t optimize_swing, const float *sigma_in,
+                           const float *d_eps, const float *d_freqs, qpmpc_result *out, float *best_out,
+                           float *sigma_out, float *costs_out) {
+    return solve_impl(h, state, reference, contact_sequence, best_in, seed, offset, 1, timing, nominal_step_frequency,
+                      optimize_swing, sigma_in, d_eps, d_freqs, out, best_out, sigma_out, costs_out);
+}
+
+extern "C" int qpmpc_solve_iterated(qpmpc_handle *h, const float *state, const float *reference,
+                                    const float *contact_sequence, const float *best_in, uint64_t seed,
+                                    uint64_t first_offset, int32_t iterations, const float *timing,
+                                    float nominal_step_frequency, int32_t optimize_swing, const float *sigma_in,
+                                    qpmpc_result *out, float *best_out, float *sigma_out, float *costs_out) {
+    return solve_impl(h, state, reference, contact_sequence, best_in, seed, first_offset, iterations, timing,
+                      nominal_step_frequency, optimize_swing, sigma_in, nullptr, nullptr, out, best_out, sigma_out,
+                      costs_out);
 }
 
 extern "C" int qpmpc_rollout_costs(qpmpc_handle *h, const float *state, const float *reference,
@@ -1513,7 +1554,7 @@ extern "C" int qpmpc_rollout_costs(qpmpc_handle *h, const float *state, const fl
     ra.state = din; ra.reference = din + 24; ra.contact = din + 48; ra.timing = din + o_timing;
     ra.best = din + 48 + 4 * H; ra.sigma = din + 48 + 4 * H + P;  // unused in costs-only mode; kept inside the block
     ra.nominal = din + o_timing + 4; ra.oswing = reinterpret_cast<const int32_t *>(din + o_timing + 5);
-    ra.inline_in = inline_in ? 1 : 0;
+    ra.inline_in = inline_in ? 7 : 0;
     ra.eps = d_params; ra.freqs = d_freqs; ra.costs = d_costs; ra.n = n; ra.costs_only = 1;
     const LaunchPlan pl = plan_launch(h, n, n);
     ra.nblk = pl.nblk;

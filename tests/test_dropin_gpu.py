@@ -174,3 +174,82 @@ def test_visual_foothold_adaptation_matches_reference_fixture(path):
         assert abs(ref_scores[l, k] - ref_scores[l, ref_idx[l]]) < 1e-6
     assert vfa.get_footholds_adapted(None)[0] is ref
     vfa.close()
+
+
+@pytest.mark.parametrize("robot,gait,method,param,ga,iters", [
+    ("go2", "bound", "mppi", "cubic_spline", True, 3),
+    ("hyqreal1", "pace", "cem_mppi", "cubic_spline", False, 3),
+    ("aliengo", "trot", "random_sampling", "zero_order", False, 2),
+    ("aliengo", "trot", "mppi", "linear_spline", False, 1),
+])
+def test_interface_chained_iterations_equal_the_python_loop(robot, gait, method, param, ga, iters):
+    """SRBDControllerInterface.compute_control with the num_sampling_iterations loop chained on the
+    device (qpmpc_solve_iterated) against the upstream loop replayed call by call on a second controller
+    (srbd_controller_interface.py:117-183): bit-identical GRFs, prediction, mean, sigma, key; two consecutive control
+    steps, the second one with a lift-off edge (parameter block zeroing)."""
+    from quadruped_pympc_tamols_b200.interfaces.srbd_controller_interface import SRBDControllerInterface
+    if ga:
+        from quadruped_pympc_tamols_b200.controllers.sampling.centroidal_nmpc_jax_gait_adaptive import Sampling_MPC
+    else:
+        from quadruped_pympc_tamols_b200.controllers.sampling.centroidal_nmpc_jax import Sampling_MPC
+    cfg = make_config(robot, sampling_method=method, control_parametrization=param, optimize_step_freq=ga,
+                      num_parallel_computations=4096, num_sampling_iterations=iters)
+    itf = SRBDControllerInterface(config=cfg)
+    loop = Sampling_MPC(config=cfg)
+    rng = np.random.default_rng(11)
+    previous_contact = np.array([1, 1, 1, 1])
+    for step in range(2):
+        st, ref, seq, timing, freq = synth_problem(robot, gait, rng)
+        if step == 1:
+            seq = np.array(seq)
+            seq[1, 0] = 0.0  # FR lifts off between the two control steps
+        state_current, ref_state = _dicts(st, ref)
+        got = itf.compute_control(state_current, ref_state, seq, cfg.inertia, timing, freq, 1)
+
+        current_contact = np.array([seq[0][0], seq[1][0], seq[2][0], seq[3][0]])
+        s_, r_ = loop.prepare_state_and_reference(state_current, ref_state, current_contact, previous_contact)
+        previous_contact = current_contact
+        for it in range(loop.num_sampling_iterations):
+            loop = loop.with_newkey()
+            if method == "cem_mppi":
+                if it == 0:
+                    loop = loop.with_newsigma(cfg.mpc_params["sigma_cem_mppi"])
+                out = loop.jitted_compute_control(s_, r_, seq, loop.best_control_parameters, loop.master_key,
+                                                  loop.sigma_cem_mppi)
+                grf, _, pred, loop.best_control_parameters, best_cost, best_freq, costs, sigma = out
+                loop = loop.with_newsigma(sigma)
+            else:
+                out = loop.jitted_compute_control(s_, r_, seq, loop.best_control_parameters, loop.master_key, timing,
+                                                  freq, 1)
+                grf, _, pred, loop.best_control_parameters, best_cost, best_freq, costs = out
+        grf = np.array(grf)
+        for k, leg in enumerate(LEGS):
+            assert np.array_equal(got[0][leg], grf[3 * k:3 * k + 3] * current_contact[k])
+            assert np.array_equal(got[1][leg], ref_state["ref_foot_" + leg][0])
+        assert got[2] is None and got[3] is None and got[4] is None
+        assert got[5] == best_freq
+        assert np.array_equal(got[6], pred)
+        assert np.array_equal(itf.controller.best_control_parameters, loop.best_control_parameters)
+        assert np.array_equal(itf.controller.master_key, loop.master_key)
+        assert itf.last_best_cost == float(best_cost) and np.array_equal(itf.last_costs, costs)
+        if method == "cem_mppi":
+            assert np.array_equal(itf.controller.sigma_cem_mppi, loop.sigma_cem_mppi)
+    assert itf.controller._handle.launch_count == 2 * iters  # one kernel launch per iteration, nothing else
+    itf.close()
+    loop.close()
+
+
+def test_interface_rejects_what_upstream_cannot_run():
+    from quadruped_pympc_tamols_b200.interfaces.srbd_controller_interface import SRBDControllerInterface
+    with pytest.raises(NotImplementedError):
+        SRBDControllerInterface(config=make_config("go2", type="nominal"))
+    itf = SRBDControllerInterface(config=make_config("go2", sampling_method="cem_mppi", optimize_step_freq=True,
+                                                     num_parallel_computations=256))
+    rng = np.random.default_rng(0)
+    st, ref, seq, timing, freq = synth_problem("go2", "trot", rng)
+    state_current, ref_state = _dicts(st, ref)
+    with pytest.raises(TypeError):
+        itf.compute_control(state_current, ref_state, seq, None, timing, freq, 1)
+    with pytest.raises(NotImplementedError):
+        itf.compute_RTI()
+    itf.close()

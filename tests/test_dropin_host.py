@@ -158,3 +158,67 @@ def test_vfa_state_machine_and_height_strategy():
     assert not v.initialized
     with pytest.raises(ImportError):
         VisualFootholdAdaptation(legs, adaptation_strategy="vfa")
+
+
+class _RecordingHandle(_NoDeviceHandle):
+    """Records the arguments of the chained solve and returns a recognisable result."""
+
+    def solve(self, state, reference, contact_sequence, best_in, seed, offset, timing=None, nominal_freq=0.0,
+              optimize_swing=0, sigma_in=None, d_eps=None, d_freqs=None, want_costs=True, iterations=1):
+        self.call = dict(state=np.array(state), best_in=np.array(best_in), seed=seed, offset=offset, timing=timing,
+                         nominal_freq=nominal_freq, optimize_swing=optimize_swing, sigma_in=sigma_in,
+                         iterations=iterations)
+        return dict(grf=np.arange(12, dtype=np.float32), footholds=np.zeros(12, np.float32),
+                    predicted_state=np.full(24, 7.0, np.float32), best=np.full(self.P, 2.0, np.float32),
+                    best_cost=np.float32(5.0), best_freq=np.float32(2.0), costs=np.ones(self.N, np.float32),
+                    sigma=None if sigma_in is None else np.full(self.P, 0.5, np.float32), best_index=3)
+
+
+@pytest.mark.parametrize("method,ga", [("mppi", True), ("cem_mppi", False)])
+def test_interface_sampling_branch_plumbing(monkeypatch, method, ga):
+    """SRBDControllerInterface (sampling branch, srbd_controller_interface.py:117-183, 224-243): ONE chained call per
+    control step, key advanced by num_sampling_iterations, lift-off zeroing, contact-masked GRFs, reference footholds."""
+    from quadruped_pympc_tamols_b200.interfaces.srbd_controller_interface import SRBDControllerInterface
+    monkeypatch.setattr(_cabi, "Handle", _RecordingHandle)
+    cfg = make_config("go2", sampling_method=method, optimize_step_freq=ga, num_sampling_iterations=4,
+                      num_parallel_computations=64)
+    itf = SRBDControllerInterface(config=cfg)
+    c = itf.controller
+    assert type(c).__module__.endswith("gait_adaptive") == ga
+    c.best_control_parameters = np.ones(c.num_control_parameters, np.float32)
+    state = {"position": np.zeros(3), "linear_velocity": np.zeros(3), "orientation": np.zeros(3),
+             "angular_velocity": np.zeros(3)}
+    ref = {"ref_position": np.zeros(3), "ref_linear_velocity": np.zeros(3), "ref_orientation": np.zeros(3),
+           "ref_angular_velocity": np.zeros(3)}
+    for k, f in enumerate(("FL", "FR", "RL", "RR")):
+        state["foot_" + f] = np.full(3, float(k))
+        ref["ref_foot_" + f] = np.full((1, 3), 10.0 + k)
+    seq = np.ones((4, 12))
+    seq[2, 0] = 0  # RL in swing now, was in stance (previous_contact_mpc starts at [1,1,1,1]): its block is zeroed
+    out = itf.compute_control(state, ref, seq, cfg.inertia, np.array([0.1, 0.6, 0.6, 0.1]), 1.4, 1)
+    call = c._handle.call
+    n = c.num_control_parameters_single_leg
+    assert call["iterations"] == 4 and call["seed"] == 42 and call["offset"] == 1
+    assert np.array_equal(c.master_key, np.array([42, 4], dtype=np.uint64))
+    assert np.all(call["best_in"][2 * n:3 * n] == 0) and np.all(call["best_in"][:2 * n] == 1)
+    assert np.array_equal(call["state"][18:21], ref["ref_foot_RL"][0])  # swing foot takes its reference foothold
+    if method == "cem_mppi":
+        assert np.all(call["sigma_in"] == cfg.mpc_params["sigma_cem_mppi"]) and call["timing"] is None
+        assert np.all(c.sigma_cem_mppi == 0.5)
+    else:
+        assert np.allclose(call["timing"], [0.1, 0.6, 0.6, 0.1]) and call["nominal_freq"] == 1.4
+        assert call["optimize_swing"] == 1 and call["sigma_in"] is None
+    grfs, footholds, jp, jv, ja, freq, pred = out
+    assert np.array_equal(grfs.FL, [0, 1, 2]) and np.array_equal(grfs.RL, [0, 0, 0]) and np.array_equal(grfs.RR, [9, 10, 11])
+    assert np.array_equal(footholds.FR, ref["ref_foot_FR"][0]) and jp is None and jv is None and ja is None
+    assert freq == 2.0 and np.all(pred == 7.0) and np.all(c.best_control_parameters == 2.0)
+    assert np.array_equal(itf.previous_contact_mpc, [1, 1, 0, 1])
+    # second control step: the key keeps advancing, nothing is zeroed (no new lift-off)
+    itf.compute_control(state, ref, seq, cfg.inertia, np.array([0.1, 0.6, 0.6, 0.1]), 1.4, 1)
+    assert c._handle.call["offset"] == 5 and np.all(c._handle.call["best_in"] == 2.0)
+
+
+def test_interface_rejects_non_sampling_types():
+    from quadruped_pympc_tamols_b200.interfaces.srbd_controller_interface import SRBDControllerInterface
+    with pytest.raises(NotImplementedError, match="sampling"):
+        SRBDControllerInterface(config=make_config("go2", type="nominal"))
