@@ -347,8 +347,38 @@ def run_batched(torch, _cabi, dev, local_rank, rank, world, barrier, max_over_ra
     step_ms = max_over_ranks(float((roll[:, 0] + roll[:, 1]).mean()))
     roll_ms = max_over_ranks(float(roll[:, 0].mean()))
     ach = FLOP_PER_ROLLOUT["zero_order"] * R * n / (roll_ms * 1e-3) / 1e12
+    # ---- the step in front of the rollouts, contact sequences of this rank's robots from R gait clocks
+    from quadruped_pympc_tamols_b200.helpers.periodic_gait_generator import PeriodicGaitGenerator
+    from oracle import gait_oracle as go  # CPU leg only
+    gen = PeriodicGaitGenerator(rng.uniform(0.5, 0.8, R), rng.uniform(1.0, 2.4, R), rng.integers(0, 7, R), 12,
+                                num_robots=R, handle=h)
+    ph0 = rng.uniform(0, 1, (R, 4))
+    gen.set_phase_signal(ph0)
+    gait_ms = []
+    with torch.cuda.stream(stream):
+        for it in range(13):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            gen.compute_contact_sequence([0.02], [12])
+            e1.record(stream)
+            e1.synchronize()
+            if it >= 3:
+                gait_ms.append(e0.elapsed_time(e1))
+    gait = {"workload": f"contact sequences [R,4,12] of {R} gait clocks per rank (PeriodicGaitGenerator.compute_contact_sequence)",
+            "p50_ms": float(np.median(gait_ms)), "sequences_per_s": robots_total / (max_over_ranks(float(np.median(gait_ms))) * 1e-3),
+            "algorithmic_bytes": R * (4 * 8 + 4 + 4 * 8 + 8 + 8 + 1 + 4 * 12 * 4),
+            "note": "2.3 MB of traffic per launch: launch-latency-bound, HBM time at the measured peak is 0.35 us"}
+    if rank == 0 and world == 1:
+        t0 = time.perf_counter()
+        reps = 0
+        while time.perf_counter() - t0 < 2.0:
+            go.contact_sequences(ph0, np.zeros((R, 4), bool), gen.phase_offset, gen.step_freq, gen.duty_factor,
+                                 go.expand_dts([0.02], [12], 12))
+            reps += 1
+        gait["cpu_numpy_ms"] = (time.perf_counter() - t0) / reps * 1e3
     h.close()
     return {"workload": f"C5: {robots_total} robots x {n} rollouts, MPPI zero_order (P=144), aliengo trot; {R} robots per rank",
+            "gait_clock": gait,
             "value": robots_total * n / (step_ms * 1e-3), "unit": "rollouts/s", "robot_solves_per_s": robots_total / (step_ms * 1e-3),
             "ms_per_step": step_ms, "scaling": "strong",
             "roofline": {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak,

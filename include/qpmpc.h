@@ -174,6 +174,31 @@ int qpmpc_profile_last(qpmpc_handle *h, float *rollout_ms, float *finalize_ms);
  * the rollout kernel's roofline (nothing here is a dense contraction, so tensor-core peaks do not apply). */
 int qpmpc_measure_fp32_peak(int32_t device, float *tflops);
 
+/* ---- the periodic gait clock for a batch of robots, the step in front of the rollouts.
+ * Replaces PeriodicGaitGenerator.run / compute_contact_sequence (helpers/periodic_gait_generator.py:47-76, 93-114)
+ * looped in Python over the robots; float64 like the reference, contact flags bit-exact.
+ * All pointers are DEVICE pointers with `num_robots` leading rows; legs in FL, FR, RL, RR order. */
+typedef struct qpmpc_gait_batch {
+    int32_t num_robots;
+    int32_t horizon;                 /* columns of the contact sequence (<= QPMPC_MAX_H) */
+    double *d_phase;                 /* [R,4] phase signals in [0,1)            (_phase_signal) */
+    uint8_t *d_init;                 /* [R,4] 1 while a leg still waits for its phase offset (_init) */
+    const double *d_phase_offset;    /* [R,4] per-gait leg delays               (phase_offset, :24-39) */
+    const double *d_step_freq;       /* [R]   step frequency                    (step_freq) */
+    const double *d_duty_factor;     /* [R]   duty factor */
+    const uint8_t *d_full_stance;    /* [R]   1 = GaitType.FULL_STANCE: all ones (:95-98), or NULL */
+    double step_dts[QPMPC_MAX_H];    /* dt of column i (entry 0 unused): contact_sequence_dts / _lenghts expanded
+                                        with the reference's rule (:104-110) */
+    float *d_contact;                /* out: [R,4,horizon] for qpmpc_contact_sequences (the layout of
+                                        qpmpc_batch.d_contact_sequence), [R,4] for qpmpc_gait_run */
+} qpmpc_gait_batch;
+
+/* compute_contact_sequence for every robot: column 0 = run(0.0, f), column i = run(step_dts[i], f); the clocks
+ * (d_phase, d_init) are left untouched, as upstream restores them (:112).  Asynchronous on the handle's stream. */
+int qpmpc_contact_sequences(qpmpc_handle *h, const qpmpc_gait_batch *g);
+/* run(dt, step_freq) for every robot: advances d_phase / d_init in place and writes the current contact flags. */
+int qpmpc_gait_run(qpmpc_handle *h, const qpmpc_gait_batch *g, double dt);
+
 #ifdef __cplusplus
 }
 #endif

@@ -56,9 +56,18 @@ class QpmpcBatch(C.Structure):
                 ("d_sigma_out", C.c_void_p), ("d_costs", C.c_void_p)]
 
 
+MAX_H = 32  # QPMPC_MAX_H
+
+
+class QpmpcGaitBatch(C.Structure):  # include/qpmpc.h: qpmpc_gait_batch
+    _fields_ = [("num_robots", C.c_int32), ("horizon", C.c_int32), ("d_phase", C.c_void_p), ("d_init", C.c_void_p),
+                ("d_phase_offset", C.c_void_p), ("d_step_freq", C.c_void_p), ("d_duty_factor", C.c_void_p),
+                ("d_full_stance", C.c_void_p), ("step_dts", C.c_double * MAX_H), ("d_contact", C.c_void_p)]
+
+
 EXPORTS = ["qpmpc_create", "qpmpc_destroy", "qpmpc_num_params", "qpmpc_last_error", "qpmpc_version", "qpmpc_stream",
            "qpmpc_launch_count", "qpmpc_solve", "qpmpc_solve_iterated", "qpmpc_solve_batched", "qpmpc_rollout_costs", "qpmpc_generate_noise", "qpmpc_set_profiling", "qpmpc_profile_last",
-           "qpmpc_measure_fp32_peak"]
+           "qpmpc_measure_fp32_peak", "qpmpc_contact_sequences", "qpmpc_gait_run"]
 
 
 def build(force=False):
@@ -101,6 +110,8 @@ def lib():
         L.qpmpc_set_profiling.argtypes = [vp, C.c_int32]
         L.qpmpc_profile_last.argtypes = [vp, fp, fp]
         L.qpmpc_measure_fp32_peak.argtypes = [C.c_int32, fp]
+        L.qpmpc_contact_sequences.argtypes = [vp, C.POINTER(QpmpcGaitBatch)]
+        L.qpmpc_gait_run.argtypes = [vp, C.POINTER(QpmpcGaitBatch), C.c_double]
         _LIB = L
     return _LIB
 
@@ -226,6 +237,12 @@ class Handle:
 
     def solve_batched(self, batch: QpmpcBatch, seed, offset):
         check(lib().qpmpc_solve_batched(self._h, C.byref(batch), int(seed), int(offset)))
+
+    def contact_sequences(self, gait_batch: QpmpcGaitBatch):
+        check(lib().qpmpc_contact_sequences(self._h, C.byref(gait_batch)))
+
+    def gait_run(self, gait_batch: QpmpcGaitBatch, dt):
+        check(lib().qpmpc_gait_run(self._h, C.byref(gait_batch), float(dt)))
 
     def rollout_costs(self, state, reference, contact_sequence, d_params, n, d_costs, timing=None, d_freqs=None):
         st, rf, cs = _f32(state).reshape(24), _f32(reference).reshape(24), _f32(contact_sequence)

@@ -1070,6 +1070,46 @@ __global__ void k_dump_noise(const __grid_constant__ DevCfg c, NoiseKey key, uin
     if (freqs_out && c.ga && idx < c.N) freqs_out[idx] = freq_sample(c, key, (int)idx, robot, nominal, oswing);
 }
 
+// ---------------------------------------------------------------- gait clock --------------
+// One thread per (robot, leg).  periodic_gait_generator.py:47-76: phase += dt * f, wrap to [0, 1), a leg in the init
+// hold stays in contact until its phase passes its offset (then restarts at 0), otherwise contact = phase < duty.
+// Separately rounded product and sum (Python floats), exact fmod.
+__device__ __forceinline__ float gait_run(double &phase, bool &init, double offset, double duty, double dt, double f) {
+    phase = __dadd_rn(phase, __dmul_rn(dt, f));
+    phase = fmod(phase, 1.0);
+    if (phase < 0.0) phase = __dadd_rn(phase, 1.0);  // Python's % takes the divisor's sign
+    if (init) {
+        if (!(phase <= offset)) {
+            init = false;
+            phase = 0.0;
+        }
+        return 1.0f;
+    }
+    return phase < duty ? 1.0f : 0.0f;
+}
+
+// steps > 0: contact sequence of `steps` columns, clock state NOT stored; steps == 0: one run(dt), state stored
+__global__ void k_gait(const __grid_constant__ qpmpc_gait_batch g, int steps, double dt) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= g.num_robots * 4) return;
+    const int r = idx >> 2;
+    double phase = g.d_phase[idx];
+    bool init = g.d_init[idx] != 0;
+    const double offset = g.d_phase_offset[idx], duty = g.d_duty_factor[r], f = g.d_step_freq[r];
+    if (steps == 0) {
+        g.d_contact[idx] = gait_run(phase, init, offset, duty, dt, f);
+        g.d_phase[idx] = phase;
+        g.d_init[idx] = init ? 1 : 0;
+        return;
+    }
+    const bool full = g.d_full_stance != nullptr && g.d_full_stance[r] != 0;
+    float *out = g.d_contact + (size_t)idx * steps;
+    for (int n = 0; n < steps; ++n) {
+        const float c = gait_run(phase, init, offset, duty, n == 0 ? 0.0 : g.step_dts[n], f);
+        out[n] = full ? 1.0f : c;
+    }
+}
+
 }  // namespace qp
 
 // ================================================================ host side ================================
@@ -1604,6 +1644,35 @@ extern "C" int qpmpc_profile_last(qpmpc_handle *h, float *rollout_ms, float *fin
     CU(cudaEventSynchronize(h->ev[2]));
     CU(cudaEventElapsedTime(rollout_ms, h->ev[0], h->ev[1]));
     CU(cudaEventElapsedTime(finalize_ms, h->ev[1], h->ev[2]));
+    return QPMPC_OK;
+}
+
+static int gait_check(qpmpc_handle *h, const qpmpc_gait_batch *g) {
+    if (!h || !g) return fail(QPMPC_E_ARG, "null argument");
+    if (g->num_robots < 1) return fail(QPMPC_E_ARG, "num_robots must be >= 1");
+    if (!g->d_phase || !g->d_init || !g->d_phase_offset || !g->d_step_freq || !g->d_duty_factor || !g->d_contact)
+        return fail(QPMPC_E_ARG, "missing device pointer in qpmpc_gait_batch");
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_contact_sequences(qpmpc_handle *h, const qpmpc_gait_batch *g) {
+    if (int rc = gait_check(h, g)) return rc;
+    if (g->horizon < 1 || g->horizon > QPMPC_MAX_H) return fail(QPMPC_E_ARG, "horizon out of range [1, 32]");
+    CU(cudaSetDevice(h->device));
+    const int threads = 128, blocks = (g->num_robots * 4 + threads - 1) / threads;
+    k_gait<<<blocks, threads, 0, h->stream>>>(*g, g->horizon, 0.0);
+    CU(cudaGetLastError());
+    h->launches += 1;
+    return QPMPC_OK;
+}
+
+extern "C" int qpmpc_gait_run(qpmpc_handle *h, const qpmpc_gait_batch *g, double dt) {
+    if (int rc = gait_check(h, g)) return rc;
+    CU(cudaSetDevice(h->device));
+    const int threads = 128, blocks = (g->num_robots * 4 + threads - 1) / threads;
+    k_gait<<<blocks, threads, 0, h->stream>>>(*g, 0, dt);
+    CU(cudaGetLastError());
+    h->launches += 1;
     return QPMPC_OK;
 }
 
