@@ -383,7 +383,9 @@ def run_batched(torch, _cabi, dev, local_rank, rank, world, barrier, max_over_ra
             "ms_per_step": step_ms, "scaling": "strong",
             "roofline": {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak,
                          "traffic": 31212032 // world, "traffic_source": "profiles/r2h_ncu_raw_c5.csv (dram read + write bytes per launch at 8192 robots)",
-                         "kernel": "k_rollout<zero_order,fixed,128>", "launch_ms": roll_ms, "flop_per_rollout": FLOP_PER_ROLLOUT["zero_order"]}}
+                         "kernel": "k_rollout<zero_order,fixed,128>", "launch_ms": roll_ms, "flop_per_rollout": FLOP_PER_ROLLOUT["zero_order"],
+                         "ncu": {"source": "profiles/r2h_ncu_raw_c5.csv (one launch, not this run)", "fma_pipe_pct_of_peak": 34.9, "alu_pipe_pct": 30.8, "xu_pipe_pct": 20.7,
+                                 "issue_slots_busy_pct": 61.8, "warp_instructions_per_rollout": 8160, "active_warps_per_scheduler": 2.97}}}
 
 
 def run_tamols(torch, dev, local_rank, rank, world, barrier, max_over_ranks, with_cpu):
