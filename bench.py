@@ -457,6 +457,36 @@ def run_tamols(torch, dev, local_rank, rank, world, barrier, max_over_ranks, wit
     ms = timed(h, lambda: h.score_device(d_h.data_ptr(), tc.F64, 1, 2048, 2048, 2048, d_jobs.data_ptr(), 4 * R, w, w,
                                          d_res.data_ptr()), 20)
     launches = h.launch_count
+    # ---- robot states -> seed footholds -> job records -> scores, all on the device (two launches)
+    from quadruped_pympc_tamols_b200.helpers.foothold_reference_generator import FootholdReferenceGenerator
+    from oracle import seed_oracle as seo  # CPU leg only
+    prng = np.random.default_rng(17 + rank)
+    pos = np.c_[prng.uniform(-15, 15, (R, 2)), np.full(R, 0.3)]
+    eul = np.c_[prng.normal(0, 0.03, (R, 2)), prng.uniform(-3.1, 3.1, R)]
+    vel, refv = prng.normal(0, 0.4, (R, 3)), np.c_[prng.normal(0.4, 0.3, R), prng.normal(0, 0.1, R), np.zeros(R)]
+    hips = pos[:, None, :] + np.array([[0.19, 0.13, 0.0], [0.19, -0.13, 0.0], [-0.19, 0.13, 0.0], [-0.19, -0.13, 0.0]])
+    feet = hips - np.array([0.0, 0.0, 0.3])
+    gen = FootholdReferenceGenerator(0.4, np.zeros((R, 4, 3)), 20, 0.3, num_robots=R, handle=h)
+    t_in = [torch.as_tensor(a, dtype=torch.float64, device=dev) for a in (pos, eul, vel, refv, hips, np.full(R, 0.3), feet)]
+    d_pj = torch.zeros(4 * R * tc.JOB_DTYPE.itemsize, dtype=torch.uint8, device=dev)
+    gmap = (2048, 2048, sc["origin"], sc["row_axis"], sc["col_axis"])
+
+    def pipeline():
+        gen.compute_footholds_reference(t_in[0], t_in[1], t_in[2], t_in[3], t_in[4], t_in[5], feet_position=t_in[6],
+                                        global_map=gmap, window=(w, w), jobs_out=d_pj)
+        h.score_device(d_h.data_ptr(), tc.F64, 1, 2048, 2048, 2048, d_pj.data_ptr(), 4 * R, w, w, d_res.data_ptr())
+
+    pms = timed(h, pipeline, 10)
+    sms = timed(h, lambda: gen.compute_footholds_reference(t_in[0], t_in[1], t_in[2], t_in[3], t_in[4], t_in[5],
+                                                           feet_position=t_in[6], global_map=gmap, window=(w, w),
+                                                           jobs_out=d_pj), 10)
+    out["pipeline"] = {"workload": f"{R} robots per rank: states -> seed footholds -> tamols_leg_job records -> scores ({w}x{w} windows) on the device",
+                       "total_ms": float(np.median(pms)), "seed_jobs_ms": float(np.median(sms)), "launches_per_step": 2}
+    if with_cpu:
+        t0 = time.perf_counter()
+        seo.seed_footholds(pos, eul, vel, refv, hips, np.full(R, 0.3), np.full(R, 0.4), np.zeros((R, 4)),
+                           [[] for _ in range(R)], 0.3)
+        out["pipeline"]["cpu_seed_oracle_ms"] = (time.perf_counter() - t0) * 1e3
     h.close()
     step_ms = max_over_ranks(float(ms.mean()))
     cand = robots_total * 4 * w * w

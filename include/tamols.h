@@ -120,6 +120,42 @@ int tamols_score_host(tamols_handle *h, const double *heights, int32_t num_maps,
                       const double *xy, const tamols_leg_job *jobs, int32_t n_jobs, tamols_result *results,
                       double *scores, int64_t scores_stride);
 
+/* ---- the step in front of the scoring, for a batch of robots on the device.
+ * (a) FootholdReferenceGenerator.compute_footholds_reference (helpers/foothold_reference_generator.py:53-157): hip
+ *     positions in the yaw-aligned frame, +-hip_offset, desired-velocity offset stance_time/2 * v_ref clipped to
+ *     +-1.5 hip_height, velocity-error compensation sqrt(h/g) (mean of the last `hist_len` velocities - v_ref) clipped
+ *     to +-0.05, back to the world frame, manual CoM offset, z = lift-off height.  The moving-average deque is the
+ *     ring d_vel_hist / d_hist_count (state, advanced by every call).
+ * (b) when d_jobs != NULL: the 4 R tamols_leg_job records of those seeds on ONE global regular height map -- the
+ *     candidate window of a leg is win_rows x win_cols cells centred on the cell nearest to its seed (clamped to the
+ *     map), replacing the per-leg HeightMap.update_height_map ray-cast grids of wb_interface.py:233-234; flags, hip,
+ *     diagonal foot, base and velocity exactly as VisualFootholdAdaptation.compute_adaptation assembles them.
+ * All pointers are DEVICE pointers with num_robots leading rows; legs in FL, FR, RL, RR order; float64. */
+typedef struct tamols_seed_batch {
+    int32_t num_robots;
+    int32_t hist_len;                /* vel_moving_average_length (20) */
+    const double *d_base_position;   /* [R,3] */
+    const double *d_base_euler;      /* [R,3] roll, pitch, yaw */
+    const double *d_base_lin_vel;    /* [R,3] world frame */
+    const double *d_ref_lin_vel;     /* [R,3] world frame (x, y used) */
+    const double *d_hips;            /* [R,4,3] hip positions, world frame */
+    const double *d_feet;            /* [R,4,3] current feet positions (job building only), or NULL */
+    const uint8_t *d_contact;        /* [R,4] 1 = stance (job building only), or NULL = all swing */
+    const double *d_com_height;      /* [R] com_height_nominal */
+    const double *d_stance_time;     /* [R] */
+    const double *d_lift_off_z;      /* [R,4] lift_off_positions[leg][2] */
+    const double *d_com_offset_b;    /* [R,3] com_pos_offset_b, or NULL (zeros) */
+    double *d_vel_hist;              /* [R,hist_len,2] state */
+    int32_t *d_hist_count;           /* [R] state: velocities pushed so far */
+    double hip_height, hip_offset, gravity;
+    double *d_ref_feet;              /* out [R,4,3] */
+    tamols_leg_job *d_jobs;          /* out [4 R] or NULL */
+    int32_t map_rows, map_cols, win_rows, win_cols;
+    double map_origin[2], map_row_axis[2], map_col_axis[2];
+} tamols_seed_batch;
+
+int tamols_seed_jobs(tamols_handle *h, const tamols_seed_batch *b);
+
 #ifdef __cplusplus
 }
 #endif

@@ -265,6 +265,12 @@ class LegsAttr:
     def __setitem__(self, k, v):
         setattr(self, k if isinstance(k, str) else ("FL", "FR", "RL", "RR")[k], v)
 
+    def __add__(self, other):  # gym_quadruped's LegsAttr adds an array (or another LegsAttr) to every leg
+        o = (lambda k: getattr(other, k)) if isinstance(other, LegsAttr) else (lambda k: other)
+        return LegsAttr(*[getattr(self, k) + o(k) for k in ("FL", "FR", "RL", "RR")])
+
+    __iadd__ = __add__
+
 
 def install_robot_stubs(hip_height=0.33):
     """gym_quadruped / mujoco.viewer stubs needed to import quadruped_pympc.config (config.py:11-16,

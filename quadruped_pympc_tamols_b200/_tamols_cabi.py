@@ -48,8 +48,20 @@ RESULT_DTYPE = np.dtype([("best_index", "<i4"), ("num_finite", "<i4"), ("best_sc
                          ("vertex1", "<f8", 3), ("vertex2", "<f8", 3)])
 assert JOB_DTYPE.itemsize == C.sizeof(TamolsLegJob) and RESULT_DTYPE.itemsize == C.sizeof(TamolsResult)
 
+class TamolsSeedBatch(C.Structure):  # include/tamols.h: tamols_seed_batch
+    _fields_ = [("num_robots", C.c_int32), ("hist_len", C.c_int32),
+                ("d_base_position", C.c_void_p), ("d_base_euler", C.c_void_p), ("d_base_lin_vel", C.c_void_p),
+                ("d_ref_lin_vel", C.c_void_p), ("d_hips", C.c_void_p), ("d_feet", C.c_void_p), ("d_contact", C.c_void_p),
+                ("d_com_height", C.c_void_p), ("d_stance_time", C.c_void_p), ("d_lift_off_z", C.c_void_p),
+                ("d_com_offset_b", C.c_void_p), ("d_vel_hist", C.c_void_p), ("d_hist_count", C.c_void_p),
+                ("hip_height", C.c_double), ("hip_offset", C.c_double), ("gravity", C.c_double),
+                ("d_ref_feet", C.c_void_p), ("d_jobs", C.c_void_p),
+                ("map_rows", C.c_int32), ("map_cols", C.c_int32), ("win_rows", C.c_int32), ("win_cols", C.c_int32),
+                ("map_origin", C.c_double * 2), ("map_row_axis", C.c_double * 2), ("map_col_axis", C.c_double * 2)]
+
+
 EXPORTS = ["tamols_create", "tamols_destroy", "tamols_set_params", "tamols_last_error", "tamols_stream",
-           "tamols_launch_count", "tamols_score_device", "tamols_score_host"]
+           "tamols_launch_count", "tamols_score_device", "tamols_score_host", "tamols_seed_jobs"]
 
 
 def make_params(tamols_params=None, robot_name="aliengo"):
@@ -120,6 +132,7 @@ def lib():
         L.tamols_score_device.argtypes = [vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp, vp,
                                           C.c_int32, C.c_int32, C.c_int32, vp, vp, C.c_int64]
         L.tamols_score_host.argtypes = [vp, vp, C.c_int32, C.c_int32, C.c_int32, vp, vp, C.c_int32, vp, vp, C.c_int64]
+        L.tamols_seed_jobs.argtypes = [vp, C.POINTER(TamolsSeedBatch)]
         _BOUND = True
     return L
 
@@ -135,6 +148,7 @@ class Handle:
     def __init__(self, params: TamolsParams, device=0, max_jobs=4):
         self._h = C.c_void_p()
         self.params = params
+        self.device = int(device)
         check(lib().tamols_create(C.byref(params), int(device), int(max_jobs), C.byref(self._h)))
 
     def close(self):
@@ -176,6 +190,10 @@ class Handle:
         check(lib().tamols_score_host(self._h, hm.ctypes.data, M, R, Cc, xyp, jb.ctypes.data, n, res.ctypes.data,
                                       scores.ctypes.data if scores is not None else None, stride))
         return res, scores
+
+    def seed_jobs(self, batch: TamolsSeedBatch):
+        """Seed footholds (and job records) of a batch of robots; asynchronous on self.stream."""
+        check(lib().tamols_seed_jobs(self._h, C.byref(batch)))
 
     def score_device(self, d_heights, height_dtype, num_maps, rows, cols, pitch, d_jobs, n_jobs, max_nr, max_nc,
                      d_results, d_xy=None, d_scores=None, scores_stride=0):

@@ -455,6 +455,99 @@ __global__ void __launch_bounds__(THREADS, TH == 32 ? 4 : 2) k_tamols_score(cons
     }
 }
 
+// ---------------------------------------------------------------- seed footholds + job records
+// One thread per robot.  foothold_reference_generator.py:84-157 in its operation order (float64, no contraction).
+__global__ void k_seed_jobs(const __grid_constant__ tamols_seed_batch b) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= b.num_robots) return;
+    const double *bp = b.d_base_position + 3 * r, *eu = b.d_base_euler + 3 * r;
+    const double *v = b.d_base_lin_vel + 3 * r, *vr = b.d_ref_lin_vel + 3 * r;
+    const double cy = cos(eu[2]), sy = sin(eu[2]);
+    // R_W2H = [[cy, sy], [-sy, cy]]
+    const double vhx = cy * v[0] + sy * v[1], vhy = -sy * v[0] + cy * v[1];
+    const double rhx = cy * vr[0] + sy * vr[1], rhy = -sy * vr[0] + cy * vr[1];
+    // deque(maxlen = hist_len).append, then the mean in deque order (oldest first)
+    const int L = b.hist_len;
+    double *hist = b.d_vel_hist + (size_t)r * L * 2;
+    const int cnt = b.d_hist_count[r];
+    hist[2 * (cnt % L)] = vhx;
+    hist[2 * (cnt % L) + 1] = vhy;
+    b.d_hist_count[r] = cnt + 1;
+    const int n = min(cnt + 1, L), first = (cnt + 1 > L) ? (cnt + 1) % L : 0;
+    double mx = 0.0, my = 0.0;
+    for (int k = 0; k < n; ++k) {
+        const int s = (first + k) % L;
+        mx += hist[2 * s];
+        my += hist[2 * s + 1];
+    }
+    mx /= (double)n;
+    my /= (double)n;
+    const double half = b.d_stance_time[r] / 2.0, lim = b.hip_height * 1.5;
+    const double dx = fmin(fmax(half * rhx, -lim), lim), dy = fmin(fmax(half * rhy, -lim), lim);
+    const double k = sqrt(b.d_com_height[r] / b.gravity);
+    double ex = k * (mx - rhx), ey = k * (my - rhy);
+    ex = ex > 0.05 ? 0.05 : ex;
+    ex = ex < -0.05 ? -0.05 : ex;
+    ey = ey > 0.05 ? 0.05 : ey;
+    ey = ey < -0.05 ? -0.05 : ey;
+    const double ox = dx + ex, oy = dy + ey;  // vel_offset + error_compensation
+    // manual CoM offset: Rotation.from_euler("xyz", euler).as_matrix() @ com_pos_offset_b, x and y rows
+    double cwx = 0.0, cwy = 0.0;
+    if (b.d_com_offset_b != nullptr) {
+        const double *co = b.d_com_offset_b + 3 * r;
+        const double cr = cos(eu[0]), sr = sin(eu[0]), cp = cos(eu[1]), sp = sin(eu[1]);
+        cwx = cp * cy * co[0] + (sr * sp * cy - cr * sy) * co[1] + (cr * sp * cy + sr * sy) * co[2];
+        cwy = cp * sy * co[0] + (sr * sp * sy + cr * cy) * co[1] + (cr * sp * sy - sr * cy) * co[2];
+    }
+    for (int l = 0; l < 4; ++l) {
+        const double *hp = b.d_hips + (size_t)(4 * r + l) * 3;
+        const double px = hp[0] - bp[0], py = hp[1] - bp[1];
+        double fx = cy * px + sy * py, fy = -sy * px + cy * py;
+        fy += (l & 1) ? -b.hip_offset : b.hip_offset;  // FL, RL: +, FR, RR: -
+        fx += ox;
+        fy += oy;
+        double wx = (cy * fx - sy * fy) + bp[0], wy = (sy * fx + cy * fy) + bp[1];  // R_W2H.T @ f + base
+        wx += cwx;
+        wy += cwy;
+        const double wz = b.d_lift_off_z[4 * r + l];
+        double *out = b.d_ref_feet + (size_t)(4 * r + l) * 3;
+        out[0] = wx;
+        out[1] = wy;
+        out[2] = wz;
+        if (b.d_jobs == nullptr) continue;
+        tamols_leg_job j;
+        j.map = 0;
+        // nearest cell of the seed in grid coordinates, window centred on it and clamped to the map
+        const double qx = wx - b.map_origin[0], qy = wy - b.map_origin[1];
+        const double r2 = b.map_row_axis[0] * b.map_row_axis[0] + b.map_row_axis[1] * b.map_row_axis[1];
+        const double c2 = b.map_col_axis[0] * b.map_col_axis[0] + b.map_col_axis[1] * b.map_col_axis[1];
+        const int ri = (int)rint((qx * b.map_row_axis[0] + qy * b.map_row_axis[1]) / r2);
+        const int ci = (int)rint((qx * b.map_col_axis[0] + qy * b.map_col_axis[1]) / c2);
+        j.nr = min(b.win_rows, b.map_rows);
+        j.nc = min(b.win_cols, b.map_cols);
+        j.r0 = min(max(ri - j.nr / 2, 0), b.map_rows - j.nr);
+        j.c0 = min(max(ci - j.nc / 2, 0), b.map_cols - j.nc);
+        j.origin[0] = b.map_origin[0]; j.origin[1] = b.map_origin[1];
+        j.row_axis[0] = b.map_row_axis[0]; j.row_axis[1] = b.map_row_axis[1];
+        j.col_axis[0] = b.map_col_axis[0]; j.col_axis[1] = b.map_col_axis[1];
+        j.seed[0] = wx; j.seed[1] = wy; j.seed[2] = wz;
+        j.hip[0] = hp[0]; j.hip[1] = hp[1]; j.hip[2] = hp[2];
+        j.vel[0] = v[0]; j.vel[1] = v[1]; j.vel[2] = v[2];
+        int flags = TAMOLS_FLAG_HAS_VELOCITY;
+        j.base_xy[0] = j.base_xy[1] = j.diag_foot[0] = j.diag_foot[1] = 0.0;
+        const bool stance = b.d_contact != nullptr && b.d_contact[4 * r + l] == 1;
+        if (b.d_feet != nullptr && !stance) {  // visual_foothold_adaptation.py:631-664: swing leg, diagonal partner
+            const int d = 3 - l;                // FL <-> RR, FR <-> RL
+            const double *df = b.d_feet + (size_t)(4 * r + d) * 3;
+            flags |= TAMOLS_FLAG_STABILITY;
+            j.base_xy[0] = bp[0]; j.base_xy[1] = bp[1];
+            j.diag_foot[0] = df[0]; j.diag_foot[1] = df[1];
+        }
+        j.flags = flags;
+        b.d_jobs[4 * r + l] = j;
+    }
+}
+
 }  // namespace tamols
 
 // ================================================================ host side ================================
@@ -762,5 +855,21 @@ extern "C" int tamols_score_host(tamols_handle *h, const double *heights, int32_
             for (int64_t i = n; i < scores_stride; ++i) dst[i] = INFINITY;
         }
     }
+    return TAMOLS_OK;
+}
+
+extern "C" int tamols_seed_jobs(tamols_handle *h, const tamols_seed_batch *b) {
+    if (!h || !b) return tfail(TAMOLS_E_ARG, "null argument");
+    if (b->num_robots < 1 || b->hist_len < 1) return tfail(TAMOLS_E_ARG, "num_robots and hist_len must be >= 1");
+    if (!b->d_base_position || !b->d_base_euler || !b->d_base_lin_vel || !b->d_ref_lin_vel || !b->d_hips ||
+        !b->d_com_height || !b->d_stance_time || !b->d_lift_off_z || !b->d_vel_hist || !b->d_hist_count || !b->d_ref_feet)
+        return tfail(TAMOLS_E_ARG, "missing device pointer in tamols_seed_batch");
+    if (b->d_jobs && (b->map_rows < 1 || b->map_cols < 1 || b->win_rows < 1 || b->win_cols < 1))
+        return tfail(TAMOLS_E_ARG, "bad map / window shape");
+    TCU(cudaSetDevice(h->device));
+    const int threads = 128, blocks = (b->num_robots + threads - 1) / threads;
+    k_seed_jobs<<<blocks, threads, 0, h->stream>>>(*b);
+    TCU(cudaGetLastError());
+    h->launches += 1;
     return TAMOLS_OK;
 }
