@@ -375,46 +375,54 @@ __global__ void __launch_bounds__(THREADS, TH == 32 ? 4 : 2) k_tamols_score(cons
             argmin_combine(s, idx, s_rs[w], s_ri[w]);
             nfin += s_rn[w];
         }
-        Partial &pt = a.partials[(long long)job * a.max_tiles + blockIdx.x];
-        pt.score = s;
-        pt.index = idx;
-        pt.nfinite = nfin;
-        __threadfence();
-        s_ticket = atomicAdd(&a.tickets[job], 1u);
-    }
-    __syncthreads();
-    if (s_ticket != (unsigned)(ntiles - 1)) return;
-
-    // ---- last block of this job: merge the tile partials, write the result (:209-222)
-    __threadfence();
-    s = inf;
-    idx = 0x7fffffff;
-    nfin = 0;
-    for (int b = t; b < ntiles; b += THREADS) {
-        // written by other blocks: read through L2 (ld.global.cg), not this SM's L1
-        const int4 raw = __ldcg(reinterpret_cast<const int4 *>(a.partials + (long long)job * a.max_tiles + b));
-        argmin_combine(s, idx, __hiloint2double(raw.y, raw.x), raw.z);
-        nfin += raw.w;
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        const double os = __shfl_xor_sync(0xffffffffu, s, o);
-        const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
-        argmin_combine(s, idx, os, oi);
-        nfin += __shfl_xor_sync(0xffffffffu, nfin, o);
-    }
-    __syncthreads();
-    if ((t & 31) == 0) {
-        s_rs[t >> 5] = s;
-        s_ri[t >> 5] = idx;
-        s_rn[t >> 5] = nfin;
-    }
-    __syncthreads();
-    if (t == 0) {
-        for (int w = 1; w < THREADS / 32; ++w) {
-            argmin_combine(s, idx, s_rs[w], s_ri[w]);
-            nfin += s_rn[w];
+        if (ntiles > 1) {
+            Partial &pt = a.partials[(long long)job * a.max_tiles + blockIdx.x];
+            pt.score = s;
+            pt.index = idx;
+            pt.nfinite = nfin;
+            __threadfence();
+            s_ticket = atomicAdd(&a.tickets[job], 1u);
         }
+    }
+    // A job that fits ONE tile (one robot's 13 x 7 sensor maps) is finished here: thread 0 already holds its
+    // (score, index, count) -- no partial, no fence, no ticket, no merge (three dependent memory round trips less).
+    if (ntiles > 1) {
+        __syncthreads();
+        if (s_ticket != (unsigned)(ntiles - 1)) return;
+
+        // ---- last block of this job: merge the tile partials (:209-222)
+        __threadfence();
+        s = inf;
+        idx = 0x7fffffff;
+        nfin = 0;
+        for (int b = t; b < ntiles; b += THREADS) {
+            // written by other blocks: read through L2 (ld.global.cg), not this SM's L1
+            const int4 raw = __ldcg(reinterpret_cast<const int4 *>(a.partials + (long long)job * a.max_tiles + b));
+            argmin_combine(s, idx, __hiloint2double(raw.y, raw.x), raw.z);
+            nfin += raw.w;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double os = __shfl_xor_sync(0xffffffffu, s, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+            argmin_combine(s, idx, os, oi);
+            nfin += __shfl_xor_sync(0xffffffffu, nfin, o);
+        }
+        __syncthreads();
+        if ((t & 31) == 0) {
+            s_rs[t >> 5] = s;
+            s_ri[t >> 5] = idx;
+            s_rn[t >> 5] = nfin;
+        }
+        __syncthreads();
+        if (t == 0) {
+            for (int w = 1; w < THREADS / 32; ++w) {
+                argmin_combine(s, idx, s_rs[w], s_ri[w]);
+                nfin += s_rn[w];
+            }
+        }
+    }
+    if (t == 0) {  // write the result
         // host-buffer call: the record is built locally and leaves as {word, sequence} pairs (below)
         tamols_result local;
         tamols_result &out = a.host_flag != nullptr ? local : a.results[job];
@@ -441,7 +449,7 @@ __global__ void __launch_bounds__(THREADS, TH == 32 ? 4 : 2) k_tamols_score(cons
         out.vertex1[1] -= a.p.constraint_box_dy;
         out.vertex2[0] += a.p.constraint_box_dx;
         out.vertex2[1] += a.p.constraint_box_dy;
-        a.tickets[job] = 0;  // ready for the next launch on this stream
+        if (ntiles > 1) a.tickets[job] = 0;  // ready for the next launch on this stream
         if (a.host_flag != nullptr) {
             // Results go to mapped host memory as 8-byte {word, sequence} stores: every pair carries its own arrival
             // flag, so neither a system-wide fence nor a job counter is needed; the host waits for each pair.
@@ -700,6 +708,9 @@ static int launch_score(tamols_handle *h, const void *d_heights, int dtype, int 
     // tile height: 32-row tiles once they alone give every SM a block, else 8-row tiles (latency regime)
     const long long tiles32 = (long long)n_jobs * ((max_nr + 31) / 32) * ((max_nc + TW - 1) / TW);
     int th = tiles32 >= (long long)h->num_sms ? 32 : 8;
+    // a window of at most 256 candidates that fits one 32 x 32 tile (one robot's 13 x 7 sensor maps): ONE tile per job,
+    // which finishes without the partial / ticket / merge round trips
+    if (max_nr <= 32 && max_nc <= TW && max_nr * max_nc <= THREADS && max_nr > 8) th = 32;
     if (const char *e = getenv("TAMOLS_TILE_ROWS")) th = atoi(e) == 32 ? 32 : 8;
     const int max_tiles = ((max_nr + th - 1) / th) * ((max_nc + TW - 1) / TW);
     const size_t need = (size_t)n_jobs * max_tiles;
