@@ -196,34 +196,61 @@ class Handle:
     def launch_count(self):
         return lib().qpmpc_launch_count(self._h)
 
+    def _io(self):
+        """Persistent host staging of solve(): float32 arrays whose addresses are taken ONCE (ndarray.ctypes.data costs
+        about a microsecond per access, a dozen of them per call were a third of the end-to-end latency)."""
+        io = getattr(self, "_io_cache", None)
+        if io is None:
+            P, H = self.P, self.H
+            arr = dict(st=np.zeros(24, np.float32), rf=np.zeros(24, np.float32), cs=np.zeros(4 * H, np.float32),
+                       bi=np.zeros(P, np.float32), tm=np.zeros(4, np.float32), sg=np.zeros(P, np.float32),
+                       res=np.zeros(RESULT_FLOATS, np.float32), bo=np.zeros(P, np.float32), so=np.zeros(P, np.float32))
+            ptr = {k: v.ctypes.data for k, v in arr.items()}
+            arr["cs2"] = arr["cs"].reshape(4, H)  # a view: the [4, H] shape callers pass
+            io = self._io_cache = (arr, ptr, lib().qpmpc_solve, lib().qpmpc_solve_iterated)
+        return io
+
     def solve(self, state, reference, contact_sequence, best_in, seed, offset, timing=None, nominal_freq=0.0,
               optimize_swing=0, sigma_in=None, d_eps=None, d_freqs=None, want_costs=True, iterations=1):
         """One jitted_compute_control call; host numpy in, dict of host numpy out.  iterations > 1: that many chained
         solves on the device (keys (seed, offset), (seed, offset + 1), ...; mean and sigma carried on the device,
         srbd_controller_interface.py:131-170), outputs of the last one."""
-        st, rf, cs, bi = _f32(state).reshape(24), _f32(reference).reshape(24), _f32(contact_sequence), _f32(best_in)
-        if cs.size != 4 * self.H or bi.size != self.P:
-            raise QpmpcError(f"contact_sequence must be [4,{self.H}] and best [{self.P}]")
-        tm = _f32(timing).reshape(4) if timing is not None else None
-        sg = None
+        arr, ptr, f_solve, f_iter = self._io()
+        try:  # the shapes the callers use: [24], [24], [4, H], [P]
+            arr["st"][:] = state
+            arr["rf"][:] = reference
+            arr["cs2"][:] = contact_sequence
+            arr["bi"][:] = best_in
+        except (ValueError, TypeError):  # anything else of the right size
+            cs, bi = np.asarray(contact_sequence), np.asarray(best_in)
+            if cs.size != 4 * self.H or bi.size != self.P:
+                raise QpmpcError(f"contact_sequence must be [4,{self.H}] and best [{self.P}]") from None
+            arr["st"][:] = np.asarray(state).reshape(24)
+            arr["rf"][:] = np.asarray(reference).reshape(24)
+            arr["cs"][:] = cs.reshape(-1)
+            arr["bi"][:] = bi.reshape(-1)
+        p_tm = p_sg = p_so = None
+        if timing is not None:
+            arr["tm"][:] = timing
+            p_tm = ptr["tm"]
         if sigma_in is not None:
-            sg = _f32(np.broadcast_to(np.asarray(sigma_in, np.float32), (self.P,)))
-        res = np.empty(RESULT_FLOATS, np.float32)  # qpmpc_result as 52 packed 4-byte words
-        best_out = np.empty(self.P, np.float32)
-        sigma_out = np.empty(self.P, np.float32) if sg is not None else None
+            arr["sg"][:] = sigma_in  # scalar or [P]
+            p_sg, p_so = ptr["sg"], ptr["so"]
         costs = np.empty(self.N, np.float32) if want_costs else None
+        p_costs = costs.ctypes.data if want_costs else None
         if iterations == 1:
-            check(lib().qpmpc_solve(self._h, _fp(st), _fp(rf), _fp(cs), _fp(bi), int(seed), int(offset), _fp(tm),
-                                    float(nominal_freq), int(optimize_swing), _fp(sg), d_eps, d_freqs,
-                                    _fp(res), _fp(best_out), _fp(sigma_out), _fp(costs)))
+            check(f_solve(self._h, ptr["st"], ptr["rf"], ptr["cs"], ptr["bi"], int(seed), int(offset), p_tm,
+                          float(nominal_freq), int(optimize_swing), p_sg, d_eps, d_freqs, ptr["res"], ptr["bo"], p_so,
+                          p_costs))
         else:
             if d_eps is not None or d_freqs is not None:
                 raise QpmpcError("chained iterations draw their own noise (no d_eps / d_freqs)")
-            check(lib().qpmpc_solve_iterated(self._h, _fp(st), _fp(rf), _fp(cs), _fp(bi), int(seed), int(offset),
-                                             int(iterations), _fp(tm), float(nominal_freq), int(optimize_swing), _fp(sg),
-                                             _fp(res), _fp(best_out), _fp(sigma_out), _fp(costs)))
-        return dict(grf=res[0:12], footholds=res[12:24], predicted_state=res[24:48], best=best_out,
-                    best_cost=res[48], best_freq=res[49], costs=costs, sigma=sigma_out,
+            check(f_iter(self._h, ptr["st"], ptr["rf"], ptr["cs"], ptr["bi"], int(seed), int(offset), int(iterations),
+                         p_tm, float(nominal_freq), int(optimize_swing), p_sg, ptr["res"], ptr["bo"], p_so, p_costs))
+        res = arr["res"].copy()  # fresh arrays: the caller keeps them across calls
+        return dict(grf=res[0:12], footholds=res[12:24], predicted_state=res[24:48], best=arr["bo"].copy(),
+                    best_cost=res[48], best_freq=res[49], costs=costs,
+                    sigma=arr["so"].copy() if sigma_in is not None else None,
                     best_index=int(res[50:51].view(np.int32)[0]))
 
     def set_profiling(self, on=True):
