@@ -1129,6 +1129,26 @@ static int fail(int code, const std::string &msg) {
 
 typedef void (*rollout_fn)(const qp::DevCfg, const qp::RolloutArgs, const qp::InlineIn);
 
+// Experiment switches, read from the environment ONCE per handle (qpmpc_create): five getenv calls per solve were
+// measurable on a 30 us call.  QPMPC_KERNEL=quad|thread, QPMPC_QB=32|72|128, QPMPC_FUSED=0, QPMPC_ZEROCOPY=0|1,
+// QPMPC_INPUTS=copy|mapped.
+struct EnvSwitches {
+    int kernel;    // 0 auto, 1 quad, 2 thread
+    int qb;        // 0 auto, else 32 / 72 / 128
+    int fused;     // 0: stand-alone k_finalize
+    int zerocopy;  // -1 unset, 0 classic copies, 1 inputs mapped too
+    int inputs;    // 0 auto (parameter block), 1 copy, 2 mapped
+};
+static EnvSwitches read_env() {
+    EnvSwitches e = {0, 0, 1, -1, 0};
+    if (const char *k = getenv("QPMPC_KERNEL")) e.kernel = !strcmp(k, "quad") ? 1 : !strcmp(k, "thread") ? 2 : 0;
+    if (const char *q = getenv("QPMPC_QB")) e.qb = atoi(q) == 128 ? 128 : atoi(q) == 72 ? 72 : 32;
+    if (const char *f = getenv("QPMPC_FUSED")) e.fused = f[0] == '0' ? 0 : 1;
+    if (const char *z = getenv("QPMPC_ZEROCOPY")) e.zerocopy = z[0] == '0' ? 0 : z[0] == '1' ? 1 : -1;
+    if (const char *i = getenv("QPMPC_INPUTS")) e.inputs = !strcmp(i, "copy") ? 1 : !strcmp(i, "mapped") ? 2 : 0;
+    return e;
+}
+
 struct qpmpc_handle {
     qpmpc_config cfg;
     DevCfg dc;
@@ -1136,6 +1156,7 @@ struct qpmpc_handle {
     cudaStream_t stream;
     int num_sms;
     rollout_fn fn128, fn32, fn_quad32, fn_quad72, fn_quad128;
+    EnvSwitches env;
     size_t max_smem;
     // single-robot staging: one pinned input block, one pinned output block
     float *h_in, *d_in;
@@ -1198,12 +1219,6 @@ static rollout_fn pick_quad(int param, int ga) {
         default: return k_rollout_quad<QPMPC_PARAM_CUBIC, true, QB>;
     }
 }
-// QPMPC_KERNEL=quad|thread pins the kernel choice (the tests exercise both kernels at every size with it)
-static const char *kernel_override() {
-    const char *e = getenv("QPMPC_KERNEL");
-    return e ? e : "";
-}
-
 struct LaunchPlan {
     bool quad;    // k_rollout_quad (4 lanes per rollout) instead of k_rollout (1 thread per rollout)
     int T, nblk;  // threads per block, blocks per robot
@@ -1216,12 +1231,12 @@ static LaunchPlan plan_launch(const qpmpc_handle *h, int n, long long total_roll
     const long long subparts = (long long)h->num_sms * 4;
     LaunchPlan pl;
     pl.quad = total_rollouts < subparts * 32 * 2;
-    if (!strcmp(kernel_override(), "quad")) pl.quad = true;
-    if (!strcmp(kernel_override(), "thread")) pl.quad = false;
+    if (h->env.kernel == 1) pl.quad = true;   // QPMPC_KERNEL pins the choice (the tests run both kernels at every size)
+    if (h->env.kernel == 2) pl.quad = false;
     // rollouts per quad block: 128 keeps the number of partials the last block merges small; 32 spreads a small solve
     // (72 x 4 threads = 9 warps: N = 10,000 becomes 139 blocks, one per SM in a single wave)
     int QB = n < 4096 ? 32 : ((n + 71) / 72 <= h->num_sms ? 72 : 128);
-    if (const char *q = getenv("QPMPC_QB")) QB = atoi(q) == 128 ? 128 : atoi(q) == 72 ? 72 : 32;
+    if (h->env.qb) QB = h->env.qb;
     if (pl.quad && QB == 72 && (size_t)quad_smem_floats(d.P, d.H, 72) * 4 > h->max_smem) QB = 32;
     if (pl.quad && QB == 128 && (size_t)quad_smem_floats(d.P, d.H, 128) * 4 > h->max_smem) QB = 32;
     if (pl.quad && (size_t)quad_smem_floats(d.P, d.H, QB) * 4 > h->max_smem) pl.quad = false;
@@ -1278,6 +1293,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     qpmpc_handle *h = new (std::nothrow) qpmpc_handle();
     if (!h) return fail(QPMPC_E_ARG, "out of host memory");
     h->cfg = c;
+    h->env = read_env();
     h->device = c.device;
     h->launches = 0;
     h->profiling = 0;
@@ -1403,8 +1419,7 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
     // (huge N with tiny P) or when QPMPC_FUSED=0 asks for the two-kernel path (tests cover both).
     const int K = d.method == QPMPC_METHOD_CEM ? d.cem_elite : 0;
     const int scratch = pl.quad ? P * (pl.T / 4 + 1) : P * (pl.T + 1);
-    const char *fe = getenv("QPMPC_FUSED");
-    ra.fused = finalize_smem_floats(P, nblk, K, pl.T) <= scratch && !(fe && fe[0] == '0');
+    ra.fused = finalize_smem_floats(P, nblk, K, pl.T) <= scratch && h->env.fused;
     if (h->profiling) CU(cudaEventRecord(h->ev[0], h->stream));
     pick_fn(h, pl)<<<dim3(nblk, R), pl.T, pl.smem, h->stream>>>(d, ra, in);
     CU(cudaGetLastError());
@@ -1458,12 +1473,10 @@ static int solve_impl(qpmpc_handle *h, const float *state, const float *referenc
     //                        fit the parameter block);   QPMPC_INPUTS=mapped   the kernel reads the inputs over PCIe
     //                        (every block does: slowest, kept as the measured negative result)
     //   QPMPC_ZEROCOPY=0     classic H2D + kernel + D2H + cudaStreamSynchronize
-    const char *zc = getenv("QPMPC_ZEROCOPY");
-    const char *im = getenv("QPMPC_INPUTS");
-    const bool zero_copy = !(zc && zc[0] == '0');
-    const bool mapped_in = zero_copy && ((zc && zc[0] == '1') || (im && !strcmp(im, "mapped")));
-    const bool inline_in = !mapped_in && h->in_floats <= (size_t)INLINE_FLOATS && !(im && !strcmp(im, "copy")) &&
-                           !(zc && zc[0] == '0');
+    const EnvSwitches &ev = h->env;
+    const bool zero_copy = ev.zerocopy != 0;
+    const bool mapped_in = zero_copy && (ev.zerocopy == 1 || ev.inputs == 2);
+    const bool inline_in = !mapped_in && h->in_floats <= (size_t)INLINE_FLOATS && ev.inputs != 1 && ev.zerocopy != 0;
     const size_t o_state = 0, o_ref = 24, o_contact = 48, o_best = o_contact + 4 * H, o_sigma = o_best + P,
                  o_timing = o_sigma + P, o_nominal = o_timing + 4, o_oswing = o_nominal + 1;
     const size_t res_floats = sizeof(qpmpc_result) / 4;
