@@ -4,6 +4,7 @@ The only place the Python host touches native code for the TAMOLS path.  No CPU 
 missing or no sm_100 GPU is present, calls raise `TamolsError`.
 """
 import ctypes as C
+import math
 
 import numpy as np
 
@@ -89,6 +90,9 @@ def make_params(tamols_params=None, robot_name="aliengo"):
     return p
 
 
+_INDEX_GRIDS = {}
+
+
 def fit_grid(xy):
     """Regular-grid description (origin, row_axis, col_axis) of sensor coordinates xy[R, C, 2]; raises when the
     points are not a regular orthogonal grid (the analytic nearest-cell lookup needs one)."""
@@ -103,12 +107,16 @@ def fit_grid(xy):
         row_axis = np.array([-col_axis[1], col_axis[0]])
     elif col_axis is None:
         col_axis = np.array([row_axis[1], -row_axis[0]])
-    rr, cc = np.meshgrid(np.arange(R), np.arange(Cc), indexing="ij")
-    model = origin + rr[..., None] * row_axis + cc[..., None] * col_axis
-    scale = min(np.linalg.norm(row_axis), np.linalg.norm(col_axis))
-    if scale <= 0 or np.max(np.abs(model - xy)) > 1e-6 * max(scale, 1e-9) + 1e-9:
+    grids = _INDEX_GRIDS.get((R, Cc))
+    if grids is None:  # row / column index of every cell, built once per map shape
+        rr, cc = np.meshgrid(np.arange(R, dtype=np.float64), np.arange(Cc, dtype=np.float64), indexing="ij")
+        grids = _INDEX_GRIDS[(R, Cc)] = (rr[..., None], cc[..., None])
+    model = origin + grids[0] * row_axis + grids[1] * col_axis
+    r0, r1, c0, c1 = float(row_axis[0]), float(row_axis[1]), float(col_axis[0]), float(col_axis[1])
+    scale = min(math.hypot(r0, r1), math.hypot(c0, c1))
+    if scale <= 0 or float(np.abs(model - xy).max()) > 1e-6 * max(scale, 1e-9) + 1e-9:
         raise TamolsError("heightmap cells are not a regular grid: the analytic nearest-cell lookup does not apply")
-    if abs(float(row_axis @ col_axis)) > 1e-6 * scale * scale:
+    if abs(r0 * c0 + r1 * c1) > 1e-6 * scale * scale:
         raise TamolsError("heightmap grid axes are not orthogonal")
     return origin, row_axis, col_axis
 

@@ -11,6 +11,8 @@ lookup per leg, :104-108) and the height-only fallback when no candidate is feas
 needs the closed-source VFA module upstream (:6-18) and raises ImportError here exactly like the reference does when
 that module is absent.
 """
+import copy
+
 import numpy as np
 
 from .. import _tamols_cabi as tc
@@ -36,6 +38,8 @@ class VisualFootholdAdaptation:
             self.robot_name = cfg.robot
             self._handle = tc.Handle(tc.make_params(self.tamols_params, self.robot_name), device=device,
                                      max_jobs=max(4, len(legs_order)))
+            self._params_seen = copy.deepcopy(self.tamols_params)  # what the handle currently holds
+            self._pack = {}
 
     # ---- state machine, visual_foothold_adaptation.py:59-72
     def update_footholds_adaptation(self, update_footholds_adaptation):
@@ -91,29 +95,29 @@ class VisualFootholdAdaptation:
         """Pack the legs into tamols_leg_job records and run the single scoring launch."""
         n = len(legs_order)
         # self.tamols_params is read with .get() on every call upstream, so a changed dict takes effect here too
-        self._handle.set_params(tc.make_params(self.tamols_params, self.robot_name))
+        if self.tamols_params != self._params_seen:
+            self._handle.set_params(tc.make_params(self.tamols_params, self.robot_name))
+            self._params_seen = copy.deepcopy(self.tamols_params)
         datas = [np.asarray(heightmaps[name].data, np.float64)[:, :, 0, :] for name in legs_order]
         R = max(d.shape[0] for d in datas)
         Cc = max(d.shape[1] for d in datas)
-        heights = np.zeros((n, R, Cc))
-        xy = np.zeros((n, R, Cc, 2))
-        jobs = np.zeros(n, tc.JOB_DTYPE)
+        pk = self._pack.get((n, R, Cc))
+        if pk is None:  # staging arrays per (legs, map shape), reused across calls
+            pk = self._pack[(n, R, Cc)] = (np.zeros((n, R, Cc)), np.zeros((n, R, Cc, 2)), np.zeros(n, tc.JOB_DTYPE))
+        heights, xy, jobs = pk
         vel = None if self.forward_vel is None else np.asarray(self.forward_vel, np.float64)
+        win = np.zeros((n, 5), np.int32)       # map, r0, c0, nr, nc
+        grid = np.zeros((n, 3, 2))             # origin, row_axis, col_axis
+        flags = np.zeros(n, np.int32)
+        stab = np.zeros((n, 2, 2))             # base_xy, diag_foot
         for k, name in enumerate(legs_order):
             d = datas[k]
             nr, nc = d.shape[:2]
             heights[k, :nr, :nc] = d[..., 2]
             xy[k, :nr, :nc] = d[..., :2]
-            origin, row_axis, col_axis = tc.fit_grid(d[..., :2])
-            j = jobs[k]
-            j["map"], j["r0"], j["c0"], j["nr"], j["nc"] = k, 0, 0, nr, nc
-            j["origin"], j["row_axis"], j["col_axis"] = origin, row_axis, col_axis
-            j["seed"] = np.asarray(reference_footholds[name], np.float64)
-            j["hip"] = np.asarray(hip_positions[name], np.float64)
-            flags = 0
-            if vel is not None:
-                flags |= tc.FLAG_HAS_VELOCITY
-                j["vel"] = vel
+            grid[k] = tc.fit_grid(d[..., :2])
+            win[k] = (k, 0, 0, nr, nc)
+            f = tc.FLAG_HAS_VELOCITY if vel is not None else 0
             # _compute_stability_cost preconditions, :631-664 (leg_id is the position in legs_order)
             diag = tc.DIAGONAL.get(name)
             in_stance = k < len(self.current_contact) and self.current_contact[k] == 1
@@ -121,10 +125,18 @@ class VisualFootholdAdaptation:
                     and not in_stance and hasattr(self.current_feet_pos, diag)):
                 if vel is None:
                     raise TypeError("forward_vel is None but the stability cost needs it (as upstream, :672)")
-                flags |= tc.FLAG_STABILITY
-                j["base_xy"] = np.asarray(self.base_position, np.float64)[:2]
-                j["diag_foot"] = np.asarray(getattr(self.current_feet_pos, diag), np.float64)[:2]
-            j["flags"] = flags
+                f |= tc.FLAG_STABILITY
+                stab[k, 0] = np.asarray(self.base_position, np.float64)[:2]
+                stab[k, 1] = np.asarray(getattr(self.current_feet_pos, diag), np.float64)[:2]
+            flags[k] = f
+        # one assignment per record field for all legs (numpy fills structured arrays field by field: slow per item)
+        jobs["map"], jobs["r0"], jobs["c0"], jobs["nr"], jobs["nc"] = win.T
+        jobs["flags"] = flags
+        jobs["origin"], jobs["row_axis"], jobs["col_axis"] = grid[:, 0], grid[:, 1], grid[:, 2]
+        jobs["seed"] = [np.asarray(reference_footholds[name], np.float64) for name in legs_order]
+        jobs["hip"] = [np.asarray(hip_positions[name], np.float64) for name in legs_order]
+        jobs["vel"] = vel if vel is not None else 0.0
+        jobs["base_xy"], jobs["diag_foot"] = stab[:, 0], stab[:, 1]
         results, _ = self._handle.score_host(heights, jobs, xy=xy)
         return results
 
