@@ -264,6 +264,19 @@ def run_cuda(args):
             b_ = h.solve(st, ref, seq, b_, 42, 3 * it + k, timing=timing, nominal_freq=nominal, optimize_swing=1,
                          want_costs=False)["best"]
 
+    # the same solve one level up: Sampling_MPC (gait-adaptive class) driven like srbd_controller_interface.py:131-168
+    from quadruped_pympc_tamols_b200._config import make_config as mk_cfg
+    from quadruped_pympc_tamols_b200.controllers.sampling.centroidal_nmpc_jax_gait_adaptive import Sampling_MPC
+    ctl = Sampling_MPC(config=mk_cfg("go2", sampling_method="mppi", control_parametrization="cubic_spline",
+                                     optimize_step_freq=True, num_parallel_computations=N_ROLLOUTS), device_index=local_rank)
+
+    def class_call(it):
+        ctl.with_newkey()
+        out_ = ctl.jitted_compute_control(st, ref, seq, ctl.best_control_parameters, ctl.master_key, timing, nominal, 1)
+        ctl.best_control_parameters = out_[3]
+
+    class_p50 = timed(class_call)
+    ctl.close()
     iterated = {"workload": "C2 with num_sampling_iterations = 3 (srbd_controller_interface.py:131-170)",
                 "chained_p50_ms": timed(lambda it: h.solve(st, ref, seq, best, 42, 3 * it, timing=timing, nominal_freq=nominal,
                                                            optimize_swing=1, want_costs=False, iterations=3)),
@@ -298,6 +311,7 @@ def run_cuda(args):
                            "multi_gpu": "one independent robot instance per rank, no collective on the control path"},
                 "e2e": {"value": e2e_value, "unit": "rollouts/s", "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": out_bytes,
                         "p50_latency_ms": float(np.median(e2e) * 1e3), "p99_latency_ms": float(np.percentile(e2e, 99) * 1e3),
+                        "class_call_p50_latency_ms": class_p50,
                         "api": "qpmpc_solve (host buffers; costs[N] left on the device as upstream)",
                         "transfers": "inputs in the kernel parameter block (host -> device with the launch); results stored by the kernel into mapped pinned host memory as {word, sequence} pairs"},
                 "gpu_launches": int(launches),
@@ -516,8 +530,42 @@ def run_tamols(torch, dev, local_rank, rank, world, barrier, max_over_ranks, wit
             wall.append(time.perf_counter() - t0)
     h.close()
     wall = np.array(wall)
+    # the same call one level up: VisualFootholdAdaptation.compute_adaptation as wb_interface.py:236-241 makes it
+    # (sensor objects in, LegsAttr footholds out; includes the Python packing of the job records)
+    from quadruped_pympc_tamols_b200._config import make_config as mk
+    from quadruped_pympc_tamols_b200.helpers.legs_attr import LegsAttr
+    from quadruped_pympc_tamols_b200.helpers.visual_foothold_adaptation import VisualFootholdAdaptation
+
+    class _Sensor:  # stands in for gym_quadruped's HeightMap: .data[R, C, 1, 3]
+        def __init__(self, xy, z):
+            self.data = np.concatenate([xy, z[..., None]], axis=-1)[:, :, None, :].copy()
+
+        def get_height(self, p):
+            d = self.data[:, :, 0, :].reshape(-1, 3)
+            return float(d[np.argmin((d[:, 0] - p[0]) ** 2 + (d[:, 1] - p[1]) ** 2), 2])
+
+    legs = ("FL", "FR", "RL", "RR")
+    vfa = VisualFootholdAdaptation(legs, "tamols", config=mk("hyqreal1", tamols_params=sy.tamols_params_for("hyqreal1")),
+                                   device=local_rank)
+    prepared = []
+    for s in scenes:
+        prepared.append((LegsAttr(**{n: s["hips"][k] for k, n in enumerate(legs)}),
+                         LegsAttr(**{n: _Sensor(s["xy"][k], s["heights"][k]) for k, n in enumerate(legs)}),
+                         LegsAttr(**{n: s["feet"][k] for k, n in enumerate(legs)}), s))
+    cwall = []
+    for it in range(10 + 200):
+        hips_, maps_, feet_, s = prepared[it % 16]
+        ref_ = LegsAttr(**{n: s["seeds"][k].copy() for k, n in enumerate(legs)})
+        vfa.reset()
+        t0 = time.perf_counter()
+        vfa.compute_adaptation(legs, ref_, hips_, maps_, s["vel"], np.zeros(3), np.zeros(3), base_position=s["base"],
+                               current_contact=s["contact"], current_feet_pos=feet_, phase_signal=np.zeros(4))
+        if it >= 10:
+            cwall.append(time.perf_counter() - t0)
+    vfa.close()
     in_b = 4 * 13 * 8 * 8 + 4 * 13 * 7 * 16 + 4 * tc.JOB_DTYPE.itemsize
     out["e2e_c3t"] = {"workload": "C3-T: hyqreal1, 4 legs x 13x7 sensor maps (stepping stones), tamols_score_host",
+                      "class_call_p50_ms": float(np.median(cwall) * 1e3),
                       "p50_ms": float(np.median(wall) * 1e3), "footholds_per_s": 4 / float(np.median(wall)),
                       "h2d_bytes_per_step": in_b, "d2h_bytes_per_step": 2 * 4 * tc.RESULT_DTYPE.itemsize,
                       "transfers": "one H2D copy of maps + jobs; results stored by the kernel into mapped pinned host memory as {word, sequence} pairs"}

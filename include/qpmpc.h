@@ -151,6 +151,12 @@ typedef struct qpmpc_batch {
  * synchronises.  No collective: robots are independent. */
 int qpmpc_solve_batched(qpmpc_handle *h, const qpmpc_batch *batch, uint64_t seed, uint64_t offset);
 
+/* costs[N] of the most recent qpmpc_solve / qpmpc_solve_iterated on this handle, copied to the host on request.
+ * Upstream the 7th return value of jitted_compute_control is a DEVICE array nobody in the control loop reads
+ * (srbd_controller_interface.py:131-168 uses best_cost only); the Python class therefore leaves the costs on the
+ * device and fetches them through this call only when they are looked at.  Synchronous. */
+int qpmpc_copy_costs(qpmpc_handle *h, float *costs_out);
+
 /* jit_vectorized_rollout (centroidal_nmpc_jax.py:176-177, ..._gait_adaptive.py:186-187):
  * d_params [n,P] (DEVICE) -> d_costs [n] (DEVICE), raw costs without the NaN/Inf saturation.
  * state / reference / contact_sequence / timing are HOST; d_freqs [n] DEVICE (gait adaptive) or NULL.

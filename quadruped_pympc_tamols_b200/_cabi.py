@@ -5,6 +5,7 @@ fallback: if the shared library is missing or no sm_100 GPU is present, calls ra
 torch is used by callers only for device buffers (tensor.data_ptr()); nothing here needs it.
 """
 import ctypes as C
+import weakref
 import os
 import subprocess
 
@@ -66,7 +67,7 @@ class QpmpcGaitBatch(C.Structure):  # include/qpmpc.h: qpmpc_gait_batch
 
 
 EXPORTS = ["qpmpc_create", "qpmpc_destroy", "qpmpc_num_params", "qpmpc_last_error", "qpmpc_version", "qpmpc_stream",
-           "qpmpc_launch_count", "qpmpc_solve", "qpmpc_solve_iterated", "qpmpc_solve_batched", "qpmpc_rollout_costs", "qpmpc_generate_noise", "qpmpc_set_profiling", "qpmpc_profile_last",
+           "qpmpc_launch_count", "qpmpc_solve", "qpmpc_solve_iterated", "qpmpc_copy_costs", "qpmpc_solve_batched", "qpmpc_rollout_costs", "qpmpc_generate_noise", "qpmpc_set_profiling", "qpmpc_profile_last",
            "qpmpc_measure_fp32_peak", "qpmpc_contact_sequences", "qpmpc_gait_run"]
 
 
@@ -104,6 +105,7 @@ def lib():
                                   vp, vp, vp, vp]  # host pointers passed as integers (cheapest ctypes marshalling)
         L.qpmpc_solve_iterated.argtypes = [vp, vp, vp, vp, vp, C.c_uint64, C.c_uint64, C.c_int32, vp, C.c_float, C.c_int32,
                                            vp, vp, vp, vp, vp]
+        L.qpmpc_copy_costs.argtypes = [vp, vp]
         L.qpmpc_solve_batched.argtypes = [vp, C.POINTER(QpmpcBatch), C.c_uint64, C.c_uint64]
         L.qpmpc_rollout_costs.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int32, vp]
         L.qpmpc_generate_noise.argtypes = [vp, C.c_uint64, C.c_uint64, C.c_int32, vp, C.c_float, C.c_int32, vp, vp]
@@ -170,6 +172,48 @@ def _fp(a):
     return a.ctypes.data if a is not None else None
 
 
+class DeviceCosts:
+    """costs[N] of a solve, still on the device -- the analogue of the jax device array upstream returns as the 7th
+    value of jitted_compute_control and never reads in the control loop (srbd_controller_interface.py:131-168).
+    Behaves like a read-only float32 numpy array: the values are fetched (one 4 N byte copy) the first time they are
+    looked at, or just before the handle's next solve overwrites them."""
+
+    def __init__(self, handle, n):
+        self._handle, self._n, self._host = handle, n, None
+
+    def _fetch(self):
+        if self._host is None:
+            h = self._handle
+            out = np.empty(self._n, np.float32)
+            if h is not None and getattr(h, "_h", None) is not None and h._h.value:
+                check(lib().qpmpc_copy_costs(h._h, out.ctypes.data))
+            else:
+                raise QpmpcError("the controller was closed before its costs were read")
+            self._host, self._handle = out, None
+        return self._host
+
+    shape = property(lambda self: (self._n,))
+    dtype = np.dtype(np.float32)
+    ndim = 1
+    size = property(lambda self: self._n)
+
+    def __array__(self, dtype=None, copy=None):
+        a = self._fetch()
+        return a if dtype is None else a.astype(dtype)
+
+    def __len__(self):
+        return self._n
+
+    def __getitem__(self, k):
+        return self._fetch()[k]
+
+    def __iter__(self):
+        return iter(self._fetch())
+
+    def __repr__(self):
+        return f"DeviceCosts({self._fetch()!r})" if self._host is not None else f"DeviceCosts(<{self._n} float32 on the device>)"
+
+
 class Handle:
     """Owns one qpmpc_handle (device scratch + stream).  Thin: every method is one C call."""
 
@@ -183,6 +227,14 @@ class Handle:
 
     def close(self):
         if getattr(self, "_h", None) is not None and self._h.value:
+            pending = getattr(self, "_lazy_costs", None)
+            c_ = pending() if pending is not None else None
+            if c_ is not None and c_._host is None:  # costs somebody still holds: fetch before the buffers go away
+                try:
+                    c_._fetch()
+                except Exception:  # noqa: BLE001  (interpreter shutdown)
+                    pass
+            self._lazy_costs = None
             lib().qpmpc_destroy(self._h)
             self._h = C.c_void_p()
 
@@ -216,6 +268,12 @@ class Handle:
         solves on the device (keys (seed, offset), (seed, offset + 1), ...; mean and sigma carried on the device,
         srbd_controller_interface.py:131-170), outputs of the last one."""
         arr, ptr, f_solve, f_iter = self._io()
+        pending = getattr(self, "_lazy_costs", None)
+        if pending is not None:  # somebody still holds the previous solve's costs: fetch them before they are overwritten
+            c_ = pending()
+            if c_ is not None and c_._host is None:
+                c_._fetch()
+            self._lazy_costs = None
         try:  # the shapes the callers use: [24], [24], [4, H], [P]
             arr["st"][:] = state
             arr["rf"][:] = reference
@@ -236,8 +294,8 @@ class Handle:
         if sigma_in is not None:
             arr["sg"][:] = sigma_in  # scalar or [P]
             p_sg, p_so = ptr["sg"], ptr["so"]
-        costs = np.empty(self.N, np.float32) if want_costs else None
-        p_costs = costs.ctypes.data if want_costs else None
+        costs = np.empty(self.N, np.float32) if want_costs is True else None
+        p_costs = costs.ctypes.data if costs is not None else None
         if iterations == 1:
             check(f_solve(self._h, ptr["st"], ptr["rf"], ptr["cs"], ptr["bi"], int(seed), int(offset), p_tm,
                           float(nominal_freq), int(optimize_swing), p_sg, d_eps, d_freqs, ptr["res"], ptr["bo"], p_so,
@@ -247,6 +305,9 @@ class Handle:
                 raise QpmpcError("chained iterations draw their own noise (no d_eps / d_freqs)")
             check(f_iter(self._h, ptr["st"], ptr["rf"], ptr["cs"], ptr["bi"], int(seed), int(offset), int(iterations),
                          p_tm, float(nominal_freq), int(optimize_swing), p_sg, ptr["res"], ptr["bo"], p_so, p_costs))
+        if want_costs == "lazy":
+            costs = DeviceCosts(self, self.N)
+            self._lazy_costs = weakref.ref(costs)
         res = arr["res"].copy()  # fresh arrays: the caller keeps them across calls
         return dict(grf=res[0:12], footholds=res[12:24], predicted_state=res[24:48], best=arr["bo"].copy(),
                     best_cost=res[48], best_freq=res[49], costs=costs,

@@ -202,7 +202,7 @@ class Sampling_MPC:
         key = np.asarray(key, dtype=np.uint64).reshape(-1)
         r = self._handle.solve(state, reference, contact_sequence, best_control_parameters, int(key[0]), int(key[-1]),
                                timing=timing, nominal_freq=float(nominal_step_frequency),
-                               optimize_swing=int(optimize_swing), sigma_in=sigma, want_costs=True)
+                               optimize_swing=int(optimize_swing), sigma_in=sigma, want_costs="lazy")
         return r
 
     def compute_control_random_sampling(self, state, reference, contact_sequence, best_control_parameters, key, timing,
@@ -241,7 +241,7 @@ class Sampling_MPC:
         key = np.asarray(self.master_key, dtype=np.uint64).reshape(-1)
         r = self._handle.solve(state, reference, contact_sequence, self.best_control_parameters, int(key[0]),
                                int(key[-1]) + 1, timing=self._timing(timing), nominal_freq=float(nominal_step_frequency),
-                               optimize_swing=int(optimize_swing), sigma_in=sigma, want_costs=True, iterations=K)
+                               optimize_swing=int(optimize_swing), sigma_in=sigma, want_costs="lazy", iterations=K)
         self.master_key = np.array([key[0], key[-1] + np.uint64(K)], dtype=np.uint64)  # K times with_newkey
         self.best_control_parameters = r["best"]
         out = (r["grf"], r["footholds"], r["predicted_state"], r["best"], r["best_cost"], r["best_freq"], r["costs"])

@@ -1583,6 +1583,16 @@ extern "C" int qpmpc_solve_iterated(qpmpc_handle *h, const float *state, const f
                       costs_out);
 }
 
+extern "C" int qpmpc_copy_costs(qpmpc_handle *h, float *costs_out) {
+    if (!h || !costs_out) return fail(QPMPC_E_ARG, "null argument");
+    CU(cudaSetDevice(h->device));
+    const size_t bytes = (size_t)h->dc.N * 4;
+    CU(cudaMemcpyAsync(h->h_out + h->out_floats, h->d_costs, bytes, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    memcpy(costs_out, h->h_out + h->out_floats, bytes);
+    return QPMPC_OK;
+}
+
 extern "C" int qpmpc_rollout_costs(qpmpc_handle *h, const float *state, const float *reference,
                                    const float *contact_sequence, const float *timing, const float *d_params,
                                    const float *d_freqs, int32_t n, float *d_costs) {

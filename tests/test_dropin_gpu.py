@@ -253,3 +253,35 @@ def test_interface_rejects_what_upstream_cannot_run():
     with pytest.raises(NotImplementedError):
         itf.compute_RTI()
     itf.close()
+
+
+def test_costs_stay_on_the_device_until_read():
+    """Sampling_MPC returns its costs like upstream's device array: fetched on first look, and before the next solve
+    overwrites them; values equal the eagerly copied costs of the same solve."""
+    from quadruped_pympc_tamols_b200 import _cabi
+    from quadruped_pympc_tamols_b200.controllers.sampling.centroidal_nmpc_jax import Sampling_MPC
+    cfg = make_config("aliengo", sampling_method="mppi", control_parametrization="linear_spline",
+                      num_parallel_computations=4096)
+    c = Sampling_MPC(config=cfg)
+    rng = np.random.default_rng(3)
+    st, ref, seq, timing, freq = synth_problem("aliengo", "trot", rng)
+    best0 = np.zeros(c.num_control_parameters, np.float32)
+    key1, key2 = np.array([42, 1], np.uint64), np.array([42, 2], np.uint64)
+    eager1 = c._handle.solve(st, ref, seq, best0, 42, 1, want_costs=True)["costs"]
+    eager2 = c._handle.solve(st, ref, seq, best0, 42, 2, want_costs=True)["costs"]
+    out1 = c.jitted_compute_control(st, ref, seq, best0, key1, None, 0.0, 0)
+    costs1 = out1[6]
+    assert isinstance(costs1, _cabi.DeviceCosts) and costs1._host is None and len(costs1) == 4096
+    out2 = c.jitted_compute_control(st, ref, seq, best0, key2, None, 0.0, 0)  # must not clobber costs1
+    assert costs1._host is not None
+    assert np.array_equal(np.asarray(costs1), eager1)
+    assert float(np.min(costs1)) == float(out1[4]) and costs1[int(np.argmin(costs1))] == out1[4]
+    assert np.array_equal(out2[6] - eager2, np.zeros(4096, np.float32))  # arithmetic goes through __array__
+    dropped = c.jitted_compute_control(st, ref, seq, best0, key1, None, 0.0, 0)[6]
+    del dropped  # nobody holds it: the next solve fetches nothing
+    n0 = c._handle.launch_count
+    c.jitted_compute_control(st, ref, seq, best0, key2, None, 0.0, 0)
+    assert c._handle.launch_count == n0 + 1
+    held = c.jitted_compute_control(st, ref, seq, best0, key1, None, 0.0, 0)[6]
+    c.close()  # closing fetches what is still held
+    assert np.array_equal(np.asarray(held), eager1)
