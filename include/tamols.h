@@ -120,6 +120,13 @@ int tamols_score_host(tamols_handle *h, const double *heights, int32_t num_maps,
                       const double *xy, const tamols_leg_job *jobs, int32_t n_jobs, tamols_result *results,
                       double *scores, int64_t scores_stride);
 
+/* Host helper (no GPU work): the regular-grid description of one sensor map's cell coordinates xy[rows, cols, 2]
+ * (gym_quadruped HeightMap.data[:, :, 0, :2]): origin = cell (0,0), row_axis / col_axis = mean step between rows /
+ * columns.  TAMOLS_E_ARG when the cells are not a regular orthogonal grid to 1e-6 of the cell size -- the analytic
+ * nearest-cell lookup that replaces the reference's cKDTree (visual_foothold_adaptation.py:23-35) needs one. */
+int tamols_fit_grid(const double *xy, int32_t rows, int32_t cols, double origin[2], double row_axis[2],
+                    double col_axis[2]);
+
 /* ---- the step in front of the scoring, for a batch of robots on the device.
  * (a) FootholdReferenceGenerator.compute_footholds_reference (helpers/foothold_reference_generator.py:53-157): hip
  *     positions in the yaw-aligned frame, +-hip_offset, desired-velocity offset stance_time/2 * v_ref clipped to

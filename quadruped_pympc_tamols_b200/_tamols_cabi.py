@@ -62,7 +62,7 @@ class TamolsSeedBatch(C.Structure):  # include/tamols.h: tamols_seed_batch
 
 
 EXPORTS = ["tamols_create", "tamols_destroy", "tamols_set_params", "tamols_last_error", "tamols_stream",
-           "tamols_launch_count", "tamols_score_device", "tamols_score_host", "tamols_seed_jobs"]
+           "tamols_launch_count", "tamols_score_device", "tamols_score_host", "tamols_seed_jobs", "tamols_fit_grid"]
 
 
 def make_params(tamols_params=None, robot_name="aliengo"):
@@ -90,35 +90,23 @@ def make_params(tamols_params=None, robot_name="aliengo"):
     return p
 
 
-_INDEX_GRIDS = {}
+_FIT_OUT = None
 
 
 def fit_grid(xy):
     """Regular-grid description (origin, row_axis, col_axis) of sensor coordinates xy[R, C, 2]; raises when the
-    points are not a regular orthogonal grid (the analytic nearest-cell lookup needs one)."""
-    xy = np.asarray(xy, np.float64)
-    R, Cc = xy.shape[:2]
-    origin = xy[0, 0].copy()
-    row_axis = (xy[R - 1, 0] - origin) / (R - 1) if R > 1 else None
-    col_axis = (xy[0, Cc - 1] - origin) / (Cc - 1) if Cc > 1 else None
-    if row_axis is None and col_axis is None:
-        row_axis, col_axis = np.array([1.0, 0.0]), np.array([0.0, 1.0])
-    elif row_axis is None:
-        row_axis = np.array([-col_axis[1], col_axis[0]])
-    elif col_axis is None:
-        col_axis = np.array([row_axis[1], -row_axis[0]])
-    grids = _INDEX_GRIDS.get((R, Cc))
-    if grids is None:  # row / column index of every cell, built once per map shape
-        rr, cc = np.meshgrid(np.arange(R, dtype=np.float64), np.arange(Cc, dtype=np.float64), indexing="ij")
-        grids = _INDEX_GRIDS[(R, Cc)] = (rr[..., None], cc[..., None])
-    model = origin + grids[0] * row_axis + grids[1] * col_axis
-    r0, r1, c0, c1 = float(row_axis[0]), float(row_axis[1]), float(col_axis[0]), float(col_axis[1])
-    scale = min(math.hypot(r0, r1), math.hypot(c0, c1))
-    if scale <= 0 or float(np.abs(model - xy).max()) > 1e-6 * max(scale, 1e-9) + 1e-9:
-        raise TamolsError("heightmap cells are not a regular grid: the analytic nearest-cell lookup does not apply")
-    if abs(r0 * c0 + r1 * c1) > 1e-6 * scale * scale:
-        raise TamolsError("heightmap grid axes are not orthogonal")
-    return origin, row_axis, col_axis
+    points are not a regular orthogonal grid (the analytic nearest-cell lookup needs one).  One C call
+    (tamols_fit_grid, host only): the numpy version of this check cost more than the scoring launch."""
+    global _FIT_OUT
+    xy = np.ascontiguousarray(xy, np.float64)
+    if _FIT_OUT is None:
+        out = np.zeros((3, 2))
+        base = out.ctypes.data
+        _FIT_OUT = (out, base, base + 16, base + 32, lib().tamols_fit_grid)
+    out, p0, p1, p2, f = _FIT_OUT
+    check(f(xy.ctypes.data, xy.shape[0], xy.shape[1], p0, p1, p2))
+    o = out.copy()
+    return o[0], o[1], o[2]
 
 
 _BOUND = False
@@ -141,6 +129,7 @@ def lib():
                                           C.c_int32, C.c_int32, C.c_int32, vp, vp, C.c_int64]
         L.tamols_score_host.argtypes = [vp, vp, C.c_int32, C.c_int32, C.c_int32, vp, vp, C.c_int32, vp, vp, C.c_int64]
         L.tamols_seed_jobs.argtypes = [vp, C.POINTER(TamolsSeedBatch)]
+        L.tamols_fit_grid.argtypes = [vp, C.c_int32, C.c_int32, vp, vp, vp]
         _BOUND = True
     return L
 

@@ -884,3 +884,32 @@ extern "C" int tamols_seed_jobs(tamols_handle *h, const tamols_seed_batch *b) {
     h->launches += 1;
     return TAMOLS_OK;
 }
+
+extern "C" int tamols_fit_grid(const double *xy, int32_t rows, int32_t cols, double origin[2], double row_axis[2],
+                               double col_axis[2]) {
+    if (!xy || !origin || !row_axis || !col_axis || rows < 1 || cols < 1) return tfail(TAMOLS_E_ARG, "bad argument");
+    auto at = [&](int r, int c, int k) { return xy[((size_t)r * cols + c) * 2 + k]; };
+    origin[0] = at(0, 0, 0);
+    origin[1] = at(0, 0, 1);
+    const bool hr = rows > 1, hc = cols > 1;
+    if (hr) for (int k = 0; k < 2; ++k) row_axis[k] = (at(rows - 1, 0, k) - origin[k]) / (double)(rows - 1);
+    if (hc) for (int k = 0; k < 2; ++k) col_axis[k] = (at(0, cols - 1, k) - origin[k]) / (double)(cols - 1);
+    if (!hr && !hc) { row_axis[0] = 1.0; row_axis[1] = 0.0; col_axis[0] = 0.0; col_axis[1] = 1.0; }
+    else if (!hr) { row_axis[0] = -col_axis[1]; row_axis[1] = col_axis[0]; }
+    else if (!hc) { col_axis[0] = row_axis[1]; col_axis[1] = -row_axis[0]; }
+    const double lr = hypot(row_axis[0], row_axis[1]), lc = hypot(col_axis[0], col_axis[1]);
+    const double scale = lr < lc ? lr : lc;
+    double worst = 0.0;
+    for (int r = 0; r < rows; ++r)
+        for (int c = 0; c < cols; ++c)
+            for (int k = 0; k < 2; ++k) {
+                const double m = origin[k] + (double)r * row_axis[k] + (double)c * col_axis[k];
+                const double e = fabs(m - at(r, c, k));
+                worst = e > worst ? e : worst;
+            }
+    if (!(scale > 0.0) || worst > 1e-6 * (scale > 1e-9 ? scale : 1e-9) + 1e-9)
+        return tfail(TAMOLS_E_ARG, "heightmap cells are not a regular grid: the analytic nearest-cell lookup does not apply");
+    if (fabs(row_axis[0] * col_axis[0] + row_axis[1] * col_axis[1]) > 1e-6 * scale * scale)
+        return tfail(TAMOLS_E_ARG, "heightmap grid axes are not orthogonal");
+    return TAMOLS_OK;
+}
