@@ -127,6 +127,26 @@ int tamols_score_host(tamols_handle *h, const double *heights, int32_t num_maps,
 int tamols_fit_grid(const double *xy, int32_t rows, int32_t cols, double origin[2], double row_axis[2],
                     double col_axis[2]);
 
+/* One leg as VisualFootholdAdaptation.compute_adaptation receives it (visual_foothold_adaptation.py:86-166): the
+ * sensor object's cell array plus the per-leg vectors.  `data` = HeightMap.data, float64 [rows, cols, 1, 3] contiguous
+ * (x, y, z of every cell). */
+typedef struct tamols_sensor_leg {
+    const double *data;
+    int32_t rows, cols;
+    int32_t flags;       /* TAMOLS_FLAG_* */
+    int32_t reserved;
+    double seed[3];      /* reference_footholds[leg] */
+    double hip[3];       /* hip_positions[leg] */
+    double diag_foot[2]; /* current_feet_pos[diagonal leg][:2] (TAMOLS_FLAG_STABILITY) */
+    double base_xy[2];   /* base_position[:2]                  (TAMOLS_FLAG_STABILITY) */
+    double vel[3];       /* forward_vel                        (TAMOLS_FLAG_HAS_VELOCITY) */
+} tamols_sensor_leg;
+
+/* The whole candidate loop of compute_adaptation for n_legs legs straight from the sensor arrays: splits every
+ * data array into heights and cell coordinates, derives and checks each leg's grid (tamols_fit_grid), assembles
+ * the job records and runs tamols_score_host -- the host-side packing in one C call instead of ~100 us of numpy. */
+int tamols_score_sensors(tamols_handle *h, const tamols_sensor_leg *legs, int32_t n_legs, tamols_result *results);
+
 /* ---- the step in front of the scoring, for a batch of robots on the device.
  * (a) FootholdReferenceGenerator.compute_footholds_reference (helpers/foothold_reference_generator.py:53-157): hip
  *     positions in the yaw-aligned frame, +-hip_offset, desired-velocity offset stance_time/2 * v_ref clipped to

@@ -48,6 +48,11 @@ JOB_DTYPE = np.dtype([("map", "<i4"), ("r0", "<i4"), ("c0", "<i4"), ("nr", "<i4"
 RESULT_DTYPE = np.dtype([("best_index", "<i4"), ("num_finite", "<i4"), ("best_score", "<f8"), ("best_xyz", "<f8", 3),
                          ("vertex1", "<f8", 3), ("vertex2", "<f8", 3)])
 assert JOB_DTYPE.itemsize == C.sizeof(TamolsLegJob) and RESULT_DTYPE.itemsize == C.sizeof(TamolsResult)
+# include/tamols.h: tamols_sensor_leg (the data pointer travels as an integer)
+SENSOR_LEG_DTYPE = np.dtype([("data", "<u8"), ("rows", "<i4"), ("cols", "<i4"), ("flags", "<i4"), ("reserved", "<i4"),
+                             ("seed", "<f8", 3), ("hip", "<f8", 3), ("diag_foot", "<f8", 2), ("base_xy", "<f8", 2),
+                             ("vel", "<f8", 3)])
+assert SENSOR_LEG_DTYPE.itemsize == 8 + 16 + 8 * 13
 
 class TamolsSeedBatch(C.Structure):  # include/tamols.h: tamols_seed_batch
     _fields_ = [("num_robots", C.c_int32), ("hist_len", C.c_int32),
@@ -62,7 +67,7 @@ class TamolsSeedBatch(C.Structure):  # include/tamols.h: tamols_seed_batch
 
 
 EXPORTS = ["tamols_create", "tamols_destroy", "tamols_set_params", "tamols_last_error", "tamols_stream",
-           "tamols_launch_count", "tamols_score_device", "tamols_score_host", "tamols_seed_jobs", "tamols_fit_grid"]
+           "tamols_launch_count", "tamols_score_device", "tamols_score_host", "tamols_seed_jobs", "tamols_fit_grid", "tamols_score_sensors"]
 
 
 def make_params(tamols_params=None, robot_name="aliengo"):
@@ -130,6 +135,7 @@ def lib():
         L.tamols_score_host.argtypes = [vp, vp, C.c_int32, C.c_int32, C.c_int32, vp, vp, C.c_int32, vp, vp, C.c_int64]
         L.tamols_seed_jobs.argtypes = [vp, C.POINTER(TamolsSeedBatch)]
         L.tamols_fit_grid.argtypes = [vp, C.c_int32, C.c_int32, vp, vp, vp]
+        L.tamols_score_sensors.argtypes = [vp, vp, C.c_int32, vp]
         _BOUND = True
     return L
 
@@ -194,6 +200,18 @@ class Handle:
             p_s = scores.ctypes.data
         check(f(self._h, p_h, M, R, Cc, p_xy if xy is not None else None, p_j, n, p_r, p_s, stride))
         return res_u8.copy().view(RESULT_DTYPE), scores
+
+    def score_sensors(self, legs):
+        """legs: structured array (SENSOR_LEG_DTYPE) whose `data` fields are the addresses of float64 [R, C, 1, 3]
+        arrays the caller keeps alive.  Returns the results structured array."""
+        n = len(legs)
+        st = getattr(self, "_sensor_stage", None)
+        if st is None or st[0] != n:
+            res = np.zeros(n * RESULT_DTYPE.itemsize, np.uint8)
+            st = self._sensor_stage = (n, res, res.ctypes.data, lib().tamols_score_sensors)
+        _, res, p_res, f = st
+        check(f(self._h, legs.ctypes.data, n, p_res))
+        return res.copy().view(RESULT_DTYPE)
 
     def seed_jobs(self, batch: TamolsSeedBatch):
         """Seed footholds (and job records) of a batch of robots; asynchronous on self.stream."""

@@ -22,6 +22,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "../../include/tamols.h"
 
@@ -594,6 +595,8 @@ struct tamols_handle {
     char *d_stage, *h_stage;
     size_t stage_cap;
     char *m_out, *md_out;      // mapped pinned block of tamols_score_host: {word, sequence} pairs of the results
+    std::vector<double> sensor_heights, sensor_xy;  // host scratch of tamols_score_sensors
+    std::vector<tamols_leg_job> sensor_jobs;
     unsigned int seq;
 };
 
@@ -912,4 +915,46 @@ extern "C" int tamols_fit_grid(const double *xy, int32_t rows, int32_t cols, dou
     if (fabs(row_axis[0] * col_axis[0] + row_axis[1] * col_axis[1]) > 1e-6 * scale * scale)
         return tfail(TAMOLS_E_ARG, "heightmap grid axes are not orthogonal");
     return TAMOLS_OK;
+}
+
+extern "C" int tamols_score_sensors(tamols_handle *h, const tamols_sensor_leg *legs, int32_t n_legs,
+                                    tamols_result *results) {
+    if (!h || !legs || !results) return tfail(TAMOLS_E_ARG, "null argument");
+    if (n_legs < 1 || n_legs > h->max_jobs) return tfail(TAMOLS_E_ARG, "n_legs exceeds max_jobs");
+    int R = 0, Cc = 0;
+    for (int k = 0; k < n_legs; ++k) {
+        if (!legs[k].data || legs[k].rows < 1 || legs[k].cols < 1) return tfail(TAMOLS_E_ARG, "bad sensor map");
+        R = legs[k].rows > R ? legs[k].rows : R;
+        Cc = legs[k].cols > Cc ? legs[k].cols : Cc;
+    }
+    const size_t cells = (size_t)R * Cc;
+    h->sensor_heights.assign((size_t)n_legs * cells, 0.0);
+    h->sensor_xy.assign((size_t)n_legs * cells * 2, 0.0);
+    h->sensor_jobs.resize(n_legs);
+    std::vector<double> dense;
+    for (int k = 0; k < n_legs; ++k) {
+        const tamols_sensor_leg &l = legs[k];
+        dense.resize((size_t)l.rows * l.cols * 2);
+        double *hz = h->sensor_heights.data() + k * cells, *hxy = h->sensor_xy.data() + k * cells * 2;
+        for (int r = 0; r < l.rows; ++r)
+            for (int c = 0; c < l.cols; ++c) {
+                const double *cell = l.data + ((size_t)r * l.cols + c) * 3;
+                hz[(size_t)r * Cc + c] = cell[2];
+                hxy[((size_t)r * Cc + c) * 2] = cell[0];
+                hxy[((size_t)r * Cc + c) * 2 + 1] = cell[1];
+                dense[((size_t)r * l.cols + c) * 2] = cell[0];
+                dense[((size_t)r * l.cols + c) * 2 + 1] = cell[1];
+            }
+        tamols_leg_job &j = h->sensor_jobs[k];
+        memset(&j, 0, sizeof j);
+        if (int rc = tamols_fit_grid(dense.data(), l.rows, l.cols, j.origin, j.row_axis, j.col_axis)) return rc;
+        j.map = k; j.r0 = 0; j.c0 = 0; j.nr = l.rows; j.nc = l.cols; j.flags = l.flags;
+        memcpy(j.seed, l.seed, sizeof j.seed);
+        memcpy(j.hip, l.hip, sizeof j.hip);
+        memcpy(j.diag_foot, l.diag_foot, sizeof j.diag_foot);
+        memcpy(j.base_xy, l.base_xy, sizeof j.base_xy);
+        memcpy(j.vel, l.vel, sizeof j.vel);
+    }
+    return tamols_score_host(h, h->sensor_heights.data(), n_legs, R, Cc, h->sensor_xy.data(), h->sensor_jobs.data(), n_legs,
+                             results, nullptr, 0);
 }

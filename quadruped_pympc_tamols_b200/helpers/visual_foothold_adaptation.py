@@ -92,31 +92,26 @@ class VisualFootholdAdaptation:
         return True
 
     def _score_on_gpu(self, legs_order, reference_footholds, hip_positions, heightmaps):
-        """Pack the legs into tamols_leg_job records and run the single scoring launch."""
+        """Describe the legs (sensor array address + the per-leg vectors) and make the single C call that packs the
+        job records and runs the one scoring launch (tamols_score_sensors)."""
         n = len(legs_order)
         # self.tamols_params is read with .get() on every call upstream, so a changed dict takes effect here too
         if self.tamols_params != self._params_seen:
             self._handle.set_params(tc.make_params(self.tamols_params, self.robot_name))
             self._params_seen = copy.deepcopy(self.tamols_params)
-        datas = [np.asarray(heightmaps[name].data, np.float64)[:, :, 0, :] for name in legs_order]
-        R = max(d.shape[0] for d in datas)
-        Cc = max(d.shape[1] for d in datas)
-        pk = self._pack.get((n, R, Cc))
-        if pk is None:  # staging arrays per (legs, map shape), reused across calls
-            pk = self._pack[(n, R, Cc)] = (np.zeros((n, R, Cc)), np.zeros((n, R, Cc, 2)), np.zeros(n, tc.JOB_DTYPE))
-        heights, xy, jobs = pk
+        legs = self._pack.get(n)
+        if legs is None:
+            legs = self._pack[n] = np.zeros(n, tc.SENSOR_LEG_DTYPE)
         vel = None if self.forward_vel is None else np.asarray(self.forward_vel, np.float64)
-        win = np.zeros((n, 5), np.int32)       # map, r0, c0, nr, nc
-        grid = np.zeros((n, 3, 2))             # origin, row_axis, col_axis
-        flags = np.zeros(n, np.int32)
-        stab = np.zeros((n, 2, 2))             # base_xy, diag_foot
+        keep, ptr, shape, flags = [], [], [], []
+        stab = np.zeros((n, 2, 2))  # base_xy, diag_foot
         for k, name in enumerate(legs_order):
-            d = datas[k]
-            nr, nc = d.shape[:2]
-            heights[k, :nr, :nc] = d[..., 2]
-            xy[k, :nr, :nc] = d[..., :2]
-            grid[k] = tc.fit_grid(d[..., :2])
-            win[k] = (k, 0, 0, nr, nc)
+            d = np.ascontiguousarray(heightmaps[name].data, np.float64)  # [R, C, 1, 3]
+            if d.ndim != 4 or d.shape[2] != 1 or d.shape[3] != 3:
+                raise tc.TamolsError(f"heightmap data of leg {name} has shape {d.shape}, expected [rows, cols, 1, 3]")
+            keep.append(d)
+            ptr.append(d.ctypes.data)
+            shape.append(d.shape[:2])
             f = tc.FLAG_HAS_VELOCITY if vel is not None else 0
             # _compute_stability_cost preconditions, :631-664 (leg_id is the position in legs_order)
             diag = tc.DIAGONAL.get(name)
@@ -128,17 +123,16 @@ class VisualFootholdAdaptation:
                 f |= tc.FLAG_STABILITY
                 stab[k, 0] = np.asarray(self.base_position, np.float64)[:2]
                 stab[k, 1] = np.asarray(getattr(self.current_feet_pos, diag), np.float64)[:2]
-            flags[k] = f
+            flags.append(f)
         # one assignment per record field for all legs (numpy fills structured arrays field by field: slow per item)
-        jobs["map"], jobs["r0"], jobs["c0"], jobs["nr"], jobs["nc"] = win.T
-        jobs["flags"] = flags
-        jobs["origin"], jobs["row_axis"], jobs["col_axis"] = grid[:, 0], grid[:, 1], grid[:, 2]
-        jobs["seed"] = [np.asarray(reference_footholds[name], np.float64) for name in legs_order]
-        jobs["hip"] = [np.asarray(hip_positions[name], np.float64) for name in legs_order]
-        jobs["vel"] = vel if vel is not None else 0.0
-        jobs["base_xy"], jobs["diag_foot"] = stab[:, 0], stab[:, 1]
-        results, _ = self._handle.score_host(heights, jobs, xy=xy)
-        return results
+        legs["data"] = ptr
+        legs["rows"], legs["cols"] = np.asarray(shape, np.int32).T
+        legs["flags"] = flags
+        legs["seed"] = [np.asarray(reference_footholds[name], np.float64) for name in legs_order]
+        legs["hip"] = [np.asarray(hip_positions[name], np.float64) for name in legs_order]
+        legs["vel"] = vel if vel is not None else 0.0
+        legs["base_xy"], legs["diag_foot"] = stab[:, 0], stab[:, 1]
+        return self._handle.score_sensors(legs)  # `keep` holds the sensor arrays until the call returns
 
     def close(self):
         if self._handle is not None:
