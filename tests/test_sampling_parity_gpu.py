@@ -389,3 +389,48 @@ def test_quad_block_sizes_agree(monkeypatch, method):
             assert np.array_equal(outs[0]["best"], o["best"])
         else:
             assert np.max(np.abs(outs[0]["best"] - o["best"])) <= 1e-5 * max(1.0, float(np.max(np.abs(o["best"]))))
+
+
+@pytest.mark.parametrize("method,param,ga,horizon,splines,n", [
+    ("mppi", "zero_order", False, 20, 1, 4500),       # P = 240: inputs exceed the kernel parameter block -> H2D copy path
+    ("random_sampling", "linear_spline", True, 8, 3, 2000),
+    ("cem_mppi", "cubic_spline", False, 16, 4, 3000),  # P = 192
+    ("mppi", "cubic_spline", True, 5, 1, 10000),       # short horizon, full-size sample count (one wave of quad blocks)
+])
+def test_other_horizons_and_spline_counts(method, param, ga, horizon, splines, n, kernel):
+    """mpc_params['horizon'] and ['num_splines'] away from the defaults (12, 2): every kernel, chained over two
+    iterations, against the oracle on the very same noise."""
+    rng = np.random.default_rng(horizon * 100 + splines)
+    mass, inertia, _, _ = ROBOTS["go2"]
+    kw = dict(mass=mass, inertia=np.array(inertia), parametrization=param, gait_adaptive=ga, horizon=horizon,
+              num_splines=splines)
+    h = _cabi.Handle(_cabi.make_config(sampling_method=method, num_parallel_computations=n, **kw))
+    ocfg = so.make_cfg(**kw)
+    P = h.P
+    assert P == {"zero_order": 12 * horizon, "linear_spline": 12 * (splines + 1), "cubic_spline": 48 * splines}[param]
+    st, ref, seq, timing, nominal = synth_problem("go2", "trot", rng, horizon=horizon)
+    best = rng.normal(size=P).astype(np.float32)
+    sigma = np.full(P, 3.0, np.float32)
+    d_eps = torch.empty((n, P), dtype=torch.float32, device="cuda")
+    d_freqs = torch.empty(n, dtype=torch.float32, device="cuda")
+    for it in range(2):
+        h.generate_noise(11, it, d_eps.data_ptr(), d_freqs.data_ptr(), sigma_in=sigma if method == "cem_mppi" else None,
+                         nominal_freq=nominal, optimize_swing=1)
+        eps = d_eps.cpu().numpy()
+        freqs = d_freqs.cpu().numpy() if ga else None
+        r = h.solve(st, ref, seq, best, seed=11, offset=it, timing=timing, nominal_freq=nominal, optimize_swing=1,
+                    sigma_in=sigma if method == "cem_mppi" else None)
+        o = so.solve(ocfg, method, st, ref, seq, best, eps, timing=timing, freqs=freqs, fast=False)
+        compare(r, o, method, tag=f"H{horizon}S{splines}it{it}", eps=eps, best_in=best)
+        best = r["best"]
+        if method == "cem_mppi":
+            sigma = r["sigma"]
+    # the two iterations chained on the device give the same final mean
+    best0 = rng.normal(size=P).astype(np.float32)
+    a = h.solve(st, ref, seq, best0, 11, 5, timing=timing, nominal_freq=nominal, optimize_swing=1,
+                sigma_in=np.full(P, 3.0, np.float32) if method == "cem_mppi" else None)
+    b = h.solve(st, ref, seq, a["best"], 11, 6, timing=timing, nominal_freq=nominal, optimize_swing=1, sigma_in=a["sigma"])
+    c2 = h.solve(st, ref, seq, best0, 11, 5, timing=timing, nominal_freq=nominal, optimize_swing=1,
+                 sigma_in=np.full(P, 3.0, np.float32) if method == "cem_mppi" else None, iterations=2)
+    assert np.array_equal(b["best"], c2["best"]) and np.array_equal(b["costs"], c2["costs"])
+    h.close()
