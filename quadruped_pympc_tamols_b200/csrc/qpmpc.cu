@@ -53,6 +53,7 @@ struct SolveArgs {
     int nblk;         // rollout blocks per robot
     int robot_offset; // global id of robot 0 of this launch (Philox subsequence = robot_offset + r)
     int fused;        // 1: the last rollout block of a robot runs finalize_robot itself (one launch per solve)
+    int pipe;         // 1: zero-order fixed-gait rollouts draw the noise of steps n+4.. while integrating step n
     int inline_in;    // bit 0: state / reference / contact / timing / nominal / oswing, bit 1: best, bit 2: sigma hold
                       // BYTE OFFSETS into the kernel's InlineIn parameter instead of device addresses
 };
@@ -169,6 +170,109 @@ __device__ __forceinline__ void noise_group_row2(const RowNoise &rn, const Noise
 __device__ __forceinline__ float4 noise_group(const DevCfg &c, const NoiseKey &nk, const float *sigma_vec, int i,
                                               int g, uint32_t robot) {
     return noise_group_row(row_noise(c, i), nk, sigma_vec, g, robot);
+}
+
+// The same values as noise_group_row WITHOUT control flow, so that a caller's independent arithmetic can share a
+// basic block (and the instruction scheduler) with the Philox / Box-Muller chain.  NS = true: scalar-sigma normals
+// only (mppi; mode 0, or mode 3 for row 0); NS = false: any mode, the unused variants are computed and deselected.
+template <bool NS>
+__device__ __forceinline__ float4 noise_group_flat(const RowNoise &rn, const NoiseKey &nk, const float *sigma_vec, int g,
+                                                   uint32_t robot) {
+    const uint4 x = draw(nk, rn.stream, g, rn.sample, robot);
+    float4 e = normal4_scaled(x, rn.k);
+    if (!NS) {
+        const float a = rn.k, w = __fmul_rn(2.0f, a);
+        const bool uni = rn.mode == 1;
+        e.x = uni ? __fmaf_rn(u01_half_open(x.x), w, -a) : e.x;
+        e.y = uni ? __fmaf_rn(u01_half_open(x.y), w, -a) : e.y;
+        e.z = uni ? __fmaf_rn(u01_half_open(x.z), w, -a) : e.z;
+        e.w = uni ? __fmaf_rn(u01_half_open(x.w), w, -a) : e.w;
+        float4 sg = make_float4(1.f, 1.f, 1.f, 1.f);  // z * 1 = z exactly
+        if (rn.mode == 2) sg = *reinterpret_cast<const float4 *>(sigma_vec + 4 * g);
+        e = make_float4(__fmul_rn(e.x, sg.x), __fmul_rn(e.y, sg.y), __fmul_rn(e.z, sg.z), __fmul_rn(e.w, sg.w));
+    }
+    const bool zero = rn.mode == 3;
+    return make_float4(zero ? 0.f : e.x, zero ? 0.f : e.y, zero ? 0.f : e.z, zero ? 0.f : e.w);
+}
+
+// Zero-order, fixed-gait rollout with the noise drawn on the way (in-kernel Philox only, H a multiple of 4).
+// Parameter p = (3 leg + axis) H + n is used at step n alone and lives in Philox group p / 4, so the 12 groups
+// {j H/4 + q, j = 3 leg + axis} hold exactly the steps 4q..4q+3.  The prologue draws the groups of steps 0..3; step
+// n of the loop then draws three of the twelve groups of the NEXT four steps while it integrates: two independent
+// instruction streams (Philox integer/SFU work and the SRBD FMA chain) in one basic block, which the scheduler
+// interleaves.  With 3 warps per scheduler (shared-memory bound) the separate fill -> rollout phases left 38 % of
+// the issue slots empty behind fixed-latency dependencies (profiles/r2r_ncu_details_c5.txt).  Same groups into the
+// same shared cells as the two-phase path: costs and partials are bit-identical (QPMPC_PIPE=0 runs the other one).
+template <int STRIDE, bool NS>
+__device__ __forceinline__ float rollout_fixed_zo_pipe(const DevCfg &c, const float *s_state, const float *s_ref,
+                                                       const FixedTables &tb, float *col, const float *s_best,
+                                                       const float *s_sigma, const RowNoise &rn, const NoiseKey &key,
+                                                       uint32_t robot) {
+    const int H = c.H, HQ = H >> 2, hs = H * STRIDE;
+#pragma unroll 1
+    for (int j = 0; j < 12; j += 2) {
+        const int ga = j * HQ, gb = ga + HQ;
+        float4 ea, eb;
+        noise_group_row2(rn, key, s_sigma, ga, gb, robot, ea, eb);
+        const float4 ba = *reinterpret_cast<const float4 *>(s_best + 4 * ga);
+        const float4 bb = *reinterpret_cast<const float4 *>(s_best + 4 * gb);
+        float *da = col + 4 * ga * STRIDE, *db = col + 4 * gb * STRIDE;
+        da[0] = ba.x + ea.x; da[STRIDE] = ba.y + ea.y; da[2 * STRIDE] = ba.z + ea.z; da[3 * STRIDE] = ba.w + ea.w;
+        db[0] = bb.x + eb.x; db[STRIDE] = bb.y + eb.y; db[2 * STRIDE] = bb.z + eb.z; db[3 * STRIDE] = bb.w + eb.w;
+    }
+    Problem pb;
+    load_problem(pb, s_state, s_ref);
+    float cost = 0.f;
+    const float *pz = col;
+    int n = 0;
+#pragma unroll 1
+    for (; n < H - 4; ++n) {
+        // every shared-memory read of the iteration first: nothing below has to wait behind the stores
+        float f[4][3];
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+            const float *p = pz + l * 3 * hs;
+            f[l][0] = p[0]; f[l][1] = p[hs]; f[l][2] = p[2 * hs];
+        }
+        const float4 st4 = *reinterpret_cast<const float4 *>(tb.st + 8 * n);
+        const float4 st34 = *reinterpret_cast<const float4 *>(tb.st + 8 * n + 4);
+        const float ref_fz = tb.reffz[n];
+        const int g0 = 3 * (n & 3) * HQ + (n >> 2) + 1;  // groups (3 (n & 3) + {0, 1, 2}) HQ + q, q = n / 4 + 1
+        const float4 b0 = *reinterpret_cast<const float4 *>(s_best + 4 * g0);
+        const float4 b1 = *reinterpret_cast<const float4 *>(s_best + 4 * (g0 + HQ));
+        const float4 b2 = *reinterpret_cast<const float4 *>(s_best + 4 * (g0 + 2 * HQ));
+        const float4 e0 = noise_group_flat<NS>(rn, key, s_sigma, g0, robot);
+        const float4 e1 = noise_group_flat<NS>(rn, key, s_sigma, g0 + HQ, robot);
+        const float4 e2 = noise_group_flat<NS>(rn, key, s_sigma, g0 + 2 * HQ, robot);
+        const float st[4] = {st4.x, st4.y, st4.z, st4.w}, st3[4] = {st34.x, st34.y, st34.z, st34.w};
+#pragma unroll
+        for (int l = 0; l < 4; ++l) shape_leg(c, f[l], st[l], st3[l], ref_fz);
+        body_step(c, pb.x, pb.feet, pb.ref, f, st, c.dts[n], cost);
+        float *d = col + 4 * g0 * STRIDE;
+        d[0] = b0.x + e0.x; d[STRIDE] = b0.y + e0.y; d[2 * STRIDE] = b0.z + e0.z; d[3 * STRIDE] = b0.w + e0.w;
+        d += 4 * HQ * STRIDE;
+        d[0] = b1.x + e1.x; d[STRIDE] = b1.y + e1.y; d[2 * STRIDE] = b1.z + e1.z; d[3 * STRIDE] = b1.w + e1.w;
+        d += 4 * HQ * STRIDE;
+        d[0] = b2.x + e2.x; d[STRIDE] = b2.y + e2.y; d[2 * STRIDE] = b2.z + e2.z; d[3 * STRIDE] = b2.w + e2.w;
+        pz += STRIDE;
+    }
+#pragma unroll 1
+    for (; n < H; ++n) {
+        const float4 st4 = *reinterpret_cast<const float4 *>(tb.st + 8 * n);
+        const float4 st34 = *reinterpret_cast<const float4 *>(tb.st + 8 * n + 4);
+        const float st[4] = {st4.x, st4.y, st4.z, st4.w}, st3[4] = {st34.x, st34.y, st34.z, st34.w};
+        const float ref_fz = tb.reffz[n];
+        float f[4][3];
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+            const float *p = pz + l * 3 * hs;
+            f[l][0] = p[0]; f[l][1] = p[hs]; f[l][2] = p[2 * hs];
+            shape_leg(c, f[l], st[l], st3[l], ref_fz);
+        }
+        body_step(c, pb.x, pb.feet, pb.ref, f, st, c.dts[n], cost);
+        pz += STRIDE;
+    }
+    return cost;
 }
 
 // step_frequencies_vec[i]: ..._gait_adaptive.py:687-692 (random_sampling), :834-838 (mppi), :994-999 (cem)
@@ -687,7 +791,12 @@ __global__ void __launch_bounds__(T, T == 128 ? 3 : 1) k_rollout(const __grid_co
 
     // ---- this thread's parameter vector -> shared column t
     const uint32_t robot = (uint32_t)(r + a.robot_offset);
-    if (a.eps) {
+    // zero-order fixed-gait launches with in-kernel noise draw it while they integrate (rollout_fixed_zo_pipe)
+    const bool pipe = PARAM == QPMPC_PARAM_ZERO_ORDER && !GA && a.pipe && !a.eps && !a.costs_only && H >= 4 && (H & 3) == 0;
+    if (pipe) {
+        if (!valid)
+            for (int p = 0; p < P; ++p) s_par[p * STRIDE + t] = 0.f;
+    } else if (a.eps) {
         const float *src = a.eps + ((size_t)r * a.n + (size_t)blockIdx.x * T) * P;
         const int rows = min(T, a.n - blockIdx.x * T);
         for (int e = t; e < T * P; e += T) {
@@ -740,7 +849,14 @@ __global__ void __launch_bounds__(T, T == 128 ? 3 : 1) k_rollout(const __grid_co
             cost = rollout_gait_adaptive<PARAM, STRIDE>(c, s_state, s_ref, s_mgk, s_timing, freq, col);
         } else {
             const FixedTables tb = {s_st, s_reffz, s_basis, s_index};
-            cost = rollout_fixed<PARAM, STRIDE>(c, s_state, s_ref, tb, col);
+            if (PARAM == QPMPC_PARAM_ZERO_ORDER && pipe) {
+                const RowNoise rn = row_noise(c, i);
+                cost = c.method == QPMPC_METHOD_MPPI
+                           ? rollout_fixed_zo_pipe<STRIDE, true>(c, s_state, s_ref, tb, s_par + t, s_best, s_sigma, rn, a.key, robot)
+                           : rollout_fixed_zo_pipe<STRIDE, false>(c, s_state, s_ref, tb, s_par + t, s_best, s_sigma, rn, a.key, robot);
+            } else {
+                cost = rollout_fixed<PARAM, STRIDE>(c, s_state, s_ref, tb, col);
+            }
         }
         if (!a.costs_only) {  // centroidal_nmpc_jax.py:686-687
             cost = isnan(cost) ? 1000000.0f : cost;
@@ -1131,21 +1247,23 @@ typedef void (*rollout_fn)(const qp::DevCfg, const qp::RolloutArgs, const qp::In
 
 // Experiment switches, read from the environment ONCE per handle (qpmpc_create): five getenv calls per solve were
 // measurable on a 30 us call.  QPMPC_KERNEL=quad|thread, QPMPC_QB=32|72|128, QPMPC_FUSED=0, QPMPC_ZEROCOPY=0|1,
-// QPMPC_INPUTS=copy|mapped.
+// QPMPC_INPUTS=copy|mapped, QPMPC_PIPE=0.
 struct EnvSwitches {
     int kernel;    // 0 auto, 1 quad, 2 thread
     int qb;        // 0 auto, else 32 / 72 / 128
     int fused;     // 0: stand-alone k_finalize
     int zerocopy;  // -1 unset, 0 classic copies, 1 inputs mapped too
     int inputs;    // 0 auto (parameter block), 1 copy, 2 mapped
+    int pipe;      // 0: noise fill and rollout as two separate phases (QPMPC_PIPE=0)
 };
 static EnvSwitches read_env() {
-    EnvSwitches e = {0, 0, 1, -1, 0};
+    EnvSwitches e = {0, 0, 1, -1, 0, 1};
     if (const char *k = getenv("QPMPC_KERNEL")) e.kernel = !strcmp(k, "quad") ? 1 : !strcmp(k, "thread") ? 2 : 0;
     if (const char *q = getenv("QPMPC_QB")) e.qb = atoi(q) == 128 ? 128 : atoi(q) == 72 ? 72 : 32;
     if (const char *f = getenv("QPMPC_FUSED")) e.fused = f[0] == '0' ? 0 : 1;
     if (const char *z = getenv("QPMPC_ZEROCOPY")) e.zerocopy = z[0] == '0' ? 0 : z[0] == '1' ? 1 : -1;
     if (const char *i = getenv("QPMPC_INPUTS")) e.inputs = !strcmp(i, "copy") ? 1 : !strcmp(i, "mapped") ? 2 : 0;
+    if (const char *q = getenv("QPMPC_PIPE")) e.pipe = q[0] == '0' ? 0 : 1;
     return e;
 }
 
@@ -1420,6 +1538,7 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
     const int K = d.method == QPMPC_METHOD_CEM ? d.cem_elite : 0;
     const int scratch = pl.quad ? P * (pl.T / 4 + 1) : P * (pl.T + 1);
     ra.fused = finalize_smem_floats(P, nblk, K, pl.T) <= scratch && h->env.fused;
+    ra.pipe = h->env.pipe;
     if (h->profiling) CU(cudaEventRecord(h->ev[0], h->stream));
     pick_fn(h, pl)<<<dim3(nblk, R), pl.T, pl.smem, h->stream>>>(d, ra, in);
     CU(cudaGetLastError());
