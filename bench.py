@@ -390,9 +390,32 @@ def run_batched(torch, _cabi, dev, local_rank, rank, world, barrier, max_over_ra
                                  go.expand_dts([0.02], [12], 12))
             reps += 1
         gait["cpu_numpy_ms"] = (time.perf_counter() - t0) / reps * 1e3
+    # ---- the step behind the solve, tau = -J^T f from the result records left on the device
+    d_jac = torch.as_tensor(rng.normal(size=(R, 4, 3, 3)), dtype=torch.float64, device=dev)
+    d_tau = torch.zeros((R, 4, 3), dtype=torch.float64, device=dev)
+    tq_ms = []
+    with torch.cuda.stream(stream):
+        for it in range(13):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            h.stance_torques(R, d_res.data_ptr(), d_jac.data_ptr(), d_tau.data_ptr())
+            e1.record(stream)
+            e1.synchronize()
+            if it >= 3:
+                tq_ms.append(e0.elapsed_time(e1))
+    torque = {"workload": f"stance torques [R,4,3] f64 of {R} robots per rank (wb_interface.py:368-371), from the device result records",
+              "p50_ms": float(np.median(tq_ms)), "robots_per_s": robots_total / (max_over_ranks(float(np.median(tq_ms))) * 1e-3),
+              "algorithmic_bytes": R * (4 * 9 * 8 + 12 * 4 + 12 * 8),
+              "note": "3.5 MB of traffic per launch: launch-latency-bound"}
+    if rank == 0 and world == 1:
+        from oracle import torque_oracle as tq  # CPU leg only
+        jac_h, grf_h = d_jac.cpu().numpy(), d_res.cpu().numpy()[:, :12]
+        t0 = time.perf_counter()
+        tq.stance_torques(jac_h, grf_h)
+        torque["cpu_numpy_ms"] = (time.perf_counter() - t0) * 1e3
     h.close()
     return {"workload": f"C5: {robots_total} robots x {n} rollouts, MPPI zero_order (P=144), aliengo trot; {R} robots per rank",
-            "gait_clock": gait,
+            "gait_clock": gait, "stance_torques": torque,
             "value": robots_total * n / (step_ms * 1e-3), "unit": "rollouts/s", "robot_solves_per_s": robots_total / (step_ms * 1e-3),
             "ms_per_step": step_ms, "scaling": "strong",
             "roofline": {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak,

@@ -205,6 +205,15 @@ int qpmpc_contact_sequences(qpmpc_handle *h, const qpmpc_gait_batch *g);
 /* run(dt, step_freq) for every robot: advances d_phase / d_init in place and writes the current contact flags. */
 int qpmpc_gait_run(qpmpc_handle *h, const qpmpc_gait_batch *g, double dt);
 
+/* ---- the step behind the solve for a batch of robots, the stance torque mapping
+ * tau[leg] = -feet_jac[leg][:, legs_qvel_idx[leg]].T @ nmpc_GRFs[leg]  (interfaces/wb_interface.py:368-371), computed from
+ * the result records qpmpc_solve_batched left on the device (no host round trip between solve and torques).
+ * d_result [R] (qpmpc_batch.d_result), d_feet_jac [R,4,3,3] float64 = each leg's 3 x 3 translational Jacobian block,
+ * row-major (upstream takes it from MuJoCo), d_tau [R,4,3] float64 out.  The swing legs' entries are overwritten by the
+ * swing controller upstream (:377-396), exactly as there.  Asynchronous on the handle's stream. */
+int qpmpc_stance_torques(qpmpc_handle *h, int32_t num_robots, const qpmpc_result *d_result, const double *d_feet_jac,
+                         double *d_tau);
+
 #ifdef __cplusplus
 }
 #endif

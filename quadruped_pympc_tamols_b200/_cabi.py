@@ -68,7 +68,8 @@ class QpmpcGaitBatch(C.Structure):  # include/qpmpc.h: qpmpc_gait_batch
 
 EXPORTS = ["qpmpc_create", "qpmpc_destroy", "qpmpc_num_params", "qpmpc_last_error", "qpmpc_version", "qpmpc_stream",
            "qpmpc_launch_count", "qpmpc_solve", "qpmpc_solve_iterated", "qpmpc_copy_costs", "qpmpc_solve_batched", "qpmpc_rollout_costs", "qpmpc_generate_noise", "qpmpc_set_profiling", "qpmpc_profile_last",
-           "qpmpc_measure_fp32_peak", "qpmpc_contact_sequences", "qpmpc_gait_run"]
+           "qpmpc_measure_fp32_peak", "qpmpc_contact_sequences", "qpmpc_gait_run",
+           "qpmpc_stance_torques"]
 
 
 def build(force=False):
@@ -114,6 +115,7 @@ def lib():
         L.qpmpc_measure_fp32_peak.argtypes = [C.c_int32, fp]
         L.qpmpc_contact_sequences.argtypes = [vp, C.POINTER(QpmpcGaitBatch)]
         L.qpmpc_gait_run.argtypes = [vp, C.POINTER(QpmpcGaitBatch), C.c_double]
+        L.qpmpc_stance_torques.argtypes = [vp, C.c_int32, vp, vp, vp]
         _LIB = L
     return _LIB
 
@@ -331,6 +333,10 @@ class Handle:
 
     def gait_run(self, gait_batch: QpmpcGaitBatch, dt):
         check(lib().qpmpc_gait_run(self._h, C.byref(gait_batch), float(dt)))
+
+    def stance_torques(self, num_robots, d_result, d_feet_jac, d_tau):
+        """tau[R,4,3] = -J^T f from the device result records (wb_interface.py:368-371); device addresses."""
+        check(lib().qpmpc_stance_torques(self._h, int(num_robots), d_result, d_feet_jac, d_tau))
 
     def rollout_costs(self, state, reference, contact_sequence, d_params, n, d_costs, timing=None, d_freqs=None):
         st, rf, cs = _f32(state).reshape(24), _f32(reference).reshape(24), _f32(contact_sequence)

@@ -1808,6 +1808,33 @@ extern "C" int qpmpc_contact_sequences(qpmpc_handle *h, const qpmpc_gait_batch *
     return QPMPC_OK;
 }
 
+// tau[leg] = -J_leg^T f_leg (interfaces/wb_interface.py:368-371) for a batch of robots, straight
+// from the result records the solve left on the device.  One thread per (robot, leg); float64 like numpy, the float32
+// forces widened first (numpy promotes the jax float32 array the same way).
+__global__ void k_stance_torques(int num_robots, const qpmpc_result *__restrict__ res, const double *__restrict__ jac,
+                                 double *__restrict__ tau) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= num_robots * 4) return;
+    const int r = idx >> 2, leg = idx & 3;
+    const double *J = jac + (size_t)idx * 9;  // feet_jac[leg][:, legs_qvel_idx[leg]], row-major 3 x 3
+    const double f0 = (double)res[r].grf[3 * leg], f1 = (double)res[r].grf[3 * leg + 1], f2 = (double)res[r].grf[3 * leg + 2];
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+        tau[(size_t)idx * 3 + j] = -__dadd_rn(__dadd_rn(__dmul_rn(J[j], f0), __dmul_rn(J[3 + j], f1)), __dmul_rn(J[6 + j], f2));
+}
+
+extern "C" int qpmpc_stance_torques(qpmpc_handle *h, int32_t num_robots, const qpmpc_result *d_result,
+                                    const double *d_feet_jac, double *d_tau) {
+    if (!h) return fail(QPMPC_E_ARG, "null handle");
+    if (num_robots < 1 || !d_result || !d_feet_jac || !d_tau) return fail(QPMPC_E_ARG, "stance_torques: null pointer or no robots");
+    CU(cudaSetDevice(h->device));
+    const int threads = 128, blocks = (num_robots * 4 + threads - 1) / threads;
+    k_stance_torques<<<blocks, threads, 0, h->stream>>>(num_robots, d_result, d_feet_jac, d_tau);
+    CU(cudaGetLastError());
+    h->launches += 1;
+    return QPMPC_OK;
+}
+
 extern "C" int qpmpc_gait_run(qpmpc_handle *h, const qpmpc_gait_batch *g, double dt) {
     if (int rc = gait_check(h, g)) return rc;
     CU(cudaSetDevice(h->device));
