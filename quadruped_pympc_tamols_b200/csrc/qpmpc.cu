@@ -737,8 +737,82 @@ __device__ __forceinline__ void weighted_rows(const float *s_par, float *s_w, un
     }
 }
 
+// Block partials of the thread-per-rollout kernel with the fewest barriers: the same arithmetic in the same order as
+// block_argmin + block_sum + weighted_rows (bit-identical partials), but each reduction owns its slice of s_red, so no
+// barrier is needed to recycle it, and the softmin sum travels with the live-sample count: 3 barriers instead of 7
+// in front of the arrival ticket.  s_red: [0, 8) cost minima | [8, 16) their indices | [16, 24) sums | [24, 32) counts.
+template <int STRIDE>
+__device__ __forceinline__ void rollout_block_partials(const DevCfg &c, const float *s_par, float *s_w, unsigned short *s_live,
+                                                       float *s_red, float cost, bool valid, int i, int P, float *part) {
+    const int t = threadIdx.x, T = blockDim.x, lane = t & 31, wid = t >> 5, nw = T >> 5;
+    float bc = cost;
+    int bi = valid ? i : 0x7fffffff;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float oc = __shfl_xor_sync(0xffffffffu, bc, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        argmin_combine(bc, bi, oc, oi);
+    }
+    if (lane == 0) {
+        s_red[wid] = bc;
+        s_red[8 + wid] = __int_as_float(bi);
+    }
+    __syncthreads();
+    bc = s_red[0];
+    bi = __float_as_int(s_red[8]);
+    for (int w = 1; w < nw; ++w) argmin_combine(bc, bi, s_red[w], __float_as_int(s_red[8 + w]));
+    if (c.method == QPMPC_METHOD_RANDOM) {
+        if (t == 0) {
+            part[0] = bc;
+            part[1] = 0.f;
+            part[2] = bc;
+            part[3] = __int_as_float(bi);
+        }
+        return;
+    }
+    // softmin numerators relative to the block minimum (merged exactly by finalize_robot), :828-836
+    const float w = valid ? __expf(-(cost - bc)) : 0.f;
+    float v = w;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    const bool live = w > 0.f;
+    const unsigned m = __ballot_sync(0xffffffffu, live);
+    if (lane == 0) {
+        s_red[16 + wid] = v;
+        s_red[24 + wid] = __int_as_float(__popc(m));
+    }
+    __syncthreads();
+    float sw = s_red[16];
+    for (int k = 1; k < nw; ++k) sw += s_red[16 + k];
+    int base = 0, total = 0;
+    for (int k = 0; k < nw; ++k) {
+        const int cnt = __float_as_int(s_red[24 + k]);
+        base += k < wid ? cnt : 0;
+        total += cnt;
+    }
+    if (t == 0) {
+        part[0] = bc;
+        part[1] = sw;
+        part[2] = bc;
+        part[3] = __int_as_float(bi);
+    }
+    if (live) {
+        const int k = base + __popc(m & ((1u << lane) - 1u));
+        s_live[k] = (unsigned short)t;
+        s_w[k] = w;
+    }
+    __syncthreads();
+    // finalize_robot turns sum_b scale_b V_b / sum_b scale_b sw_b into the updated parameters
+    for (int p = t; p < P; p += T) {
+        const float *row = s_par + p * STRIDE;
+        float acc = 0.f;
+        for (int k = 0; k < total; ++k) acc = fmaf(s_w[k], row[s_live[k]], acc);
+        part[PART_HDR + p] = acc;
+    }
+}
+
 template <int PARAM, bool GA, int T>
-__global__ void __launch_bounds__(T, T == 128 ? 3 : 1) k_rollout(const __grid_constant__ DevCfg c, const RolloutArgs a_,
+__global__ void __launch_bounds__(T, T == 128 ? 3 : T == 64 ? 6 : 1) k_rollout(const __grid_constant__ DevCfg c, const RolloutArgs a_,
                                                                   const __grid_constant__ InlineIn in) {
     const RolloutArgs a = resolve_inputs(a_, in);
     extern __shared__ __align__(16) float smem[];
@@ -867,30 +941,9 @@ __global__ void __launch_bounds__(T, T == 128 ? 3 : 1) k_rollout(const __grid_co
     if (a.costs_only) return;
 
     // ---- block partials
-    float bc = cost;
-    int bi = valid ? i : 0x7fffffff;
-    block_argmin(bc, bi, s_red);
     float *part = a.partials + ((size_t)r * a.nblk + blockIdx.x) * (PART_HDR + P);
-    if (c.method == QPMPC_METHOD_RANDOM) {
-        if (t == 0) {
-            part[0] = bc;
-            part[1] = 0.f;
-            part[2] = bc;
-            part[3] = __int_as_float(bi);
-        }
-    } else {
-        // softmin numerators relative to the block minimum (merged exactly by finalize_robot), :828-836
-        const float w = valid ? __expf(-(cost - bc)) : 0.f;
-        const float sw = block_sum(w, s_red);
-        if (t == 0) {
-            part[0] = bc;
-            part[1] = sw;
-            part[2] = bc;
-            part[3] = __int_as_float(bi);
-        }
-        // finalize_robot turns sum_b scale_b V_b / sum_b scale_b sw_b into the updated parameters
-        weighted_rows<STRIDE>(s_par, s_w, s_live, s_red, w, P, part);
-    }
+    static_assert(T <= 256, "rollout_block_partials keeps one s_red slot per warp in slices of 8");
+    rollout_block_partials<STRIDE>(c, s_par, s_w, s_live, s_red, cost, valid, i, P, part);
     if (a.fused && last_block_of_robot(a.tickets + r, a.nblk)) finalize_robot(c, resolve_inputs(a_, in), r, s_par);
 }
 
@@ -1251,19 +1304,21 @@ typedef void (*rollout_fn)(const qp::DevCfg, const qp::RolloutArgs, const qp::In
 struct EnvSwitches {
     int kernel;    // 0 auto, 1 quad, 2 thread
     int qb;        // 0 auto, else 32 / 72 / 128
-    int fused;     // 0: stand-alone k_finalize
+    int fused;     // -1 auto (fused unless the launch is many waves deep), 0: stand-alone k_finalize, 1: fused
     int zerocopy;  // -1 unset, 0 classic copies, 1 inputs mapped too
     int inputs;    // 0 auto (parameter block), 1 copy, 2 mapped
     int pipe;      // 0: noise fill and rollout as two separate phases (QPMPC_PIPE=0)
+    int threads;   // 0 auto (128 rollouts per block of the thread-per-rollout kernel), 64 (QPMPC_T=64)
 };
 static EnvSwitches read_env() {
-    EnvSwitches e = {0, 0, 1, -1, 0, 1};
+    EnvSwitches e = {0, 0, -1, -1, 0, 1, 0};
     if (const char *k = getenv("QPMPC_KERNEL")) e.kernel = !strcmp(k, "quad") ? 1 : !strcmp(k, "thread") ? 2 : 0;
     if (const char *q = getenv("QPMPC_QB")) e.qb = atoi(q) == 128 ? 128 : atoi(q) == 72 ? 72 : 32;
     if (const char *f = getenv("QPMPC_FUSED")) e.fused = f[0] == '0' ? 0 : 1;
     if (const char *z = getenv("QPMPC_ZEROCOPY")) e.zerocopy = z[0] == '0' ? 0 : z[0] == '1' ? 1 : -1;
     if (const char *i = getenv("QPMPC_INPUTS")) e.inputs = !strcmp(i, "copy") ? 1 : !strcmp(i, "mapped") ? 2 : 0;
     if (const char *q = getenv("QPMPC_PIPE")) e.pipe = q[0] == '0' ? 0 : 1;
+    if (const char *q = getenv("QPMPC_T")) e.threads = atoi(q) == 64 ? 64 : 0;
     return e;
 }
 
@@ -1273,7 +1328,7 @@ struct qpmpc_handle {
     int device;
     cudaStream_t stream;
     int num_sms;
-    rollout_fn fn128, fn32, fn_quad32, fn_quad72, fn_quad128;
+    rollout_fn fn128, fn64, fn32, fn_quad32, fn_quad72, fn_quad128;
     EnvSwitches env;
     size_t max_smem;
     // single-robot staging: one pinned input block, one pinned output block
@@ -1363,7 +1418,8 @@ static LaunchPlan plan_launch(const qpmpc_handle *h, int n, long long total_roll
         pl.nblk = (n + QB - 1) / QB;
         pl.smem = (size_t)quad_smem_floats(d.P, d.H, QB) * 4;
     } else {
-        const int T = (size_t)rollout_smem_floats(d.P, d.H, 128, d.method == QPMPC_METHOD_CEM) * 4 <= h->max_smem ? 128 : 32;
+        int T = (size_t)rollout_smem_floats(d.P, d.H, 128, d.method == QPMPC_METHOD_CEM) * 4 <= h->max_smem ? 128 : 32;
+        if (T == 128 && h->env.threads == 64) T = 64;
         pl.T = T;
         pl.nblk = (n + T - 1) / T;
         pl.smem = (size_t)rollout_smem_floats(d.P, d.H, T, d.method == QPMPC_METHOD_CEM) * 4;
@@ -1373,7 +1429,7 @@ static LaunchPlan plan_launch(const qpmpc_handle *h, int n, long long total_roll
 
 static rollout_fn pick_fn(const qpmpc_handle *h, const LaunchPlan &pl) {
     if (pl.quad) return pl.T == 512 ? h->fn_quad128 : pl.T == 288 ? h->fn_quad72 : h->fn_quad32;
-    return pl.T == 128 ? h->fn128 : h->fn32;
+    return pl.T == 128 ? h->fn128 : pl.T == 64 ? h->fn64 : h->fn32;
 }
 
 extern "C" const char *qpmpc_last_error(void) { return g_err.c_str(); }
@@ -1441,18 +1497,19 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     }
     h->fn128 = pick_rollout<128>(d.param, d.ga);
     h->fn32 = pick_rollout<32>(d.param, d.ga);
+    h->fn64 = pick_rollout<64>(d.param, d.ga);
     h->fn_quad32 = pick_quad<32>(d.param, d.ga);
     h->fn_quad72 = pick_quad<72>(d.param, d.ga);
     h->fn_quad128 = pick_quad<128>(d.param, d.ga);
     cudaError_t e = cudaSuccess;
     size_t static_smem = 0;  // the kernels' own __shared__ variables come out of the same per-block budget
-    for (rollout_fn f : {h->fn128, h->fn32, h->fn_quad32, h->fn_quad72, h->fn_quad128}) {
+    for (rollout_fn f : {h->fn128, h->fn64, h->fn32, h->fn_quad32, h->fn_quad72, h->fn_quad128}) {
         cudaFuncAttributes fa;
         if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, (const void *)f);
         if (e == cudaSuccess && fa.sharedSizeBytes > static_smem) static_smem = fa.sharedSizeBytes;
     }
     h->max_smem -= static_smem;
-    for (rollout_fn f : {h->fn128, h->fn32, h->fn_quad32, h->fn_quad72, h->fn_quad128})
+    for (rollout_fn f : {h->fn128, h->fn64, h->fn32, h->fn_quad32, h->fn_quad72, h->fn_quad128})
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute((const void *)f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_smem);
     if (e != cudaSuccess) { delete h; return fail(QPMPC_E_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e)); }
@@ -1537,7 +1594,12 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
     // (huge N with tiny P) or when QPMPC_FUSED=0 asks for the two-kernel path (tests cover both).
     const int K = d.method == QPMPC_METHOD_CEM ? d.cem_elite : 0;
     const int scratch = pl.quad ? P * (pl.T / 4 + 1) : P * (pl.T + 1);
-    ra.fused = finalize_smem_floats(P, nblk, K, pl.T) <= scratch && h->env.fused;
+    // Throughput regime (batched robots, many waves of blocks): the stand-alone k_finalize wins -- the arrival ticket
+    // (fence + atomic round trip with the block's warps parked) and a last block that finalizes while two of its
+    // SM's three slots wait cost more than one extra launch (C5: 3.09 -> 2.93 ms).  Latency regime: one launch.
+    const bool deep = !pl.quad && (long long)R * nblk > 8LL * h->num_sms;
+    const bool want_fused = h->env.fused < 0 ? !deep : h->env.fused != 0;
+    ra.fused = finalize_smem_floats(P, nblk, K, pl.T) <= scratch && want_fused;
     ra.pipe = h->env.pipe;
     if (h->profiling) CU(cudaEventRecord(h->ev[0], h->stream));
     pick_fn(h, pl)<<<dim3(nblk, R), pl.T, pl.smem, h->stream>>>(d, ra, in);
