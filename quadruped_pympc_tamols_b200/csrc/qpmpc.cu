@@ -837,17 +837,29 @@ __global__ void __launch_bounds__(T, T == 128 ? 3 : T == 64 ? 6 : 1) k_rollout(c
     const int i = blockIdx.x * T + t;
     const bool valid = i < a.n;
 
-    // ---- stage the per-robot problem and its step tables
-    for (int p = t; p < P; p += T) {
-        s_best[p] = a.costs_only ? 0.f : a.best[(size_t)r * P + p];
-        if (c.method == QPMPC_METHOD_CEM) s_sigma[p] = a.sigma ? a.sigma[(size_t)r * P + p] : 0.f;
-    }
-    for (int k = t; k < 24; k += T) s_state[k] = a.state[r * 24 + k];
-    for (int k = t; k < 12; k += T) s_ref[k] = a.reference[r * 24 + k];
-    if (!GA) {
+    // ---- stage the per-robot problem and its step tables.  Every global load of the thread is issued before its
+    // first store, and the small jobs (state, reference, step tables) go to different warps: with all of them on warp
+    // 0 behind the parameter copy, that warp chained four global round trips while the others sat at the barrier
+    // (9 % of the C5 kernel's stall samples on this one barrier, profiles/r4a_ncu_source_c5.txt).
+    {
+        const bool wide = T >= 128;
+        const int role = wide ? (t >> 5) : 0, tl = wide ? (t & 31) : t;
+        const bool cem = c.method == QPMPC_METHOD_CEM;
+        const bool j_best = t < P, j_state = (!wide || role == 1) && tl < 24, j_ref = (!wide || role == 2) && tl < 12;
+        const bool j_tab = !GA && (!wide || role == 3) && tl < H;
         const float *cs = a.contact + (size_t)r * 4 * H;
-        for (int n = t; n < H; n += T) {
-            const float s0 = cs[n], s1 = cs[H + n], s2 = cs[2 * H + n], s3 = cs[3 * H + n];
+        float bv = 0.f, sv = 0.f, stv = 0.f, rfv = 0.f, s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        if (j_best && !a.costs_only) bv = a.best[(size_t)r * P + t];
+        if (j_best && cem && a.sigma) sv = a.sigma[(size_t)r * P + t];
+        if (j_state) stv = a.state[r * 24 + tl];
+        if (j_ref) rfv = a.reference[r * 24 + tl];
+        if (j_tab) { s0 = cs[tl]; s1 = cs[H + tl]; s2 = cs[2 * H + tl]; s3 = cs[3 * H + tl]; }
+        if (j_best) s_best[t] = bv;
+        if (j_best && cem) s_sigma[t] = sv;
+        if (j_state) s_state[tl] = stv;
+        if (j_ref) s_ref[tl] = rfv;
+        if (j_tab) {
+            const int n = tl;
             s_reffz[n] = c.mg / (((s0 + s1) + s2) + s3);
             s_st[8 * n + 0] = s0; s_st[8 * n + 1] = s1; s_st[8 * n + 2] = s2; s_st[8 * n + 3] = s3;
             s_st[8 * n + 4] = s0 * (1.0f / 3.0f); s_st[8 * n + 5] = s1 * (1.0f / 3.0f);
@@ -857,9 +869,14 @@ __global__ void __launch_bounds__(T, T == 128 ? 3 : T == 64 ? 6 : 1) k_rollout(c
             const float4 B = chunk_basis<PARAM>(chunk_tau(c, (float)n, (float)H, idx));
             *reinterpret_cast<float4 *>(s_basis + 4 * n) = B;
         }
-    } else {
-        if (t < 5) s_mgk[t] = c.mg / (float)t;
-        if (t < 4) s_timing[t] = a.timing[r * 4 + t];
+        for (int p = t + T; p < P; p += T) {
+            s_best[p] = a.costs_only ? 0.f : a.best[(size_t)r * P + p];
+            if (cem) s_sigma[p] = a.sigma ? a.sigma[(size_t)r * P + p] : 0.f;
+        }
+        if (GA) {
+            if (t < 5) s_mgk[t] = c.mg / (float)t;
+            if (t < 4) s_timing[t] = a.timing[r * 4 + t];
+        }
     }
     __syncthreads();
 
