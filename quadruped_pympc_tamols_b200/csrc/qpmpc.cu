@@ -351,7 +351,7 @@ __device__ __forceinline__ void quad_leg_step(const DevCfg &c, float f[3], float
     // lanes 0, 1, 2 of the quad evaluate sin/cos of roll, pitch, yaw and hand them round
     const float ang = leg == 0 ? x[6] : (leg == 1 ? x[7] : x[8]);
     float sa, ca;
-    sincosf(ang, &sa, &ca);
+    sincos_fast(ang, &sa, &ca);
     const float sr = __shfl_sync(0xffffffffu, sa, qbase), cr = __shfl_sync(0xffffffffu, ca, qbase);
     const float sp = __shfl_sync(0xffffffffu, sa, qbase + 1), cp = __shfl_sync(0xffffffffu, ca, qbase + 1);
     const float sy = __shfl_sync(0xffffffffu, sa, qbase + 2), cy = __shfl_sync(0xffffffffu, ca, qbase + 2);

@@ -12,8 +12,9 @@
 //   * the Euler-rate division and the per-sample-gait chunk position use the SFU reciprocal (2 ulp);
 //   * fd's second multiplication of the already masked forces by the contact flag is dropped for fx, fy (an exact
 //     identity there) and kept for fz (a non-zero grf_min makes the clamp lift a swing leg's fz);
-//   * sin/cos stay the 1-ulp library sincosf: the SFU versions (5e-7 absolute) moved costs by ~1e-6 relative, which
-//     the temperature-1 softmin of the update amplifies beyond the 1e-3 bar.
+//   * sin/cos are sincos_fast (srbd.cuh): the library sincosf's accuracy class (1.6 ulp) without its slow-path
+//     branch; the SFU versions (5e-7 absolute) moved costs by ~1e-6 relative, which the temperature-1 softmin of
+//     the update amplifies beyond the 1e-3 bar.
 #pragma once
 #include "srbd.cuh"
 
@@ -47,9 +48,9 @@ __device__ __forceinline__ void body_step(const DevCfg &c, float x[12], const fl
         tz += rx * fy - ry * fx;
     }
     float sr, cr, sp, cp, sy, cy;
-    sincosf(x[6], &sr, &cr);
-    sincosf(x[7], &sp, &cp);
-    sincosf(x[8], &sy, &cy);
+    sincos_fast(x[6], &sr, &cr);
+    sincos_fast(x[7], &sp, &cp);
+    sincos_fast(x[8], &sy, &cy);
     const float wx = x[9], wy = x[10], wz = x[11];
     const float yaw_rate = __fdividef(sr * wy + cr * wz, cp);
     const float pitch_rate = cr * wy - sr * wz;

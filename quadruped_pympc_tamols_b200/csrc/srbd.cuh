@@ -19,6 +19,33 @@ namespace qp {
 
 constexpr int MAX_SPLINES = 16;
 
+// sin and cos of an Euler angle without control flow: three-term Cody-Waite reduction by pi/2 and the two degree-7/8
+// minimax polynomials on [-pi/4, pi/4] (<= 1.6 ulp, 9.3e-8 absolute over |a| < 1e5 against float64, the class of the
+// library sincosf; checked by tests/test_sincos_fast.py on the host arithmetic and by the GPU parity tests).
+// The library sincosf carries an out-of-line Payne-Hanek path behind a branch: three of them per step cut the step
+// body into seven basic blocks and cost BSSY/BSYNC plus instruction-fetch stalls (profiles/r4a_ncu_source_c5.txt).
+// |a| >= 105615 (the library's own switch point), NaN and Inf are evaluated at 0: such a rollout is already lost --
+// the angle itself stays in the state, its cost term is > 2e12 or NaN (-> 1e6 by the saturation).
+__device__ __forceinline__ void sincos_fast(float a, float *sp, float *cp) {
+    const float b = fabsf(a) < 105615.0f ? a : 0.0f;
+    const int q = __float2int_rn(b * 0.636619772f);
+    const float k = (float)q;
+    float r = fmaf(k, -1.5707962513e+0f, b);
+    r = fmaf(k, -7.5497894159e-8f, r);
+    r = fmaf(k, -5.3903029535e-15f, r);
+    const float r2 = r * r;
+    float c = fmaf(r2, 2.443315711809948e-5f, -1.388731625493765e-3f);
+    c = fmaf(c, r2, 4.166664568298827e-2f);
+    c = fmaf(c * r2, r2, fmaf(-0.5f, r2, 1.0f));
+    float s = fmaf(r2, -1.9515295891e-4f, 8.3321608736e-3f);
+    s = fmaf(s, r2, -1.6666654611e-1f);
+    s = fmaf(s * r2, r, r);
+    const bool odd = q & 1;
+    const float ss = odd ? c : s, cc = odd ? s : c;
+    *sp = (q & 2) ? -ss : ss;
+    *cp = ((q + 1) & 2) ? -cc : cc;
+}
+
 // Sample-invariant constants of one controller (kernel parameter, lives in the constant bank).
 struct DevCfg {
     int H, param, S, ga, method, N, P, np;  // np = parameters per leg
