@@ -316,7 +316,7 @@ def run_cuda(args):
                         "transfers": "inputs in the kernel parameter block (host -> device with the launch); results stored by the kernel into mapped pinned host memory as {word, sequence} pairs"},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak,
-                             "traffic": 77568, "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, profiles/r4a_ncu_raw_c2.csv (bytes)",
+                             "traffic": 77568, "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, profiles/r4c_ncu_raw_c2.csv (bytes)",
                              "kernel": "k_rollout_quad<cubic,gait_adaptive,72> (139 blocks x 288 threads; rollouts + fused finalize, one launch per solve)", "launch_ms": float(roll[:, 0].mean()),
                              "finalize_ms": float(roll[:, 1].mean()), "finalize": "fused into the rollout kernel (last block per robot)", "flop_per_rollout": FLOP_PER_ROLLOUT["cubic_spline_ga"],
                              "peak_source": "FP32 FMA-chain microbenchmark in this run (qpmpc_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 figure",
@@ -419,10 +419,10 @@ def run_batched(torch, _cabi, dev, local_rank, rank, world, barrier, max_over_ra
             "value": robots_total * n / (step_ms * 1e-3), "unit": "rollouts/s", "robot_solves_per_s": robots_total / (step_ms * 1e-3),
             "ms_per_step": step_ms, "scaling": "strong",
             "roofline": {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak,
-                         "traffic": 24273408 // world, "traffic_source": "profiles/r4a_ncu_raw_c5.csv (dram read + write bytes per launch at 8192 robots)",
+                         "traffic": 23960832 // world, "traffic_source": "profiles/r4c_ncu_raw_c5.csv (dram read + write bytes per launch at 8192 robots)",
                          "kernel": "k_rollout<zero_order,fixed,128> (+ k_finalize, one block per robot, in ms_per_step)", "launch_ms": roll_ms, "flop_per_rollout": FLOP_PER_ROLLOUT["zero_order"],
-                         "ncu": {"source": "profiles/r4a_ncu_raw_c5.csv (one launch, not this run)", "fma_pipe_pct_of_peak": 38.9, "alu_pipe_pct": 36.2, "xu_pipe_pct": 22.7,
-                                 "issue_slots_busy_pct": 69.2, "warp_instructions_per_rollout": 8280, "active_warps_per_scheduler": 2.89}}}
+                         "ncu": {"source": "profiles/r4c_ncu_raw_c5.csv (one launch, not this run)", "fma_pipe_pct_of_peak": 39.9, "alu_pipe_pct": 41.3, "xu_pipe_pct": 23.9,
+                                 "issue_slots_busy_pct": 71.8, "warp_instructions_per_rollout": 8170, "active_warps_per_scheduler": 2.87}}}
 
 
 def run_tamols(torch, dev, local_rank, rank, world, barrier, max_over_ranks, with_cpu):
