@@ -88,6 +88,10 @@ const char *qpmpc_version(void);
 void *qpmpc_stream(qpmpc_handle *h);
 /* Number of kernels launched by this handle since creation (bench.py's gpu_launches claim). */
 int64_t qpmpc_launch_count(const qpmpc_handle *h);
+/* Which rollout kernel the most recent solve / rollout_costs call launched: "pair" (two rollouts per thread, packed
+ * FP32: zero-order fixed-gait launches of the throughput regime), "quad" (four lanes per rollout: latency regime) or
+ * "thread" (one thread per rollout).  Measurement and test hook; no reference counterpart. */
+const char *qpmpc_last_kernel(const qpmpc_handle *h);
 
 /*
  * jitted_compute_control for ONE robot with host buffers in and out:

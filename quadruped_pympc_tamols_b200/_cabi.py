@@ -67,7 +67,7 @@ class QpmpcGaitBatch(C.Structure):  # include/qpmpc.h: qpmpc_gait_batch
 
 
 EXPORTS = ["qpmpc_create", "qpmpc_destroy", "qpmpc_num_params", "qpmpc_last_error", "qpmpc_version", "qpmpc_stream",
-           "qpmpc_launch_count", "qpmpc_solve", "qpmpc_solve_iterated", "qpmpc_copy_costs", "qpmpc_solve_batched", "qpmpc_rollout_costs", "qpmpc_generate_noise", "qpmpc_set_profiling", "qpmpc_profile_last",
+           "qpmpc_launch_count", "qpmpc_last_kernel", "qpmpc_solve", "qpmpc_solve_iterated", "qpmpc_copy_costs", "qpmpc_solve_batched", "qpmpc_rollout_costs", "qpmpc_generate_noise", "qpmpc_set_profiling", "qpmpc_profile_last",
            "qpmpc_measure_fp32_peak", "qpmpc_contact_sequences", "qpmpc_gait_run",
            "qpmpc_stance_torques"]
 
@@ -102,6 +102,8 @@ def lib():
         L.qpmpc_stream.restype = vp
         L.qpmpc_launch_count.argtypes = [vp]
         L.qpmpc_launch_count.restype = C.c_int64
+        L.qpmpc_last_kernel.argtypes = [vp]
+        L.qpmpc_last_kernel.restype = C.c_char_p
         L.qpmpc_solve.argtypes = [vp, vp, vp, vp, vp, C.c_uint64, C.c_uint64, vp, C.c_float, C.c_int32, vp, vp, vp,
                                   vp, vp, vp, vp]  # host pointers passed as integers (cheapest ctypes marshalling)
         L.qpmpc_solve_iterated.argtypes = [vp, vp, vp, vp, vp, C.c_uint64, C.c_uint64, C.c_int32, vp, C.c_float, C.c_int32,
@@ -249,6 +251,11 @@ class Handle:
     @property
     def launch_count(self):
         return lib().qpmpc_launch_count(self._h)
+
+    @property
+    def last_kernel(self):
+        """"pair" | "quad" | "thread": the rollout kernel the most recent launch used."""
+        return lib().qpmpc_last_kernel(self._h).decode()
 
     def _io(self):
         """Persistent host staging of solve(): float32 arrays whose addresses are taken ONCE (ndarray.ctypes.data costs

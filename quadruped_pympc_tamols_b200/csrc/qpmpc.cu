@@ -26,7 +26,9 @@
 #include "../../include/qpmpc.h"
 #include "philox.cuh"
 #include "srbd.cuh"
+#include "noise.cuh"
 #include "rollout.cuh"
+#include "rollout_pair.cuh"
 
 namespace qp {
 
@@ -53,7 +55,7 @@ struct SolveArgs {
     int nblk;         // rollout blocks per robot
     int robot_offset; // global id of robot 0 of this launch (Philox subsequence = robot_offset + r)
     int fused;        // 1: the last rollout block of a robot runs finalize_robot itself (one launch per solve)
-    int pipe;         // 1: zero-order fixed-gait rollouts draw the noise of steps n+4.. while integrating step n
+    int chunk;        // rollouts per block of this launch
     int inline_in;    // bit 0: state / reference / contact / timing / nominal / oswing, bit 1: best, bit 2: sigma hold
                       // BYTE OFFSETS into the kernel's InlineIn parameter instead of device addresses
 };
@@ -83,198 +85,7 @@ __device__ __forceinline__ SolveArgs resolve_inputs(const SolveArgs &a_, const I
     return a;
 }
 
-// ---------------------------------------------------------------- noise ------------------------------------
-// additional_random_parameters[i, 4g..4g+3] (sigma applied) for robot `robot`:
-//   random_sampling centroidal_nmpc_jax.py:647-677 (the two Gaussian thirds share ONE key upstream, hence the
-//   same normals scaled by sigma[0] and sigma[1]; the uniform block is U(-sigma[2], sigma[2]));
-//   mppi :806-812; cem_mppi :951-958 (normals * sigma vector).  Row 0 is always zero.
-// Everything that depends only on the row i is resolved once per rollout (RowNoise), so the per-group work is the
-// Philox block and the Box-Muller transform; a scalar sigma is folded into the square root's argument.
-struct RowNoise {
-    int mode;         // 0: N(0, sigma^2) with scalar sigma; 1: U[-a, a); 2: N(0,1) * sigma_vec[p]; 3: zero row
-    uint32_t stream, sample;
-    float k;          // mode 0: sigma^2 * NEG_2LN2; mode 1: a; mode 2: NEG_2LN2
-};
-
-__device__ __forceinline__ RowNoise row_noise(const DevCfg &c, int i) {
-    RowNoise rn;
-    rn.stream = STREAM_NORMAL;
-    rn.sample = (uint32_t)(i - 1);
-    if (i == 0) {
-        rn.mode = 3;
-        rn.k = 0.f;
-    } else if (c.method == QPMPC_METHOD_RANDOM) {
-        const int third = c.N / 3;
-        if (i < 1 + 2 * third) {
-            const bool first = i < 1 + third;
-            const float s = first ? c.sig_rs[0] : c.sig_rs[1];
-            rn.mode = 0;
-            rn.sample = (uint32_t)(first ? i - 1 : i - 1 - third);
-            rn.k = __fmul_rn(__fmul_rn(s, s), NEG_2LN2);
-        } else {
-            rn.mode = 1;
-            rn.stream = STREAM_UNIFORM;
-            rn.sample = (uint32_t)(i - 1 - 2 * third);
-            rn.k = c.sig_rs[2];
-        }
-    } else if (c.method == QPMPC_METHOD_MPPI) {
-        rn.mode = 0;
-        rn.k = __fmul_rn(__fmul_rn(c.sig_mppi, c.sig_mppi), NEG_2LN2);
-    } else {
-        rn.mode = 2;
-        rn.k = NEG_2LN2;
-    }
-    return rn;
-}
-
-__device__ __forceinline__ float4 noise_group_row(const RowNoise &rn, const NoiseKey &nk, const float *sigma_vec, int g,
-                                                  uint32_t robot) {
-    if (rn.mode == 3) return make_float4(0.f, 0.f, 0.f, 0.f);
-    const uint4 x = draw(nk, rn.stream, g, rn.sample, robot);
-    if (rn.mode == 1) {
-        const float a = rn.k, w = __fmul_rn(2.0f, a);
-        return make_float4(__fmaf_rn(u01_half_open(x.x), w, -a), __fmaf_rn(u01_half_open(x.y), w, -a),
-                           __fmaf_rn(u01_half_open(x.z), w, -a), __fmaf_rn(u01_half_open(x.w), w, -a));
-    }
-    const float4 z = normal4_scaled(x, rn.k);
-    if (rn.mode == 0) return z;
-    return make_float4(__fmul_rn(z.x, sigma_vec[4 * g]), __fmul_rn(z.y, sigma_vec[4 * g + 1]),
-                       __fmul_rn(z.z, sigma_vec[4 * g + 2]), __fmul_rn(z.w, sigma_vec[4 * g + 3]));
-}
-
-// groups ga and gb of the same row under ONE control flow, so that the two Philox blocks and the two Box-Muller
-// chains interleave (same values as two noise_group_row calls)
-__device__ __forceinline__ void noise_group_row2(const RowNoise &rn, const NoiseKey &nk, const float *sigma_vec, int ga,
-                                                 int gb, uint32_t robot, float4 &ea, float4 &eb) {
-    ea = eb = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (rn.mode == 3) return;
-    const uint4 xa = draw(nk, rn.stream, ga, rn.sample, robot);
-    const uint4 xb = draw(nk, rn.stream, gb, rn.sample, robot);
-    if (rn.mode == 1) {
-        const float a = rn.k, w = __fmul_rn(2.0f, a);
-        ea = make_float4(__fmaf_rn(u01_half_open(xa.x), w, -a), __fmaf_rn(u01_half_open(xa.y), w, -a),
-                         __fmaf_rn(u01_half_open(xa.z), w, -a), __fmaf_rn(u01_half_open(xa.w), w, -a));
-        eb = make_float4(__fmaf_rn(u01_half_open(xb.x), w, -a), __fmaf_rn(u01_half_open(xb.y), w, -a),
-                         __fmaf_rn(u01_half_open(xb.z), w, -a), __fmaf_rn(u01_half_open(xb.w), w, -a));
-        return;
-    }
-    ea = normal4_scaled(xa, rn.k);
-    eb = normal4_scaled(xb, rn.k);
-    if (rn.mode == 0) return;
-    ea = make_float4(__fmul_rn(ea.x, sigma_vec[4 * ga]), __fmul_rn(ea.y, sigma_vec[4 * ga + 1]),
-                     __fmul_rn(ea.z, sigma_vec[4 * ga + 2]), __fmul_rn(ea.w, sigma_vec[4 * ga + 3]));
-    eb = make_float4(__fmul_rn(eb.x, sigma_vec[4 * gb]), __fmul_rn(eb.y, sigma_vec[4 * gb + 1]),
-                     __fmul_rn(eb.z, sigma_vec[4 * gb + 2]), __fmul_rn(eb.w, sigma_vec[4 * gb + 3]));
-}
-
-__device__ __forceinline__ float4 noise_group(const DevCfg &c, const NoiseKey &nk, const float *sigma_vec, int i,
-                                              int g, uint32_t robot) {
-    return noise_group_row(row_noise(c, i), nk, sigma_vec, g, robot);
-}
-
-// The same values as noise_group_row WITHOUT control flow, so that a caller's independent arithmetic can share a
-// basic block (and the instruction scheduler) with the Philox / Box-Muller chain.  NS = true: scalar-sigma normals
-// only (mppi; mode 0, or mode 3 for row 0); NS = false: any mode, the unused variants are computed and deselected.
-template <bool NS>
-__device__ __forceinline__ float4 noise_group_flat(const RowNoise &rn, const NoiseKey &nk, const float *sigma_vec, int g,
-                                                   uint32_t robot) {
-    const uint4 x = draw(nk, rn.stream, g, rn.sample, robot);
-    float4 e = normal4_scaled(x, rn.k);
-    if (!NS) {
-        const float a = rn.k, w = __fmul_rn(2.0f, a);
-        const bool uni = rn.mode == 1;
-        e.x = uni ? __fmaf_rn(u01_half_open(x.x), w, -a) : e.x;
-        e.y = uni ? __fmaf_rn(u01_half_open(x.y), w, -a) : e.y;
-        e.z = uni ? __fmaf_rn(u01_half_open(x.z), w, -a) : e.z;
-        e.w = uni ? __fmaf_rn(u01_half_open(x.w), w, -a) : e.w;
-        float4 sg = make_float4(1.f, 1.f, 1.f, 1.f);  // z * 1 = z exactly
-        if (rn.mode == 2) sg = *reinterpret_cast<const float4 *>(sigma_vec + 4 * g);
-        e = make_float4(__fmul_rn(e.x, sg.x), __fmul_rn(e.y, sg.y), __fmul_rn(e.z, sg.z), __fmul_rn(e.w, sg.w));
-    }
-    const bool zero = rn.mode == 3;
-    return make_float4(zero ? 0.f : e.x, zero ? 0.f : e.y, zero ? 0.f : e.z, zero ? 0.f : e.w);
-}
-
-// Zero-order, fixed-gait rollout with the noise drawn on the way (in-kernel Philox only, H a multiple of 4).
-// Parameter p = (3 leg + axis) H + n is used at step n alone and lives in Philox group p / 4, so the 12 groups
-// {j H/4 + q, j = 3 leg + axis} hold exactly the steps 4q..4q+3.  The prologue draws the groups of steps 0..3; step
-// n of the loop then draws three of the twelve groups of the NEXT four steps while it integrates: two independent
-// instruction streams (Philox integer/SFU work and the SRBD FMA chain) in one basic block, which the scheduler
-// interleaves.  With 3 warps per scheduler (shared-memory bound) the separate fill -> rollout phases left 38 % of
-// the issue slots empty behind fixed-latency dependencies (profiles/r2r_ncu_details_c5.txt).  Same groups into the
-// same shared cells as the two-phase path: costs and partials are bit-identical (QPMPC_PIPE=0 runs the other one).
-template <int STRIDE, bool NS>
-__device__ __forceinline__ float rollout_fixed_zo_pipe(const DevCfg &c, const float *s_state, const float *s_ref,
-                                                       const FixedTables &tb, float *col, const float *s_best,
-                                                       const float *s_sigma, const RowNoise &rn, const NoiseKey &key,
-                                                       uint32_t robot) {
-    const int H = c.H, HQ = H >> 2, hs = H * STRIDE;
-#pragma unroll 1
-    for (int j = 0; j < 12; j += 2) {
-        const int ga = j * HQ, gb = ga + HQ;
-        float4 ea, eb;
-        noise_group_row2(rn, key, s_sigma, ga, gb, robot, ea, eb);
-        const float4 ba = *reinterpret_cast<const float4 *>(s_best + 4 * ga);
-        const float4 bb = *reinterpret_cast<const float4 *>(s_best + 4 * gb);
-        float *da = col + 4 * ga * STRIDE, *db = col + 4 * gb * STRIDE;
-        da[0] = ba.x + ea.x; da[STRIDE] = ba.y + ea.y; da[2 * STRIDE] = ba.z + ea.z; da[3 * STRIDE] = ba.w + ea.w;
-        db[0] = bb.x + eb.x; db[STRIDE] = bb.y + eb.y; db[2 * STRIDE] = bb.z + eb.z; db[3 * STRIDE] = bb.w + eb.w;
-    }
-    Problem pb;
-    load_problem(pb, s_state, s_ref);
-    float cost = 0.f;
-    const float *pz = col;
-    int n = 0;
-#pragma unroll 1
-    for (; n < H - 4; ++n) {
-        // every shared-memory read of the iteration first: nothing below has to wait behind the stores
-        float f[4][3];
-#pragma unroll
-        for (int l = 0; l < 4; ++l) {
-            const float *p = pz + l * 3 * hs;
-            f[l][0] = p[0]; f[l][1] = p[hs]; f[l][2] = p[2 * hs];
-        }
-        const float4 st4 = *reinterpret_cast<const float4 *>(tb.st + 8 * n);
-        const float4 st34 = *reinterpret_cast<const float4 *>(tb.st + 8 * n + 4);
-        const float ref_fz = tb.reffz[n];
-        const int g0 = 3 * (n & 3) * HQ + (n >> 2) + 1;  // groups (3 (n & 3) + {0, 1, 2}) HQ + q, q = n / 4 + 1
-        const float4 b0 = *reinterpret_cast<const float4 *>(s_best + 4 * g0);
-        const float4 b1 = *reinterpret_cast<const float4 *>(s_best + 4 * (g0 + HQ));
-        const float4 b2 = *reinterpret_cast<const float4 *>(s_best + 4 * (g0 + 2 * HQ));
-        const float4 e0 = noise_group_flat<NS>(rn, key, s_sigma, g0, robot);
-        const float4 e1 = noise_group_flat<NS>(rn, key, s_sigma, g0 + HQ, robot);
-        const float4 e2 = noise_group_flat<NS>(rn, key, s_sigma, g0 + 2 * HQ, robot);
-        const float st[4] = {st4.x, st4.y, st4.z, st4.w}, st3[4] = {st34.x, st34.y, st34.z, st34.w};
-#pragma unroll
-        for (int l = 0; l < 4; ++l) shape_leg(c, f[l], st[l], st3[l], ref_fz);
-        body_step(c, pb.x, pb.feet, pb.ref, f, st, c.dts[n], cost);
-        float *d = col + 4 * g0 * STRIDE;
-        d[0] = b0.x + e0.x; d[STRIDE] = b0.y + e0.y; d[2 * STRIDE] = b0.z + e0.z; d[3 * STRIDE] = b0.w + e0.w;
-        d += 4 * HQ * STRIDE;
-        d[0] = b1.x + e1.x; d[STRIDE] = b1.y + e1.y; d[2 * STRIDE] = b1.z + e1.z; d[3 * STRIDE] = b1.w + e1.w;
-        d += 4 * HQ * STRIDE;
-        d[0] = b2.x + e2.x; d[STRIDE] = b2.y + e2.y; d[2 * STRIDE] = b2.z + e2.z; d[3 * STRIDE] = b2.w + e2.w;
-        pz += STRIDE;
-    }
-#pragma unroll 1
-    for (; n < H; ++n) {
-        const float4 st4 = *reinterpret_cast<const float4 *>(tb.st + 8 * n);
-        const float4 st34 = *reinterpret_cast<const float4 *>(tb.st + 8 * n + 4);
-        const float st[4] = {st4.x, st4.y, st4.z, st4.w}, st3[4] = {st34.x, st34.y, st34.z, st34.w};
-        const float ref_fz = tb.reffz[n];
-        float f[4][3];
-#pragma unroll
-        for (int l = 0; l < 4; ++l) {
-            const float *p = pz + l * 3 * hs;
-            f[l][0] = p[0]; f[l][1] = p[hs]; f[l][2] = p[2 * hs];
-            shape_leg(c, f[l], st[l], st3[l], ref_fz);
-        }
-        body_step(c, pb.x, pb.feet, pb.ref, f, st, c.dts[n], cost);
-        pz += STRIDE;
-    }
-    return cost;
-}
-
+// ---------------------------------------------------------------- noise: noise.cuh (blocks of 12 values) ---
 // step_frequencies_vec[i]: ..._gait_adaptive.py:687-692 (random_sampling), :834-838 (mppi), :994-999 (cem)
 __device__ __forceinline__ float freq_sample(const DevCfg &c, const NoiseKey &nk, int i, uint32_t robot,
                                              float nominal, int oswing) {
@@ -387,9 +198,15 @@ __device__ __forceinline__ void quad_leg_step(const DevCfg &c, float f[3], float
 // Finalize step of robot r, run by ALL threads of one block (any multiple of 32): either the last rollout block of
 // the robot (fused, scratch = that block's parameter columns, no longer needed) or the stand-alone k_finalize.
 // Partials and costs were written by other blocks: they are read through L2 (ld.global.cg).
-__host__ __device__ inline int finalize_smem_floats(int P, int nblk, int cem_elite, int threads) {
+constexpr int CEM_SLICES_MAX = 16;  // elite slices of the CEM spread pass (one noise block per thread and elite)
+__host__ __device__ inline int finalize_acc_rows(int P, int cem_elite, int threads) {
     const int G = threads / (P / 4) > 1 ? threads / (P / 4) : 1;
-    return G * P + P + 64 + 3 * nblk + 1 + cem_elite + (int)(sizeof(qpmpc_result) / 4) + 8;
+    int J = threads / (P / 12) < CEM_SLICES_MAX ? threads / (P / 12) : CEM_SLICES_MAX;
+    if (J < 1) J = 1;
+    return cem_elite > 0 && J > G ? J : G;
+}
+__host__ __device__ inline int finalize_smem_floats(int P, int nblk, int cem_elite, int threads) {
+    return finalize_acc_rows(P, cem_elite, threads) * P + P + 64 + 3 * nblk + 1 + cem_elite + (int)(sizeof(qpmpc_result) / 4) + 8;
 }
 
 #ifdef QPMPC_TIMING
@@ -404,7 +221,7 @@ __device__ void finalize_robot(const DevCfg &c, const FinalizeArgs &a, const int
 #endif
     QP_TICK(0);
     // scratch: acc[G][P] | best[P] | red[64] | sc[nblk] | sw[nblk] | lb[nblk + 1] | sel[cem_elite] | result record
-    const int G_ = max(1, (int)blockDim.x / (P >> 2));
+    const int G_ = finalize_acc_rows(P, c.method == QPMPC_METHOD_CEM ? c.cem_elite : 0, (int)blockDim.x);
     float *s_acc = smem;
     float *s_best = s_acc + G_ * P;
     float *s_red = s_best + P;
@@ -490,16 +307,20 @@ __device__ void finalize_robot(const DevCfg &c, const FinalizeArgs &a, const int
     QP_TICK(1);
 
     if (c.method == QPMPC_METHOD_RANDOM) {  // best = control_parameters_vec[best_index], :692
-        for (int p = t; p < P; p += blockDim.x) {
-            float e;
-            if (a.eps) {
-                e = a.eps[((size_t)r * N + bi) * P + p];
-            } else {
-                const float4 v = noise_group(c, a.key, nullptr, bi, p >> 2, robot);
-                const int k = p & 3;
-                e = k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w));
+        if (a.eps) {
+            for (int p = t; p < P; p += blockDim.x)
+                s_best[p] = __fadd_rn(a.best[(size_t)r * P + p], a.eps[((size_t)r * N + bi) * P + p]);
+        } else {  // the winner's row is drawn again, one noise block per thread
+            const RowNoise rn = row_noise(c, bi);
+            for (int b = t; b < P / NOISE_BLOCK; b += blockDim.x) {
+                float e[NOISE_BLOCK];
+                noise_block(rn, a.key, b, robot, e, [](int) { return 1.0f; });
+#pragma unroll
+                for (int k = 0; k < NOISE_BLOCK; ++k) {
+                    const int p = param_of(c, b, k);
+                    s_best[p] = __fadd_rn(a.best[(size_t)r * P + p], e[k]);
+                }
             }
-            s_best[p] = __fadd_rn(a.best[(size_t)r * P + p], e);
         }
     } else {
         const float den = s_hdr[2];
@@ -643,31 +464,55 @@ __device__ void finalize_robot(const DevCfg &c, const FinalizeArgs &a, const int
         li = mi;
     }
     __syncthreads();
-    for (int p = t; p < P; p += blockDim.x) {
-        float mean = 0.f;
+    // Per-parameter mean and spread of the elites' noise rows, two passes (jnp.cov: mean, then centred squares).  The
+    // rows are drawn again: thread (j, b) owns noise block b of the elites k = j, j + J, ...; the J slice sums are then
+    // added in slice order.  s_acc: [J][P] (order-index layout), s_best is free by now and keeps the means.
+    {
+        const int B = P / NOISE_BLOCK;
+        const int J = max(1, min((int)blockDim.x / B, (int)CEM_SLICES_MAX));
+        const float *sig = a.sigma + (size_t)r * P;
+        float *s_mean = s_best;
         for (int pass = 0; pass < 2; ++pass) {
-            float acc = 0.f;
-            for (int k = 0; k < K; ++k) {
-                const int i = s_sel[k];
-                float e;
-                if (a.eps) {
-                    e = a.eps[((size_t)r * N + i) * P + p];
-                } else {
-                    const float4 v = noise_group(c, a.key, a.sigma + (size_t)r * P, i, p >> 2, robot);
-                    const int kk = p & 3;
-                    e = kk == 0 ? v.x : (kk == 1 ? v.y : (kk == 2 ? v.z : v.w));
+            for (int q = t; q < J * B; q += blockDim.x) {
+                const int j = q / B, b = q - j * B;
+                float acc[NOISE_BLOCK];
+#pragma unroll
+                for (int k = 0; k < NOISE_BLOCK; ++k) acc[k] = 0.f;
+                for (int k0 = j; k0 < K; k0 += J) {
+                    const int i = s_sel[k0];
+                    float e[NOISE_BLOCK];
+                    if (a.eps) {
+#pragma unroll
+                        for (int k = 0; k < NOISE_BLOCK; ++k) e[k] = a.eps[((size_t)r * N + i) * P + param_of(c, b, k)];
+                    } else {
+                        noise_block(row_noise(c, i), a.key, b, robot, e, [&](int k) { return sig[param_of(c, b, k)]; });
+                    }
+#pragma unroll
+                    for (int k = 0; k < NOISE_BLOCK; ++k) {
+                        const float d = e[k] - (pass == 0 ? 0.f : s_mean[param_of(c, b, k)]);
+                        acc[k] += pass == 0 ? d : d * d;
+                    }
                 }
-                acc += pass == 0 ? e : (e - mean) * (e - mean);
+#pragma unroll
+                for (int k = 0; k < NOISE_BLOCK; ++k) s_acc[j * P + b * NOISE_BLOCK + k] = acc[k];
             }
-            if (pass == 0) mean = acc / (float)K;
-            else {
-                float v = acc / (float)(K - 1) + 1e-8f;
-                if (c.cem_sqrt) v = sqrtf(v);
-                v = v > c.cem_hi ? c.cem_hi : v;
-                v = v < c.cem_lo ? c.cem_lo : v;
-                if (ll) ll_store(RW + P + p, v);
-                else a.sigma_out[(size_t)r * P + p] = v;
+            __syncthreads();
+            for (int o = t; o < P; o += blockDim.x) {
+                float sum = 0.f;
+                for (int j = 0; j < J; ++j) sum += s_acc[j * P + o];
+                const int p = param_of(c, o / NOISE_BLOCK, o % NOISE_BLOCK);
+                if (pass == 0) {
+                    s_mean[p] = sum / (float)K;
+                } else {
+                    float v = sum / (float)(K - 1) + 1e-8f;
+                    if (c.cem_sqrt) v = sqrtf(v);
+                    v = v > c.cem_hi ? c.cem_hi : v;
+                    v = v < c.cem_lo ? c.cem_lo : v;
+                    if (ll) ll_store(RW + P + p, v);
+                    else a.sigma_out[(size_t)r * P + p] = v;
+                }
             }
+            __syncthreads();
         }
     }
     }
@@ -697,7 +542,7 @@ __device__ __forceinline__ bool last_block_of_robot(unsigned int *ticket, int nb
 // ---------------------------------------------------------------- rollout kernel (throughput regime) -------
 // Shared memory layout (floats):
 //   w[T] | live[T] (u16) | par[P][T+1] | best[P] | sigma[P] (cem only) | state[24] | ref[12] | timing[4] | st[8H] |
-//   ref_fz[H] | basis[4H] | index[H] (int) | mgk[8] | red[64]
+//   basis[4H] | ref_fz[H] | index[H] (int) | mgk[8] | red[64]
 // par[p][t] = best[p] + eps[t][p] is the parameter vector of thread t's rollout, one COLUMN per thread: the rollout's
 // own reads are conflict-free, and with the row stride T+1 so are the row-wise reads of the softmin-weighted sum.
 // (sigma only exists for cem_mppi: at P = 144, T = 128 leaving it out is what lets three blocks share an SM.)
@@ -827,10 +672,10 @@ __global__ void __launch_bounds__(T, T == 128 ? 3 : T == 64 ? 6 : 1) k_rollout(c
     float *s_ref = s_state + 24;
     float *s_timing = s_ref + 12;
     float *s_st = s_timing + 4;
-    float *s_reffz = s_st + 8 * H;
-    float *s_basis = s_reffz + H;
-    int *s_index = reinterpret_cast<int *>(s_basis + 4 * H);
-    float *s_mgk = s_basis + 5 * H;
+    float *s_basis = s_st + 8 * H;  // float4 tables first: 16-byte aligned for every horizon
+    float *s_reffz = s_basis + 4 * H;
+    int *s_index = reinterpret_cast<int *>(s_reffz + H);
+    float *s_mgk = s_reffz + 2 * H;
     float *s_red = s_mgk + 8;
 
     const int r = blockIdx.y;
@@ -882,12 +727,7 @@ __global__ void __launch_bounds__(T, T == 128 ? 3 : T == 64 ? 6 : 1) k_rollout(c
 
     // ---- this thread's parameter vector -> shared column t
     const uint32_t robot = (uint32_t)(r + a.robot_offset);
-    // zero-order fixed-gait launches with in-kernel noise draw it while they integrate (rollout_fixed_zo_pipe)
-    const bool pipe = PARAM == QPMPC_PARAM_ZERO_ORDER && !GA && a.pipe && !a.eps && !a.costs_only && H >= 4 && (H & 3) == 0;
-    if (pipe) {
-        if (!valid)
-            for (int p = 0; p < P; ++p) s_par[p * STRIDE + t] = 0.f;
-    } else if (a.eps) {
+    if (a.eps) {
         const float *src = a.eps + ((size_t)r * a.n + (size_t)blockIdx.x * T) * P;
         const int rows = min(T, a.n - blockIdx.x * T);
         for (int e = t; e < T * P; e += T) {
@@ -896,36 +736,19 @@ __global__ void __launch_bounds__(T, T == 128 ? 3 : T == 64 ? 6 : 1) k_rollout(c
         }
         __syncthreads();
     } else {
-        const RowNoise rn = row_noise(c, valid ? i : 0);
         float *dst = s_par + t;
-        const int G4 = P / 4;
         if (!valid) {  // tail block: zero columns keep everything finite
             for (int p = 0; p < P; ++p) dst[p * STRIDE] = 0.f;
         } else {
-            // two groups per trip under one control flow: the two Philox blocks and Box-Muller chains interleave
-            int g = 0;
-            for (; g + 1 < G4; g += 2) {
-                float4 e, e2;
-                noise_group_row2(rn, a.key, s_sigma, g, g + 1, robot, e, e2);
-                const float4 b = *reinterpret_cast<const float4 *>(s_best + 4 * g);
-                const float4 b2 = *reinterpret_cast<const float4 *>(s_best + 4 * g + 4);
-                dst[0] = b.x + e.x;
-                dst[STRIDE] = b.y + e.y;
-                dst[2 * STRIDE] = b.z + e.z;
-                dst[3 * STRIDE] = b.w + e.w;
-                dst[4 * STRIDE] = b2.x + e2.x;
-                dst[5 * STRIDE] = b2.y + e2.y;
-                dst[6 * STRIDE] = b2.z + e2.z;
-                dst[7 * STRIDE] = b2.w + e2.w;
-                dst += 8 * STRIDE;
-            }
-            if (g < G4) {
-                const float4 e = noise_group_row(rn, a.key, s_sigma, g, robot);
-                const float4 b = *reinterpret_cast<const float4 *>(s_best + 4 * g);
-                dst[0] = b.x + e.x;
-                dst[STRIDE] = b.y + e.y;
-                dst[2 * STRIDE] = b.z + e.z;
-                dst[3 * STRIDE] = b.w + e.w;
+            const RowNoise rn = row_noise(c, i);
+            for (int b = 0; b < P / NOISE_BLOCK; ++b) {
+                float e[NOISE_BLOCK];
+                noise_block(rn, a.key, b, robot, e, [&](int k) { return s_sigma[param_of(c, b, k)]; });
+#pragma unroll
+                for (int k = 0; k < NOISE_BLOCK; ++k) {
+                    const int p = param_of(c, b, k);
+                    dst[p * STRIDE] = s_best[p] + e[k];
+                }
             }
         }
     }
@@ -940,14 +763,7 @@ __global__ void __launch_bounds__(T, T == 128 ? 3 : T == 64 ? 6 : 1) k_rollout(c
             cost = rollout_gait_adaptive<PARAM, STRIDE>(c, s_state, s_ref, s_mgk, s_timing, freq, col);
         } else {
             const FixedTables tb = {s_st, s_reffz, s_basis, s_index};
-            if (PARAM == QPMPC_PARAM_ZERO_ORDER && pipe) {
-                const RowNoise rn = row_noise(c, i);
-                cost = c.method == QPMPC_METHOD_MPPI
-                           ? rollout_fixed_zo_pipe<STRIDE, true>(c, s_state, s_ref, tb, s_par + t, s_best, s_sigma, rn, a.key, robot)
-                           : rollout_fixed_zo_pipe<STRIDE, false>(c, s_state, s_ref, tb, s_par + t, s_best, s_sigma, rn, a.key, robot);
-            } else {
-                cost = rollout_fixed<PARAM, STRIDE>(c, s_state, s_ref, tb, col);
-            }
+            cost = rollout_fixed<PARAM, STRIDE>(c, s_state, s_ref, tb, col);
         }
         if (!a.costs_only) {  // centroidal_nmpc_jax.py:686-687
             cost = isnan(cost) ? 1000000.0f : cost;
@@ -962,6 +778,239 @@ __global__ void __launch_bounds__(T, T == 128 ? 3 : T == 64 ? 6 : 1) k_rollout(c
     static_assert(T <= 256, "rollout_block_partials keeps one s_red slot per warp in slices of 8");
     rollout_block_partials<STRIDE>(c, s_par, s_w, s_live, s_red, cost, valid, i, P, part);
     if (a.fused && last_block_of_robot(a.tickets + r, a.nblk)) finalize_robot(c, resolve_inputs(a_, in), r, s_par);
+}
+
+// ---------------------------------------------------------------- pair rollout kernel (throughput regime) --
+// Zero-order parametrisation, fixed gait: TWO rollouts per thread in packed FP32 (rollout_pair.cuh), and NO parameter
+// matrix anywhere.  The twelve forces of horizon step n are noise block n of the rollout's row (noise.cuh): the thread
+// draws them in the same basic block in which it integrates the step, uses them and forgets them.  A block owns
+// `chunk` = 2 T passes rollouts of one robot (all N of them when robots alone fill the machine: one block per robot,
+// the robot's problem staged once, no ticket) and keeps their costs in shared memory.  The softmin-weighted parameter
+// sum of the update, sum_i w_i (best + eps_i), visits the LIVE samples only -- at temperature 1 with costs of
+// 1e3..1e5 all but a handful of weights underflow to exactly 0 -- and draws their rows again from the counter
+// (thread (s, b) = noise block b of the live samples s, s + S, ...; slice sums added in slice order: deterministic).
+// Compared with k_rollout<zero_order>: no 74 KB of parameter columns per 128 rollouts (occupancy no longer bound by
+// shared memory), no 144 shared-memory stores and loads per rollout, half the issue slots for the FP32 work.
+// Shared memory (floats): best_t[H][12] | sigma_t[H][12] (cem) | state[24] | ref[12] | st[H][8] | ref_fz[H] (padded to
+//   4) | cost[chunk] | w[chunk] | live[chunk] (u16) | red[64] | acc[S][P]; the fused finalize overlays cost.. onwards.
+// MODE 0: in-kernel noise, scalar-sigma normals (mppi); 1: in-kernel noise, any method; 2: rows supplied in global
+// memory (reference noise for the equivalence tests, or the parameter matrix of jit_vectorized_rollout).
+constexpr int PAIR_T = 128;
+__host__ __device__ inline int pair_fixed_floats(int P, int H, bool cem) {
+    return (cem ? 2 : 1) * P + 24 + 12 + 8 * H + ((H + 3) & ~3);
+}
+__host__ __device__ inline int pair_smem_floats(int P, int H, int chunk, int T, bool cem) {
+    const int S = T / (P / NOISE_BLOCK) > 1 ? T / (P / NOISE_BLOCK) : 1;
+    return pair_fixed_floats(P, H, cem) + chunk + chunk + chunk / 2 + 64 + S * P;
+}
+
+template <int MODE, int T>
+__global__ void __launch_bounds__(T, 3) k_rollout_pair(const __grid_constant__ DevCfg c, const RolloutArgs a_,
+                                                       const __grid_constant__ InlineIn in) {
+    const RolloutArgs a = resolve_inputs(a_, in);
+    extern __shared__ __align__(16) float smem[];
+    const int P = c.P, H = c.H, t = threadIdx.x;
+    const bool cem = c.method == QPMPC_METHOD_CEM;
+    float *s_bt = smem;
+    float *s_sg = s_bt + P;
+    float *s_state = s_sg + (cem ? P : 0);
+    float *s_ref = s_state + 24;
+    float *s_st = s_ref + 12;
+    float *s_reffz = s_st + 8 * H;
+    float *s_cost = s_reffz + ((H + 3) & ~3);
+    const int chunk = a.chunk;
+    float *s_w = s_cost + chunk;
+    unsigned short *s_live = reinterpret_cast<unsigned short *>(s_w + chunk);
+    float *s_red = s_w + chunk + chunk / 2;
+    float *s_acc = s_red + 64;
+
+    const int r = blockIdx.y;
+    const int base = blockIdx.x * chunk;
+    const int cn = min(chunk, a.n - base);  // rollouts of this block
+    const uint32_t robot = (uint32_t)(r + a.robot_offset);
+
+    // ---- stage the robot's problem: best / sigma transposed to step-major order (value k of step n at [12 n + k]),
+    // state, reference, contact tables.  All global loads of a thread are issued before its first store.
+    {
+        const int role = t >> 5, tl = t & 31;
+        const bool j_state = role == 1 && tl < 24, j_ref = role == 2 && tl < 12, j_tab = role == 3 && tl < H;
+        const float *cs = a.contact + (size_t)r * 4 * H;
+        float stv = 0.f, rfv = 0.f, s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        if (j_state) stv = a.state[r * 24 + tl];
+        if (j_ref) rfv = a.reference[r * 24 + tl];
+        if (j_tab) { s0 = cs[tl]; s1 = cs[H + tl]; s2 = cs[2 * H + tl]; s3 = cs[3 * H + tl]; }
+        for (int p = t; p < P; p += T) {
+            const int k = p / H, n = p - k * H;
+            s_bt[NOISE_BLOCK * n + k] = a.costs_only ? 0.f : a.best[(size_t)r * P + p];
+            if (cem) s_sg[NOISE_BLOCK * n + k] = a.sigma ? a.sigma[(size_t)r * P + p] : 0.f;
+        }
+        if (j_state) s_state[tl] = stv;
+        if (j_ref) s_ref[tl] = rfv;
+        if (j_tab) {
+            const int n = tl;
+            s_reffz[n] = c.mg / (((s0 + s1) + s2) + s3);
+            s_st[8 * n + 0] = s0; s_st[8 * n + 1] = s1; s_st[8 * n + 2] = s2; s_st[8 * n + 3] = s3;
+            s_st[8 * n + 4] = s0 * (1.0f / 3.0f); s_st[8 * n + 5] = s1 * (1.0f / 3.0f);
+            s_st[8 * n + 6] = s2 * (1.0f / 3.0f); s_st[8 * n + 7] = s3 * (1.0f / 3.0f);
+        }
+    }
+    __syncthreads();
+
+    float feet[12], ref[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) {
+        feet[k] = s_state[12 + k];
+        ref[k] = s_ref[k];
+    }
+
+    // ---- rollouts: pass q integrates rollouts base + 2 T q + t (A) and base + 2 T q + T + t (B)
+    for (int q0 = 0; q0 < cn; q0 += 2 * T) {
+        const int ja = q0 + t, jb = q0 + T + t;
+        const bool va = ja < cn, vb = jb < cn;
+        const int ia = base + ja, ib = base + jb;
+        v2 x[12];
+#pragma unroll
+        for (int k = 0; k < 12; ++k) x[k] = f2(s_state[k]);
+        v2 cost = f2(0.f);
+        const RowNoise rna = row_noise(c, va ? ia : 0), rnb = row_noise(c, vb ? ib : 0);
+        const float *ea = nullptr, *eb = nullptr;
+        if (MODE == 2) {
+            ea = a.eps + ((size_t)r * a.n + (va ? ia : base)) * P;
+            eb = a.eps + ((size_t)r * a.n + (vb ? ib : base)) * P;
+        }
+#pragma unroll 1
+        for (int n = 0; n < H; ++n) {
+            v2 f[NOISE_BLOCK];
+            const float4 b0 = *reinterpret_cast<const float4 *>(s_bt + NOISE_BLOCK * n);
+            const float4 b1 = *reinterpret_cast<const float4 *>(s_bt + NOISE_BLOCK * n + 4);
+            const float4 b2 = *reinterpret_cast<const float4 *>(s_bt + NOISE_BLOCK * n + 8);
+            const float bst[NOISE_BLOCK] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w};
+            if (MODE == 2) {
+#pragma unroll
+                for (int k = 0; k < NOISE_BLOCK; ++k) f[k] = vadd(f2(ea[k * H + n], eb[k * H + n]), bst[k]);
+            } else {
+                noise_block_pair<MODE == 0>(rna, rnb, a.key, n, robot, bst, f, [&](int k) { return s_sg[NOISE_BLOCK * n + k]; });
+            }
+            const float4 st4 = *reinterpret_cast<const float4 *>(s_st + 8 * n);
+            const float4 st34 = *reinterpret_cast<const float4 *>(s_st + 8 * n + 4);
+            const float st[4] = {st4.x, st4.y, st4.z, st4.w}, st3[4] = {st34.x, st34.y, st34.z, st34.w};
+            pair_step(c, x, feet, ref, f, st, st3, s_reffz[n], c.dts[n], cost);
+        }
+        if (!a.costs_only) {  // centroidal_nmpc_jax.py:686-687
+            cost.x = isnan(cost.x) ? 1000000.0f : cost.x;
+            cost.x = isinf(cost.x) ? 1000000.0f : cost.x;
+            cost.y = isnan(cost.y) ? 1000000.0f : cost.y;
+            cost.y = isinf(cost.y) ? 1000000.0f : cost.y;
+        }
+        if (va) {
+            a.costs[(size_t)r * a.n + ia] = cost.x;
+            s_cost[ja] = cost.x;
+        }
+        if (vb) {
+            a.costs[(size_t)r * a.n + ib] = cost.y;
+            s_cost[jb] = cost.y;
+        }
+    }
+    if (a.costs_only) return;
+    __syncthreads();
+
+    // ---- block partials {min, sum w, min, argmin} + V[P]
+    float *part = a.partials + ((size_t)r * a.nblk + blockIdx.x) * (PART_HDR + P);
+    float bc = INFINITY;
+    int bi = 0x7fffffff;
+    for (int j = t; j < cn; j += T) argmin_combine(bc, bi, s_cost[j], base + j);
+    block_argmin(bc, bi, s_red);
+    if (c.method == QPMPC_METHOD_RANDOM) {
+        if (t == 0) {
+            part[0] = bc;
+            part[1] = 0.f;
+            part[2] = bc;
+            part[3] = __int_as_float(bi);
+        }
+    } else {
+        // softmin numerators relative to the block minimum (merged exactly by finalize_robot), :828-836.  Thread t owns
+        // the contiguous costs [E t, E t + E): live samples are compacted in ascending order with one block scan.
+        const int E = (chunk + T - 1) / T, j0 = E * t, j1 = min(j0 + E, cn);
+        const int lane = t & 31, wid = t >> 5;
+        float sw = 0.f;
+        int cnt = 0;
+        for (int j = j0; j < j1; ++j) {
+            const float w = __expf(-(s_cost[j] - bc));
+            sw += w;
+            cnt += w > 0.f ? 1 : 0;
+        }
+        int incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sw += __shfl_xor_sync(0xffffffffu, sw, o);
+        __syncthreads();  // s_red free again
+        if (lane == 31) s_red[wid] = __int_as_float(incl);
+        if (lane == 0) s_red[32 + wid] = sw;
+        __syncthreads();
+        int off = incl - cnt, nlive = 0;
+        float swb = 0.f;
+        for (int k = 0; k < T / 32; ++k) {
+            const int wc = __float_as_int(s_red[k]);
+            off += k < wid ? wc : 0;
+            nlive += wc;
+            swb += s_red[32 + k];
+        }
+        for (int j = j0; j < j1; ++j) {
+            const float w = __expf(-(s_cost[j] - bc));
+            if (w > 0.f) {
+                s_live[off] = (unsigned short)j;
+                s_w[off] = w;
+                ++off;
+            }
+        }
+        if (t == 0) {
+            part[0] = bc;
+            part[1] = swb;
+            part[2] = bc;
+            part[3] = __int_as_float(bi);
+        }
+        __syncthreads();
+        const int B = P / NOISE_BLOCK, S = max(1, T / B);
+        for (int u = t; u < S * B; u += T) {
+            const int sl = u / B, b = u - sl * B;
+            float acc[NOISE_BLOCK];
+#pragma unroll
+            for (int k = 0; k < NOISE_BLOCK; ++k) acc[k] = 0.f;
+            for (int l = sl; l < nlive; l += S) {
+                const int i = base + s_live[l];
+                const float w = s_w[l];
+                float e[NOISE_BLOCK];
+                if (MODE == 2) {
+                    const float *src = a.eps + ((size_t)r * a.n + i) * P;
+#pragma unroll
+                    for (int k = 0; k < NOISE_BLOCK; ++k) e[k] = src[k * H + b];
+                } else {
+                    noise_block(row_noise(c, i), a.key, b, robot, e, [&](int k) { return s_sg[NOISE_BLOCK * b + k]; });
+                }
+#pragma unroll
+                for (int k = 0; k < NOISE_BLOCK; ++k) acc[k] = fmaf(w, __fadd_rn(e[k], s_bt[NOISE_BLOCK * b + k]), acc[k]);
+            }
+#pragma unroll
+            for (int k = 0; k < NOISE_BLOCK; ++k) s_acc[sl * P + NOISE_BLOCK * b + k] = acc[k];
+        }
+        __syncthreads();
+        for (int o = t; o < P; o += T) {
+            float v = 0.f;
+            for (int sl = 0; sl < S; ++sl) v += s_acc[sl * P + o];
+            part[PART_HDR + param_of(c, o / NOISE_BLOCK, o % NOISE_BLOCK)] = v;
+        }
+    }
+    if (!a.fused) return;
+    if (a.nblk > 1) {
+        if (!last_block_of_robot(a.tickets + r, a.nblk)) return;
+    } else {
+        __syncthreads();  // the block's own partial, written above, is read back through L2 by finalize_robot
+    }
+    finalize_robot(c, resolve_inputs(a_, in), r, s_cost);
 }
 
 // ---------------------------------------------------------------- quad rollout kernel (latency regime) ------
@@ -1048,30 +1097,20 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
         }
         __syncthreads();
     } else {
+        // lane `leg` of the quad draws noise blocks leg, leg + 4, ... of the rollout's row
         const RowNoise rn = row_noise(c, valid ? i : 0);
-        // two groups per trip: their Philox rounds and Box-Muller SFU chains are independent and interleave
-        const int G4 = P / 4;
-        for (int g = leg; g < G4; g += 8) {
-            const int g2 = g + 4;
-            const bool two = g2 < G4;
-            float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
-            float4 e2 = e, b = e, b2 = e;
+        for (int b = leg; b < P / NOISE_BLOCK; b += 4) {
+            float e[NOISE_BLOCK];
             if (valid) {
-                noise_group_row2(rn, a.key, s_sigma, g, two ? g2 : g, robot, e, e2);
-                b = *reinterpret_cast<const float4 *>(s_best + 4 * g);
-                b2 = *reinterpret_cast<const float4 *>(s_best + 4 * (two ? g2 : g));
+                noise_block(rn, a.key, b, robot, e, [&](int k) { return s_sigma[param_of(c, b, k)]; });
+            } else {
+#pragma unroll
+                for (int k = 0; k < NOISE_BLOCK; ++k) e[k] = 0.f;
             }
-            float *dst = s_par + (4 * g) * stride + rb;
-            dst[0] = b.x + e.x;
-            dst[stride] = b.y + e.y;
-            dst[2 * stride] = b.z + e.z;
-            dst[3 * stride] = b.w + e.w;
-            if (two) {
-                dst += 16 * stride;
-                dst[0] = b2.x + e2.x;
-                dst[stride] = b2.y + e2.y;
-                dst[2 * stride] = b2.z + e2.z;
-                dst[3 * stride] = b2.w + e2.w;
+#pragma unroll
+            for (int k = 0; k < NOISE_BLOCK; ++k) {
+                const int p = param_of(c, b, k);
+                s_par[p * stride + rb] = valid ? s_best[p] + e[k] : 0.f;
             }
         }
         __syncwarp();
@@ -1246,14 +1285,36 @@ __global__ void __launch_bounds__(4 * QB) k_rollout_quad(const __grid_constant__
 // ---------------------------------------------------------------- noise dump -------------------------------
 __global__ void k_dump_noise(const __grid_constant__ DevCfg c, NoiseKey key, uint32_t robot, const float *sigma,
                              float nominal, int oswing, float *eps_out, float *freqs_out) {
-    const int G = c.P / 4;
+    const int B = c.P / NOISE_BLOCK;
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx < (long long)c.N * G) {
-        const int i = (int)(idx / G), g = (int)(idx % G);
-        const float4 e = noise_group(c, key, sigma, i, g, robot);
-        reinterpret_cast<float4 *>(eps_out)[idx] = e;
+    if (idx < (long long)c.N * B) {
+        const int i = (int)(idx / B), b = (int)(idx % B);
+        float e[NOISE_BLOCK];
+        noise_block(row_noise(c, i), key, b, robot, e, [&](int k) { return sigma[param_of(c, b, k)]; });
+#pragma unroll
+        for (int k = 0; k < NOISE_BLOCK; ++k) eps_out[(size_t)i * c.P + param_of(c, b, k)] = e[k];
     }
     if (freqs_out && c.ga && idx < c.N) freqs_out[idx] = freq_sample(c, key, (int)idx, robot, nominal, oswing);
+}
+
+// The same dump through the PACKED generator of k_rollout_pair (rows i and i + half of a thread as its halves A and
+// B): the test hook behind "the two generators are bit-identical" (QPMPC_DUMP=pair, tests/test_sampling_parity_gpu.py).
+__global__ void k_dump_noise_pair(const __grid_constant__ DevCfg c, NoiseKey key, uint32_t robot, const float *sigma,
+                                  float *eps_out) {
+    const int B = c.P / NOISE_BLOCK, half = (c.N + 1) / 2;
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)half * B) return;
+    const int ia = (int)(idx / B), b = (int)(idx % B), ib = ia + half;
+    const bool vb = ib < c.N;
+    v2 e[NOISE_BLOCK];
+    auto sig = [&](int k) { return sigma ? sigma[param_of(c, b, k)] : 1.0f; };
+    if (c.method == QPMPC_METHOD_MPPI) noise_block_pair_eps<true>(row_noise(c, ia), row_noise(c, vb ? ib : 0), key, b, robot, e, sig);
+    else noise_block_pair_eps<false>(row_noise(c, ia), row_noise(c, vb ? ib : 0), key, b, robot, e, sig);
+#pragma unroll
+    for (int k = 0; k < NOISE_BLOCK; ++k) {
+        eps_out[(size_t)ia * c.P + param_of(c, b, k)] = e[k].x;
+        if (vb) eps_out[(size_t)ib * c.P + param_of(c, b, k)] = e[k].y;
+    }
 }
 
 // ---------------------------------------------------------------- gait clock --------------
@@ -1317,25 +1378,27 @@ typedef void (*rollout_fn)(const qp::DevCfg, const qp::RolloutArgs, const qp::In
 
 // Experiment switches, read from the environment ONCE per handle (qpmpc_create): five getenv calls per solve were
 // measurable on a 30 us call.  QPMPC_KERNEL=quad|thread, QPMPC_QB=32|72|128, QPMPC_FUSED=0, QPMPC_ZEROCOPY=0|1,
-// QPMPC_INPUTS=copy|mapped, QPMPC_PIPE=0.
+// QPMPC_INPUTS=copy|mapped, QPMPC_PAIR=0.
 struct EnvSwitches {
     int kernel;    // 0 auto, 1 quad, 2 thread
     int qb;        // 0 auto, else 32 / 72 / 128
     int fused;     // -1 auto (fused unless the launch is many waves deep), 0: stand-alone k_finalize, 1: fused
     int zerocopy;  // -1 unset, 0 classic copies, 1 inputs mapped too
     int inputs;    // 0 auto (parameter block), 1 copy, 2 mapped
-    int pipe;      // 0: noise fill and rollout as two separate phases (QPMPC_PIPE=0)
     int threads;   // 0 auto (128 rollouts per block of the thread-per-rollout kernel), 64 (QPMPC_T=64)
+    int pair;      // 0: QPMPC_PAIR=0 keeps the thread-per-rollout kernel where the packed pair kernel would run
+    int dump_pair; // 1: QPMPC_DUMP=pair makes qpmpc_generate_noise use the packed generator (test hook)
 };
 static EnvSwitches read_env() {
-    EnvSwitches e = {0, 0, -1, -1, 0, 1, 0};
+    EnvSwitches e = {0, 0, -1, -1, 0, 0, 1, 0};
     if (const char *k = getenv("QPMPC_KERNEL")) e.kernel = !strcmp(k, "quad") ? 1 : !strcmp(k, "thread") ? 2 : 0;
     if (const char *q = getenv("QPMPC_QB")) e.qb = atoi(q) == 128 ? 128 : atoi(q) == 72 ? 72 : 32;
     if (const char *f = getenv("QPMPC_FUSED")) e.fused = f[0] == '0' ? 0 : 1;
     if (const char *z = getenv("QPMPC_ZEROCOPY")) e.zerocopy = z[0] == '0' ? 0 : z[0] == '1' ? 1 : -1;
     if (const char *i = getenv("QPMPC_INPUTS")) e.inputs = !strcmp(i, "copy") ? 1 : !strcmp(i, "mapped") ? 2 : 0;
-    if (const char *q = getenv("QPMPC_PIPE")) e.pipe = q[0] == '0' ? 0 : 1;
     if (const char *q = getenv("QPMPC_T")) e.threads = atoi(q) == 64 ? 64 : 0;
+    if (const char *q = getenv("QPMPC_PAIR")) e.pair = q[0] == '0' ? 0 : 1;
+    if (const char *q = getenv("QPMPC_DUMP")) e.dump_pair = !strcmp(q, "pair") ? 1 : 0;
     return e;
 }
 
@@ -1345,7 +1408,7 @@ struct qpmpc_handle {
     int device;
     cudaStream_t stream;
     int num_sms;
-    rollout_fn fn128, fn64, fn32, fn_quad32, fn_quad72, fn_quad128;
+    rollout_fn fn128, fn64, fn32, fn_quad32, fn_quad72, fn_quad128, fn_pair[3];
     EnvSwitches env;
     size_t max_smem;
     // single-robot staging: one pinned input block, one pinned output block
@@ -1360,6 +1423,7 @@ struct qpmpc_handle {
     unsigned int *d_tickets;  // [max_robots], zero between launches
     size_t partial_floats;
     int64_t launches;
+    const char *last_kernel;       // rollout kernel of the most recent launch: "pair", "quad" or "thread"
     int profiling;                  // qpmpc_set_profiling: record events around each kernel of a solve
     cudaEvent_t ev[3];
 };
@@ -1411,7 +1475,9 @@ static rollout_fn pick_quad(int param, int ga) {
 }
 struct LaunchPlan {
     bool quad;    // k_rollout_quad (4 lanes per rollout) instead of k_rollout (1 thread per rollout)
+    bool pair;    // k_rollout_pair (2 rollouts per thread, packed FP32; zero-order fixed gait, throughput regime)
     int T, nblk;  // threads per block, blocks per robot
+    int chunk;    // rollouts per block
     size_t smem;
 };
 // Latency regime (fewer than two rollouts-as-threads warps per SM sub-partition, e.g. one robot x 10,000 rollouts):
@@ -1420,6 +1486,7 @@ static LaunchPlan plan_launch(const qpmpc_handle *h, int n, long long total_roll
     const DevCfg &d = h->dc;
     const long long subparts = (long long)h->num_sms * 4;
     LaunchPlan pl;
+    pl.pair = false;
     pl.quad = total_rollouts < subparts * 32 * 2;
     if (h->env.kernel == 1) pl.quad = true;   // QPMPC_KERNEL pins the choice (the tests run both kernels at every size)
     if (h->env.kernel == 2) pl.quad = false;
@@ -1430,21 +1497,42 @@ static LaunchPlan plan_launch(const qpmpc_handle *h, int n, long long total_roll
     if (pl.quad && QB == 72 && (size_t)quad_smem_floats(d.P, d.H, 72) * 4 > h->max_smem) QB = 32;
     if (pl.quad && QB == 128 && (size_t)quad_smem_floats(d.P, d.H, 128) * 4 > h->max_smem) QB = 32;
     if (pl.quad && (size_t)quad_smem_floats(d.P, d.H, QB) * 4 > h->max_smem) pl.quad = false;
+    const bool cem = d.method == QPMPC_METHOD_CEM;
     if (pl.quad) {
         pl.T = 4 * QB;
         pl.nblk = (n + QB - 1) / QB;
+        pl.chunk = QB;
         pl.smem = (size_t)quad_smem_floats(d.P, d.H, QB) * 4;
+    } else if (d.param == QPMPC_PARAM_ZERO_ORDER && !d.ga && h->env.pair != 0) {
+        // one block per robot (all passes in one block: the problem is staged once, no ticket) as long as the robots
+        // alone give every SM its three blocks; fewer passes per block, more blocks per robot, otherwise
+        const long long R = total_rollouts / (n > 0 ? n : 1);
+        const int per_pass = 2 * PAIR_T;
+        int passes = (n + per_pass - 1) / per_pass;
+        auto blocks_of = [&](int ps) { return (n + per_pass * ps - 1) / (per_pass * ps); };
+        while (passes > 1 && (R * blocks_of(passes) < 3LL * h->num_sms || per_pass * passes > 32768 ||
+                              (size_t)pair_smem_floats(d.P, d.H, per_pass * passes, PAIR_T, cem) * 4 > h->max_smem))
+            passes = (passes + 1) / 2;
+        pl.pair = true;
+        pl.T = PAIR_T;
+        pl.chunk = per_pass * passes;
+        pl.nblk = blocks_of(passes);
+        pl.smem = (size_t)pair_smem_floats(d.P, d.H, pl.chunk, PAIR_T, cem) * 4;
     } else {
         int T = (size_t)rollout_smem_floats(d.P, d.H, 128, d.method == QPMPC_METHOD_CEM) * 4 <= h->max_smem ? 128 : 32;
         if (T == 128 && h->env.threads == 64) T = 64;
         pl.T = T;
         pl.nblk = (n + T - 1) / T;
+        pl.chunk = T;
         pl.smem = (size_t)rollout_smem_floats(d.P, d.H, T, d.method == QPMPC_METHOD_CEM) * 4;
     }
     return pl;
 }
 
-static rollout_fn pick_fn(const qpmpc_handle *h, const LaunchPlan &pl) {
+// eps: rows supplied in global memory (reference noise or the parameter matrix of jit_vectorized_rollout)
+static rollout_fn pick_fn(qpmpc_handle *h, const LaunchPlan &pl, bool eps) {
+    h->last_kernel = pl.pair ? "pair" : pl.quad ? "quad" : "thread";
+    if (pl.pair) return eps ? h->fn_pair[2] : h->dc.method == QPMPC_METHOD_MPPI ? h->fn_pair[0] : h->fn_pair[1];
     if (pl.quad) return pl.T == 512 ? h->fn_quad128 : pl.T == 288 ? h->fn_quad72 : h->fn_quad32;
     return pl.T == 128 ? h->fn128 : pl.T == 64 ? h->fn64 : h->fn32;
 }
@@ -1452,7 +1540,7 @@ static rollout_fn pick_fn(const qpmpc_handle *h, const LaunchPlan &pl) {
 extern "C" const char *qpmpc_last_error(void) { return g_err.c_str(); }
 #define QPMPC_STR2(x) #x
 #define QPMPC_STR(x) QPMPC_STR2(x)
-extern "C" const char *qpmpc_version(void) { return "qpmpc-b200 0.1 (sm_100a, cudart " QPMPC_STR(CUDART_VERSION) ")"; }
+extern "C" const char *qpmpc_version(void) { return "qpmpc-b200 0.2 noise-v2 (sm_100a, cudart " QPMPC_STR(CUDART_VERSION) ")"; }
 
 extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     if (!cfg || !out) return fail(QPMPC_E_ARG, "null argument");
@@ -1487,6 +1575,7 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     h->env = read_env();
     h->device = c.device;
     h->launches = 0;
+    h->last_kernel = "none";
     h->profiling = 0;
     DevCfg &d = h->dc;
     memset(&d, 0, sizeof d);
@@ -1518,15 +1607,18 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     h->fn_quad32 = pick_quad<32>(d.param, d.ga);
     h->fn_quad72 = pick_quad<72>(d.param, d.ga);
     h->fn_quad128 = pick_quad<128>(d.param, d.ga);
+    h->fn_pair[0] = k_rollout_pair<0, PAIR_T>;
+    h->fn_pair[1] = k_rollout_pair<1, PAIR_T>;
+    h->fn_pair[2] = k_rollout_pair<2, PAIR_T>;
     cudaError_t e = cudaSuccess;
     size_t static_smem = 0;  // the kernels' own __shared__ variables come out of the same per-block budget
-    for (rollout_fn f : {h->fn128, h->fn64, h->fn32, h->fn_quad32, h->fn_quad72, h->fn_quad128}) {
+    for (rollout_fn f : {h->fn128, h->fn64, h->fn32, h->fn_quad32, h->fn_quad72, h->fn_quad128, h->fn_pair[0], h->fn_pair[1], h->fn_pair[2]}) {
         cudaFuncAttributes fa;
         if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, (const void *)f);
         if (e == cudaSuccess && fa.sharedSizeBytes > static_smem) static_smem = fa.sharedSizeBytes;
     }
     h->max_smem -= static_smem;
-    for (rollout_fn f : {h->fn128, h->fn64, h->fn32, h->fn_quad32, h->fn_quad72, h->fn_quad128})
+    for (rollout_fn f : {h->fn128, h->fn64, h->fn32, h->fn_quad32, h->fn_quad72, h->fn_quad128, h->fn_pair[0], h->fn_pair[1], h->fn_pair[2]})
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute((const void *)f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_smem);
     if (e != cudaSuccess) { delete h; return fail(QPMPC_E_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e)); }
@@ -1583,6 +1675,7 @@ extern "C" int qpmpc_destroy(qpmpc_handle *h) {
 extern "C" int qpmpc_num_params(const qpmpc_handle *h) { return h ? h->dc.P : QPMPC_E_ARG; }
 extern "C" void *qpmpc_stream(qpmpc_handle *h) { return h ? (void *)h->stream : nullptr; }
 extern "C" int64_t qpmpc_launch_count(const qpmpc_handle *h) { return h ? h->launches : 0; }
+extern "C" const char *qpmpc_last_kernel(const qpmpc_handle *h) { return h ? h->last_kernel : "none"; }
 
 // launches k_rollout + k_finalize for `b` on the handle's stream (no synchronisation)
 static const InlineIn g_no_inline = {};
@@ -1610,16 +1703,19 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
     // parameter columns occupied.  Falls back to the stand-alone k_finalize when that scratch is too small
     // (huge N with tiny P) or when QPMPC_FUSED=0 asks for the two-kernel path (tests cover both).
     const int K = d.method == QPMPC_METHOD_CEM ? d.cem_elite : 0;
-    const int scratch = pl.quad ? P * (pl.T / 4 + 1) : P * (pl.T + 1);
+    const int scratch = pl.pair ? pair_smem_floats(P, d.H, pl.chunk, pl.T, d.method == QPMPC_METHOD_CEM) -
+                                      pair_fixed_floats(P, d.H, d.method == QPMPC_METHOD_CEM)
+                        : pl.quad ? P * (pl.T / 4 + 1) : P * (pl.T + 1);
     // Throughput regime (batched robots, many waves of blocks): the stand-alone k_finalize wins -- the arrival ticket
     // (fence + atomic round trip with the block's warps parked) and a last block that finalizes while two of its
     // SM's three slots wait cost more than one extra launch (C5: 3.09 -> 2.93 ms).  Latency regime: one launch.
-    const bool deep = !pl.quad && (long long)R * nblk > 8LL * h->num_sms;
+    // (the pair kernel with one block per robot has no ticket: it always finalizes in place)
+    const bool deep = !pl.quad && !(pl.pair && nblk == 1) && (long long)R * nblk > 8LL * h->num_sms;
     const bool want_fused = h->env.fused < 0 ? !deep : h->env.fused != 0;
     ra.fused = finalize_smem_floats(P, nblk, K, pl.T) <= scratch && want_fused;
-    ra.pipe = h->env.pipe;
+    ra.chunk = pl.chunk;
     if (h->profiling) CU(cudaEventRecord(h->ev[0], h->stream));
-    pick_fn(h, pl)<<<dim3(nblk, R), pl.T, pl.smem, h->stream>>>(d, ra, in);
+    pick_fn(h, pl, b.d_eps != nullptr)<<<dim3(nblk, R), pl.T, pl.smem, h->stream>>>(d, ra, in);
     CU(cudaGetLastError());
     if (h->profiling) CU(cudaEventRecord(h->ev[1], h->stream));
     h->launches += 1;
@@ -1819,7 +1915,8 @@ extern "C" int qpmpc_rollout_costs(qpmpc_handle *h, const float *state, const fl
     ra.eps = d_params; ra.freqs = d_freqs; ra.costs = d_costs; ra.n = n; ra.costs_only = 1;
     const LaunchPlan pl = plan_launch(h, n, n);
     ra.nblk = pl.nblk;
-    pick_fn(h, pl)<<<dim3(pl.nblk, 1), pl.T, pl.smem, h->stream>>>(d, ra, inline_in ? inl : g_no_inline);
+    ra.chunk = pl.chunk;
+    pick_fn(h, pl, true)<<<dim3(pl.nblk, 1), pl.T, pl.smem, h->stream>>>(d, ra, inline_in ? inl : g_no_inline);
     CU(cudaGetLastError());
     h->launches += 1;
     CU(cudaStreamSynchronize(h->stream));
@@ -1840,7 +1937,7 @@ extern "C" int qpmpc_generate_noise(qpmpc_handle *h, uint64_t seed, uint64_t off
         CU(cudaMemcpyAsync(h->d_in + o_sigma, h->h_in + o_sigma, (size_t)d.P * 4, cudaMemcpyHostToDevice, h->stream));
         d_sigma = h->d_in + o_sigma;
     }
-    const long long total = (long long)d.N * (d.P / 4);
+    const long long total = (long long)d.N * (d.P / NOISE_BLOCK);
     const int threads = 256;
     const long long blocks = (total + threads - 1) / threads;
     k_dump_noise<<<(unsigned)blocks, threads, 0, h->stream>>>(d, NoiseKey{seed, offset}, (uint32_t)robot, d_sigma,
@@ -1848,6 +1945,12 @@ extern "C" int qpmpc_generate_noise(qpmpc_handle *h, uint64_t seed, uint64_t off
                                                              d_freqs_out);
     CU(cudaGetLastError());
     h->launches += 1;
+    if (h->env.dump_pair) {  // test hook: overwrite the rows with the packed generator's (must be bit-identical)
+        k_dump_noise_pair<<<(unsigned)blocks, threads, 0, h->stream>>>(d, NoiseKey{seed, offset}, (uint32_t)robot, d_sigma,
+                                                                      d_eps_out);
+        CU(cudaGetLastError());
+        h->launches += 1;
+    }
     CU(cudaStreamSynchronize(h->stream));
     return QPMPC_OK;
 }

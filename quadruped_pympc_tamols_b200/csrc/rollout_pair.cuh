@@ -1,0 +1,135 @@
+// Two rollouts per thread on sm_100's packed FP32 (FFMA2 / FMUL2 / FADD2 on 64-bit register pairs): the SRBD step
+// of the throughput regime (batched robots, zero-order parametrisation, fixed gait).
+// Why packed: the thread-per-rollout kernel was bound by ISSUE SLOTS, not by the FMA pipe (profiles/r4c: 8,170 warp
+// instructions per rollout for 4,380 algorithmic FLOP, issue 72 % busy, FMA pipe 40 %).  A packed instruction does the
+// same arithmetic for rollouts A (.x) and B (.y) in one slot; per-robot values (feet, reference, contact flags,
+// inertia, weights) enter as broadcast scalar operands (R.F32 / UR.F32 / immediate), so they cost no pair registers.
+// Measured instruction rates behind the design: tools/ubench.cu -> profiles/r5_ubench.txt.
+// Every operation is an explicit round-to-nearest intrinsic: the arithmetic does not depend on the compiler's
+// contraction choices.  Math restated from
+//   controllers/sampling/centroidal_model_jax.py:93-174 (fd + Euler step),
+//   controllers/sampling/centroidal_nmpc_jax.py:259-314 (zero-order forces, force limits), :316-496 (rollout, cost).
+#pragma once
+#include "noise.cuh"
+
+namespace qp {
+
+__device__ __forceinline__ v2 vadd(v2 a, v2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ v2 vadd(v2 a, float s) { return __fadd2_rn(a, f2(s)); }
+__device__ __forceinline__ v2 vneg(v2 a) { return f2(-a.x, -a.y); }
+__device__ __forceinline__ v2 vsub(v2 a, v2 b) { return __fadd2_rn(a, vneg(b)); }
+__device__ __forceinline__ v2 vmul(v2 a, v2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ v2 vmul(v2 a, float s) { return __fmul2_rn(a, f2(s)); }
+__device__ __forceinline__ v2 vfma(v2 a, v2 b, v2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ v2 vfma(v2 a, float s, v2 c) { return __ffma2_rn(a, f2(s), c); }
+__device__ __forceinline__ v2 vfma(v2 a, v2 b, float s) { return __ffma2_rn(a, b, f2(s)); }
+__device__ __forceinline__ v2 vfma(v2 a, float s, float d) { return __ffma2_rn(a, f2(s), f2(d)); }
+
+// sincos_fast (srbd.cuh) for both halves: same reduction constants and polynomials; the quadrant comes from the
+// magic-number rounding (b * 2/pi + 1.5 * 2^23) - 1.5 * 2^23 = rint(b * 2/pi) for |b * 2/pi| < 2^22, whose low mantissa
+// bits are q -- one packed FMA and one packed add instead of F2I + I2F per half on the quarter-rate conversion pipe.
+// (The product is not rounded before the rint, so a quadrant can differ from the scalar version's at an exact tie of
+// b * 2/pi: the reduced argument then sits 1e-7 beyond pi/4, where both polynomials are still accurate to 1e-7.)
+__device__ __forceinline__ void sincos_fast2(v2 a, v2 &s, v2 &c) {
+    const v2 b = f2(fabsf(a.x) < 105615.0f ? a.x : 0.0f, fabsf(a.y) < 105615.0f ? a.y : 0.0f);
+    const v2 t = vfma(b, 0.636619772f, 12582912.0f);  // (written fused: ptxas would contract the pair anyway)
+    const v2 k = vadd(t, -12582912.0f);
+    v2 r = vfma(k, -1.5707962513e+0f, b);
+    r = vfma(k, -7.5497894159e-8f, r);
+    r = vfma(k, -5.3903029535e-15f, r);
+    const v2 r2 = vmul(r, r);
+    v2 cc = vfma(r2, 2.443315711809948e-5f, -1.388731625493765e-3f);
+    cc = vfma(cc, r2, 4.166664568298827e-2f);
+    cc = vfma(vmul(cc, r2), r2, vfma(r2, -0.5f, 1.0f));
+    v2 ss = vfma(r2, -1.9515295891e-4f, 8.3321608736e-3f);
+    ss = vfma(ss, r2, -1.6666654611e-1f);
+    ss = vfma(vmul(ss, r2), r, r);
+    const uint32_t qx = __float_as_uint(t.x), qy = __float_as_uint(t.y);
+    const bool ox = qx & 1u, oy = qy & 1u;
+    const uint32_t sx = __float_as_uint(ox ? cc.x : ss.x), cx = __float_as_uint(ox ? ss.x : cc.x);
+    const uint32_t sy = __float_as_uint(oy ? cc.y : ss.y), cy = __float_as_uint(oy ? ss.y : cc.y);
+    // sin: negate when bit 1 of q is set; cos: when bit 1 of q + 1 is set = bit 1 xor bit 0
+    s = f2(__uint_as_float(sx ^ ((qx << 30) & 0x80000000u)), __uint_as_float(sy ^ ((qy << 30) & 0x80000000u)));
+    c = f2(__uint_as_float(cx ^ (((qx << 30) ^ (qx << 31)) & 0x80000000u)),
+           __uint_as_float(cy ^ (((qy << 30) ^ (qy << 31)) & 0x80000000u)));
+}
+
+__device__ __forceinline__ v2 rcp2(v2 a) {
+    v2 y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y.x) : "f"(a.x));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y.y) : "f"(a.y));
+    return y;
+}
+
+// One SRBD step of rollouts A and B.  f[3 leg + axis] = the raw control parameters of this step (best + eps); st / st3 /
+// ref_fz / feet / ref are per-robot scalars.  Force shaping: centroidal_nmpc_jax.py:377-402 then :270-314 (max / min keep
+// the BOUND for a NaN input exactly like the reference's selects); fd multiplies the masked forces by the contact flag a
+// second time (centroidal_model_jax.py:111-116, 132-135), kept for all three components.
+__device__ __forceinline__ void pair_step(const DevCfg &c, v2 x[12], const float feet[12], const float ref[12], v2 f[12],
+                                          const float st[4], const float st3[4], float ref_fz, float dt, v2 &cost) {
+    v2 lx = f2(0.f), ly = f2(0.f), lz = f2(0.f), tx = f2(0.f), ty = f2(0.f), tz = f2(0.f);
+#pragma unroll
+    for (int l = 0; l < 4; ++l) {
+        v2 fz = vmul(vadd(f[3 * l + 2], ref_fz), st[l]);
+        v2 fx = vmul(f[3 * l], st3[l]), fy = vmul(f[3 * l + 1], st3[l]);
+        fz = f2(fminf(fmaxf(fz.x, c.fzmin), c.fzmax), fminf(fmaxf(fz.y, c.fzmin), c.fzmax));
+        const v2 lim = vmul(fz, c.mu);
+        fx = f2(fminf(fmaxf(fx.x, -lim.x), lim.x), fminf(fmaxf(fx.y, -lim.y), lim.y));
+        fy = f2(fminf(fmaxf(fy.x, -lim.x), lim.x), fminf(fmaxf(fy.y, -lim.y), lim.y));
+        fx = vmul(fx, st[l]);
+        fy = vmul(fy, st[l]);
+        fz = vmul(fz, st[l]);
+        lx = vadd(lx, fx);
+        ly = vadd(ly, fy);
+        lz = vadd(lz, fz);
+        const v2 rx = vsub(f2(feet[3 * l]), x[0]), ry = vsub(f2(feet[3 * l + 1]), x[1]), rz = vsub(f2(feet[3 * l + 2]), x[2]);
+        tx = vfma(ry, fz, tx);
+        tx = vfma(vneg(rz), fy, tx);
+        ty = vfma(rz, fx, ty);
+        ty = vfma(vneg(rx), fz, ty);
+        tz = vfma(rx, fy, tz);
+        tz = vfma(vneg(ry), fx, tz);
+    }
+    v2 sr, cr, sp, cp, sy, cy;
+    sincos_fast2(x[6], sr, cr);
+    sincos_fast2(x[7], sp, cp);
+    sincos_fast2(x[8], sy, cy);
+    const v2 wx = x[9], wy = x[10], wz = x[11];
+    // Euler-rate map, closed form of inv(conj_euler_rates) @ w (centroidal_model_jax.py:124-137), SFU reciprocal
+    const v2 yaw_rate = vmul(vfma(sr, wy, vmul(cr, wz)), rcp2(cp));
+    const v2 pitch_rate = vfma(cr, wy, vneg(vmul(sr, wz)));
+    const v2 roll_rate = vfma(sp, yaw_rate, wx);
+    // b_R_w @ tau (centroidal_model_jax.py:141-155)
+    const v2 srsp = vmul(sr, sp), crsp = vmul(cr, sp);
+    const v2 bx = vfma(vmul(cp, cy), tx, vfma(vmul(cp, sy), ty, vneg(vmul(sp, tz))));
+    const v2 by = vfma(vfma(srsp, cy, vneg(vmul(cr, sy))), tx, vfma(vfma(srsp, sy, vmul(cr, cy)), ty, vmul(vmul(sr, cp), tz)));
+    const v2 bz = vfma(vfma(crsp, cy, vmul(sr, sy)), tx, vfma(vfma(crsp, sy, vneg(vmul(sr, cy))), ty, vmul(vmul(cr, cp), tz)));
+    const v2 Iwx = vfma(wx, c.I[0], vfma(wy, c.I[1], vmul(wz, c.I[2])));
+    const v2 Iwy = vfma(wx, c.I[3], vfma(wy, c.I[4], vmul(wz, c.I[5])));
+    const v2 Iwz = vfma(wx, c.I[6], vfma(wy, c.I[7], vmul(wz, c.I[8])));
+    const v2 gx = vfma(wz, Iwy, vfma(vneg(wy), Iwz, bx));
+    const v2 gy = vfma(wx, Iwz, vfma(vneg(wz), Iwx, by));
+    const v2 gz = vfma(wy, Iwx, vfma(vneg(wx), Iwy, bz));
+    const v2 ax = vfma(gx, c.Iinv[0], vfma(gy, c.Iinv[1], vmul(gz, c.Iinv[2])));
+    const v2 ay = vfma(gx, c.Iinv[3], vfma(gy, c.Iinv[4], vmul(gz, c.Iinv[5])));
+    const v2 az = vfma(gx, c.Iinv[6], vfma(gy, c.Iinv[7], vmul(gz, c.Iinv[8])));
+    x[0] = vfma(x[3], dt, x[0]);
+    x[1] = vfma(x[4], dt, x[1]);
+    x[2] = vfma(x[5], dt, x[2]);
+    x[3] = vfma(vmul(lx, c.inv_mass), dt, x[3]);
+    x[4] = vfma(vmul(ly, c.inv_mass), dt, x[4]);
+    x[5] = vfma(vfma(lz, c.inv_mass, -9.81f), dt, x[5]);
+    x[6] = vfma(roll_rate, dt, x[6]);
+    x[7] = vfma(pitch_rate, dt, x[7]);
+    x[8] = vfma(yaw_rate, dt, x[8]);
+    x[9] = vfma(ax, dt, x[9]);
+    x[10] = vfma(ay, dt, x[10]);
+    x[11] = vfma(az, dt, x[11]);
+#pragma unroll
+    for (int k = 0; k < 12; ++k) {
+        const v2 e = vadd(x[k], -ref[k]);
+        cost = vfma(vmul(e, c.q[k]), e, cost);
+    }
+}
+
+}  // namespace qp

@@ -13,7 +13,8 @@ torch = pytest.importorskip("torch")
 
 from oracle import srbd_oracle as so  # noqa: E402  (checker only)
 from quadruped_pympc_tamols_b200 import _cabi  # noqa: E402
-from tests.util import fixture_kwargs, rel_err, sampling_fixtures, softmin_tolerance, softmin_update_f64  # noqa: E402
+from tests.util import (fixture_kwargs, oracle_tail, rel_err, sampling_fixtures, softmin_tolerance,  # noqa: E402
+                        softmin_update_f64)
 
 pytestmark = pytest.mark.gpu
 
@@ -79,7 +80,7 @@ def dev(a):
     return torch.as_tensor(np.ascontiguousarray(a, np.float32), device="cuda")
 
 
-def compare(r, o, method, tag="", best_atol=BEST_ATOL, eps=None, best_in=None):
+def compare(r, o, method, tag="", best_atol=BEST_ATOL, eps=None, best_in=None, tail=None):
     """Every output of one solve against the oracle.  With `eps` (the noise both sides consumed) the update is checked
     twice: tightly (1e-4) against the float64 softmin of the CUDA path's OWN costs, which pins the update arithmetic,
     and against the oracle's update with the conditioning-aware tolerance of tests/util.py:softmin_tolerance."""
@@ -91,7 +92,13 @@ def compare(r, o, method, tag="", best_atol=BEST_ATOL, eps=None, best_in=None):
     assert abs(float(r["best_cost"]) - float(o["best_cost"])) <= COST_RTOL * abs(float(o["best_cost"])), tag
     assert np.max(np.abs(r["best"] - o["best"])) < best_atol, tag
     assert np.max(np.abs(r["grf"] - o["grf"])) < best_atol * 10, tag
-    assert rel_err(r["predicted_state"], o["predicted_state"], 1e-2) < 1e-4, tag
+    # the prediction inherits the update's conditioning (it is one Euler step under the first GRFs): 1e-4 while the
+    # plain 1e-3 bar applies to the update, scaled with the widened tolerance otherwise; `tail` (when given) is the
+    # oracle's GRF / prediction evaluated at the CUDA path's OWN mean and pins that arithmetic tightly
+    assert rel_err(r["predicted_state"], o["predicted_state"], 1e-2) < 1e-4 * best_atol / BEST_ATOL, tag
+    if tail is not None:
+        assert np.max(np.abs(r["grf"] - tail[0])) < 1e-4 * max(1.0, float(np.max(np.abs(tail[0])))), tag
+        assert rel_err(r["predicted_state"], tail[1], 1e-2) < 1e-5, tag
     assert abs(float(r["best_freq"]) - float(o["best_freq"])) < 1e-6, tag
     assert np.all(r["footholds"] == 0)
     if method == "cem_mppi":
@@ -167,13 +174,20 @@ def test_philox_solve_matches_oracle_on_same_noise(robot, gait, method, param, g
         r = h.solve(st, ref, seq, best, seed=42, offset=it, timing=timing, nominal_freq=nominal, optimize_swing=oswing,
                     sigma_in=sigma if method == "cem_mppi" else None)
         o = so.solve(ocfg, method, st, ref, seq, best, eps, timing=timing, freqs=freqs, fast=False)
-        compare(r, o, method, tag=f"it{it}", eps=eps, best_in=best)
-        # the supplied-noise path must agree with the Philox path bit for bit on the costs
+        compare(r, o, method, tag=f"it{it}", eps=eps, best_in=best,
+                tail=oracle_tail(so, ocfg, st, ref, seq, r["best"], timing=timing))
+        # the supplied-noise path must agree with the in-kernel path bit for bit on the costs.  (The packed pair kernel
+        # folds the parameter addition into the Box-Muller product, best + r cos = one FMA: its parameters carry one
+        # rounding fewer than best + eps of the dumped noise, <= 1 ulp, so its costs agree to round-off instead.)
         r2 = h.solve(st, ref, seq, best, seed=42, offset=it, timing=timing, nominal_freq=nominal, optimize_swing=oswing,
                      sigma_in=sigma if method == "cem_mppi" else None, d_eps=d_eps.data_ptr(),
                      d_freqs=d_freqs.data_ptr() if ga else None)
-        assert np.array_equal(r["costs"], r2["costs"])
-        assert np.max(np.abs(r["best"] - r2["best"])) < 1e-5
+        if h.last_kernel == "pair":
+            assert rel_err(r["costs"], r2["costs"]) < 5e-6
+            assert np.max(np.abs(r["best"] - r2["best"])) < softmin_tolerance(r["costs"], r2["costs"], eps, base=1e-5)
+        else:
+            assert np.array_equal(r["costs"], r2["costs"])
+            assert np.max(np.abs(r["best"] - r2["best"])) < 1e-5
         best = r["best"]
         if method == "cem_mppi":
             sigma = r["sigma"]
@@ -295,7 +309,10 @@ def test_batched_robots_match_single_solves(kernel):
         tol = softmin_tolerance(costs[r], o["costs"], eps, base=BEST_ATOL)
         assert np.max(np.abs(bo[r] - o["best"])) < tol
         assert np.max(np.abs(res[r, :12] - o["grf"])) < tol * 10
-        assert rel_err(res[r, 24:48], o["predicted_state"], 1e-2) < 1e-4
+        assert rel_err(res[r, 24:48], o["predicted_state"], 1e-2) < 1e-4 * tol / BEST_ATOL
+        grf_t, pred_t = oracle_tail(so, ocfg, probs[r][0], probs[r][1], probs[r][2], bo[r])
+        assert np.max(np.abs(res[r, :12] - grf_t)) < 1e-4 * max(1.0, float(np.max(np.abs(grf_t))))
+        assert rel_err(res[r, 24:48], pred_t, 1e-2) < 1e-5
         assert abs(res[r, 48] - o["best_cost"]) <= COST_RTOL * abs(o["best_cost"])
     assert not np.array_equal(costs[0, 1:], costs[1, 1:])
     h.close()

@@ -76,6 +76,16 @@ def softmin_tolerance(costs_gpu, costs_oracle, eps, base=1e-3):
     return base + (np.exp(2 * delta) - 1) * spread
 
 
+def oracle_tail(so, ocfg, state, ref, contact_seq, best, timing=None):
+    """First-step GRFs and one-step prediction of the ORACLE evaluated at a given mean `best`
+    (centroidal_nmpc_jax.py:707-784): one solve with a single zero-noise sample.  Pins the tail of the CUDA solve
+    tightly, independent of the conditioning of the update that produced `best`."""
+    best = np.asarray(best, np.float32)
+    o = so.solve(ocfg, "random_sampling", state, ref, contact_seq, best, np.zeros((1, best.size), np.float32),
+                 timing=timing, freqs=np.full(1, 1.4, np.float32))
+    return o["grf"], o["predicted_state"]
+
+
 def softmin_update_f64(best_in, costs, eps):
     """best + sum_i softmin(costs)_i eps_i evaluated in float64 from the given (already saturated) costs."""
     c = np.asarray(costs, np.float64)
