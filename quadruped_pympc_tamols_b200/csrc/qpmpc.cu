@@ -796,6 +796,7 @@ __global__ void __launch_bounds__(T, T == 128 ? 3 : T == 64 ? 6 : 1) k_rollout(c
 // MODE 0: in-kernel noise, scalar-sigma normals (mppi); 1: in-kernel noise, any method; 2: rows supplied in global
 // memory (reference noise for the equivalence tests, or the parameter matrix of jit_vectorized_rollout).
 constexpr int PAIR_T = 128;
+constexpr float PAIR_LIVE_CUTOFF = 24.0f;  // cost distance from the minimum beyond which a sample's weight is dropped
 __host__ __device__ inline int pair_fixed_floats(int P, int H, bool cem) {
     return (cem ? 2 : 1) * P + 24 + 12 + 8 * H + ((H + 3) & ~3);
 }
@@ -930,14 +931,21 @@ __global__ void __launch_bounds__(T, 3) k_rollout_pair(const __grid_constant__ D
     } else {
         // softmin numerators relative to the block minimum (merged exactly by finalize_robot), :828-836.  Thread t owns
         // the contiguous costs [E t, E t + E): live samples are compacted in ascending order with one block scan.
+        // LIVE = within PAIR_LIVE_CUTOFF of the block minimum, i.e. weight >= e^-24 = 3.8e-11 of the largest: the
+        // rest is left out of numerator AND denominator, which moves the update by at most 2 N e^-24 max|eps| (1e-6
+        // at N = 1024), below the float32 round-off of the sum itself.  Without the cutoff a converged controller
+        // (cost spread of tens, not thousands) keeps hundreds of samples at weights of 1e-30 whose rows would all
+        // have to be drawn again for nothing (tools/debug_nlive.py: 757 of 1024 with w > 0, 206 within the cutoff).
         const int E = (chunk + T - 1) / T, j0 = E * t, j1 = min(j0 + E, cn);
         const int lane = t & 31, wid = t >> 5;
         float sw = 0.f;
         int cnt = 0;
         for (int j = j0; j < j1; ++j) {
-            const float w = __expf(-(s_cost[j] - bc));
-            sw += w;
-            cnt += w > 0.f ? 1 : 0;
+            const float d = s_cost[j] - bc;
+            if (d <= PAIR_LIVE_CUTOFF) {
+                sw += __expf(-d);
+                ++cnt;
+            }
         }
         int incl = cnt;
 #pragma unroll
@@ -960,10 +968,10 @@ __global__ void __launch_bounds__(T, 3) k_rollout_pair(const __grid_constant__ D
             swb += s_red[32 + k];
         }
         for (int j = j0; j < j1; ++j) {
-            const float w = __expf(-(s_cost[j] - bc));
-            if (w > 0.f) {
+            const float d = s_cost[j] - bc;
+            if (d <= PAIR_LIVE_CUTOFF) {
                 s_live[off] = (unsigned short)j;
-                s_w[off] = w;
+                s_w[off] = __expf(-d);
                 ++off;
             }
         }
@@ -974,25 +982,42 @@ __global__ void __launch_bounds__(T, 3) k_rollout_pair(const __grid_constant__ D
             part[3] = __int_as_float(bi);
         }
         __syncthreads();
+        // V[p] = sum over the live samples of w (best[p] + eps[p]): thread (sl, b) draws noise block b of the live
+        // samples 2 sl, 2 sl + 1, then 2 (sl + S), ... again, two rows at a time through the packed generator
         const int B = P / NOISE_BLOCK, S = max(1, T / B);
         for (int u = t; u < S * B; u += T) {
             const int sl = u / B, b = u - sl * B;
             float acc[NOISE_BLOCK];
+            if (MODE == 2) {
 #pragma unroll
-            for (int k = 0; k < NOISE_BLOCK; ++k) acc[k] = 0.f;
-            for (int l = sl; l < nlive; l += S) {
-                const int i = base + s_live[l];
-                const float w = s_w[l];
-                float e[NOISE_BLOCK];
-                if (MODE == 2) {
-                    const float *src = a.eps + ((size_t)r * a.n + i) * P;
+                for (int k = 0; k < NOISE_BLOCK; ++k) acc[k] = 0.f;
+                for (int l = sl; l < nlive; l += S) {
+                    const float *src = a.eps + ((size_t)r * a.n + base + s_live[l]) * P;
+                    const float w = s_w[l];
 #pragma unroll
-                    for (int k = 0; k < NOISE_BLOCK; ++k) e[k] = src[k * H + b];
-                } else {
-                    noise_block(row_noise(c, i), a.key, b, robot, e, [&](int k) { return s_sg[NOISE_BLOCK * b + k]; });
+                    for (int k = 0; k < NOISE_BLOCK; ++k)
+                        acc[k] = fmaf(w, __fadd_rn(src[k * H + b], s_bt[NOISE_BLOCK * b + k]), acc[k]);
+                }
+            } else {
+                v2 acc2[NOISE_BLOCK];
+                float bst[NOISE_BLOCK];
+#pragma unroll
+                for (int k = 0; k < NOISE_BLOCK; ++k) {
+                    acc2[k] = f2(0.f);
+                    bst[k] = s_bt[NOISE_BLOCK * b + k];
+                }
+                for (int l = 2 * sl; l < nlive; l += 2 * S) {
+                    const bool two = l + 1 < nlive;
+                    const int ia = base + s_live[l], ib = base + s_live[two ? l + 1 : l];
+                    const v2 w2 = f2(s_w[l], two ? s_w[l + 1] : 0.f);
+                    v2 par[NOISE_BLOCK];
+                    noise_block_pair<MODE == 0>(row_noise(c, ia), row_noise(c, ib), a.key, b, robot, bst, par,
+                                                [&](int k) { return s_sg[NOISE_BLOCK * b + k]; });
+#pragma unroll
+                    for (int k = 0; k < NOISE_BLOCK; ++k) acc2[k] = vfma(par[k], w2, acc2[k]);
                 }
 #pragma unroll
-                for (int k = 0; k < NOISE_BLOCK; ++k) acc[k] = fmaf(w, __fadd_rn(e[k], s_bt[NOISE_BLOCK * b + k]), acc[k]);
+                for (int k = 0; k < NOISE_BLOCK; ++k) acc[k] = acc2[k].x + acc2[k].y;
             }
 #pragma unroll
             for (int k = 0; k < NOISE_BLOCK; ++k) s_acc[sl * P + NOISE_BLOCK * b + k] = acc[k];

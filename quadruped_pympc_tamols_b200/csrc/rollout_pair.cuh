@@ -64,20 +64,21 @@ __device__ __forceinline__ v2 rcp2(v2 a) {
 // One SRBD step of rollouts A and B.  f[3 leg + axis] = the raw control parameters of this step (best + eps); st / st3 /
 // ref_fz / feet / ref are per-robot scalars.  Force shaping: centroidal_nmpc_jax.py:377-402 then :270-314 (max / min keep
 // the BOUND for a NaN input exactly like the reference's selects); fd multiplies the masked forces by the contact flag a
-// second time (centroidal_model_jax.py:111-116, 132-135), kept for all three components.
+// second time (centroidal_model_jax.py:111-116, 132-135): fz explicitly, fx and fy through the masked friction limit.
 __device__ __forceinline__ void pair_step(const DevCfg &c, v2 x[12], const float feet[12], const float ref[12], v2 f[12],
                                           const float st[4], const float st3[4], float ref_fz, float dt, v2 &cost) {
+    const float must[4] = {c.mu * st[0], c.mu * st[1], c.mu * st[2], c.mu * st[3]};
     v2 lx = f2(0.f), ly = f2(0.f), lz = f2(0.f), tx = f2(0.f), ty = f2(0.f), tz = f2(0.f);
 #pragma unroll
     for (int l = 0; l < 4; ++l) {
         v2 fz = vmul(vadd(f[3 * l + 2], ref_fz), st[l]);
         v2 fx = vmul(f[3 * l], st3[l]), fy = vmul(f[3 * l + 1], st3[l]);
         fz = f2(fminf(fmaxf(fz.x, c.fzmin), c.fzmax), fminf(fmaxf(fz.y, c.fzmin), c.fzmax));
-        const v2 lim = vmul(fz, c.mu);
+        // friction limit already masked by the contact flag: a swing leg clamps to [-0, 0], which is what the second
+        // multiplication by the flag in fd gives for fx, fy (also for a NaN parameter); fz keeps its own
+        const v2 lim = vmul(fz, must[l]);
         fx = f2(fminf(fmaxf(fx.x, -lim.x), lim.x), fminf(fmaxf(fx.y, -lim.y), lim.y));
         fy = f2(fminf(fmaxf(fy.x, -lim.x), lim.x), fminf(fmaxf(fy.y, -lim.y), lim.y));
-        fx = vmul(fx, st[l]);
-        fy = vmul(fy, st[l]);
         fz = vmul(fz, st[l]);
         lx = vadd(lx, fx);
         ly = vadd(ly, fy);

@@ -32,14 +32,15 @@ __device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
 enum Kind {
     K_FFMA_RRR, K_FFMA_RRC, K_FFMA_SHARED_OPS, K_FMUL_RR, K_FADD_RR, K_FFMA2, K_FMUL2, K_FADD2, K_IMADW, K_IMAD, K_LOP3,
     K_IADD3, K_FMNMX, K_FSEL, K_MUFU_LG2, K_MUFU_SIN, K_MUFU_RCP, K_MUFU_SQRT, K_I2F, K_F2I, K_SHFL, K_MIX_FFMA_LOP,
-    K_MIX_FFMA2_LOP, K_MIX_FFMA2_IMADW, K_MIX_FFMA_MUFU, K_MIX_ALL, K_LDS, K_COUNT
+    K_MIX_FFMA2_LOP, K_MIX_FFMA2_IMADW, K_MIX_FFMA_MUFU, K_MIX_ALL, K_LDS, K_FFMA2_BCAST, K_FFMA2_SHARED, K_FFMA2_CONST, K_FFMA2_ACC, K_FADD2_BCAST, K_SHF, K_FFMA_ACC, K_COUNT
 };
 static const char *names[K_COUNT] = {
     "FFMA r,r,r (distinct regs)", "FFMA r,r,c (const bank)", "FFMA r,r,r (2 shared operands)", "FMUL r,r", "FADD r,r",
     "FFMA2 (fma.rn.f32x2)", "FMUL2 (mul.rn.f32x2)", "FADD2 (add.rn.f32x2)", "IMAD.WIDE (umulhi+lo)", "IMAD (32-bit)", "LOP3",
     "IADD3", "FMNMX", "FSEL/compare-select", "MUFU.LG2", "MUFU.SIN", "MUFU.RCP", "MUFU.SQRT", "I2FP (u32->f32)", "F2I",
     "SHFL.BFLY", "mix 1 FFMA : 1 LOP3", "mix 1 FFMA2 : 1 LOP3", "mix 1 FFMA2 : 1 IMAD.WIDE", "mix 4 FFMA : 1 MUFU",
-    "mix FFMA2+IMAD.WIDE+LOP3+MUFU (4:2:2:1)", "LDS.32 conflict-free"};
+    "mix FFMA2+IMAD.WIDE+LOP3+MUFU (4:2:2:1)", "LDS.32 conflict-free",
+    "FFMA2 p,scalar-bcast,r (R.F32)", "FFMA2 p,q0,r0 (2 shared pairs)", "FFMA2 p,const,const-ish (c-bank/imm)", "FFMA2 acc: p=fma(q,r,p)", "FADD2 p,scalar-bcast", "SHF.L.W (rotate)", "FFMA acc: x=fma(y,z,x)"};
 
 template <int KIND>
 __global__ void __launch_bounds__(256) k_bench(float *out, const float *in, int iters, float ca, float cb) {
@@ -135,6 +136,13 @@ __global__ void __launch_bounds__(256) k_bench(float *out, const float *in, int 
                     asm volatile("lg2.approx.ftz.f32 %0, %0;" : "+f"(x[k]));
                 }
                 if (KIND == K_LDS) x[k] += s_buf[(t + 32 * k + (i & 1) * 256) & 1023];
+                if (KIND == K_FFMA2_BCAST) p[k] = ffma2(p[k], make_float2(y[k], y[k]), r[k]);
+                if (KIND == K_FFMA2_SHARED) p[k] = ffma2(p[k], q[0], r[0]);
+                if (KIND == K_FFMA2_CONST) p[k] = ffma2(p[k], make_float2(ca, ca), make_float2(cb, cb));
+                if (KIND == K_FFMA2_ACC) p[k] = ffma2(q[k], r[k], p[k]);
+                if (KIND == K_FADD2_BCAST) p[k] = fadd2(p[k], make_float2(y[k], y[k]));
+                if (KIND == K_SHF) u[k] = __funnelshift_l(u[k], u[k], 11) ^ v[k];
+                if (KIND == K_FFMA_ACC) x[k] = fmaf(y[k], z[k], x[k]);
             }
         }
     }
@@ -217,5 +225,12 @@ int main() {
     run<K_MIX_FFMA_MUFU>(d_out, d_in, sms, clk, 5, 8);
     run<K_MIX_ALL>(d_out, d_in, sms, clk, 8, 16);
     run<K_LDS>(d_out, d_in, sms, clk, 2, 1);
+    run<K_FFMA2_BCAST>(d_out, d_in, sms, clk, 1, 4);
+    run<K_FFMA2_SHARED>(d_out, d_in, sms, clk, 1, 4);
+    run<K_FFMA2_CONST>(d_out, d_in, sms, clk, 1, 4);
+    run<K_FFMA2_ACC>(d_out, d_in, sms, clk, 1, 4);
+    run<K_FADD2_BCAST>(d_out, d_in, sms, clk, 1, 2);
+    run<K_SHF>(d_out, d_in, sms, clk, 2, 0);
+    run<K_FFMA_ACC>(d_out, d_in, sms, clk, 1, 2);
     return 0;
 }
