@@ -805,7 +805,7 @@ __host__ __device__ inline int pair_smem_floats(int P, int H, int chunk, int T, 
     return pair_fixed_floats(P, H, cem) + chunk + chunk + chunk / 2 + 64 + S * P;
 }
 
-template <int MODE, int T>
+template <int MODE, int T, bool QSPARSE>
 __global__ void __launch_bounds__(T, 3) k_rollout_pair(const __grid_constant__ DevCfg c, const RolloutArgs a_,
                                                        const __grid_constant__ InlineIn in) {
     const RolloutArgs a = resolve_inputs(a_, in);
@@ -895,7 +895,7 @@ __global__ void __launch_bounds__(T, 3) k_rollout_pair(const __grid_constant__ D
             const float4 st4 = *reinterpret_cast<const float4 *>(s_st + 8 * n);
             const float4 st34 = *reinterpret_cast<const float4 *>(s_st + 8 * n + 4);
             const float st[4] = {st4.x, st4.y, st4.z, st4.w}, st3[4] = {st34.x, st34.y, st34.z, st34.w};
-            pair_step(c, x, feet, ref, f, st, st3, s_reffz[n], c.dts[n], cost);
+            pair_step<QSPARSE>(c, x, feet, ref, f, st, st3, s_reffz[n], c.dts[n], cost);
         }
         if (!a.costs_only) {  // centroidal_nmpc_jax.py:686-687
             cost.x = isnan(cost.x) ? 1000000.0f : cost.x;
@@ -1632,9 +1632,12 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     h->fn_quad32 = pick_quad<32>(d.param, d.ga);
     h->fn_quad72 = pick_quad<72>(d.param, d.ga);
     h->fn_quad128 = pick_quad<128>(d.param, d.ga);
-    h->fn_pair[0] = k_rollout_pair<0, PAIR_T>;
-    h->fn_pair[1] = k_rollout_pair<1, PAIR_T>;
-    h->fn_pair[2] = k_rollout_pair<2, PAIR_T>;
+    // stage cost without its zero-weight terms when Q has the reference's pattern (rollout_pair.cuh: QSPARSE)
+    const bool qsparse = c.q_diag[0] == 0.f && c.q_diag[1] == 0.f && c.q_diag[8] == 0.f && c.q_diag[3] > 0.f &&
+                         c.q_diag[4] > 0.f && c.q_diag[6] > 0.f;
+    h->fn_pair[0] = qsparse ? k_rollout_pair<0, PAIR_T, true> : k_rollout_pair<0, PAIR_T, false>;
+    h->fn_pair[1] = qsparse ? k_rollout_pair<1, PAIR_T, true> : k_rollout_pair<1, PAIR_T, false>;
+    h->fn_pair[2] = qsparse ? k_rollout_pair<2, PAIR_T, true> : k_rollout_pair<2, PAIR_T, false>;
     cudaError_t e = cudaSuccess;
     size_t static_smem = 0;  // the kernels' own __shared__ variables come out of the same per-block budget
     for (rollout_fn f : {h->fn128, h->fn64, h->fn32, h->fn_quad32, h->fn_quad72, h->fn_quad128, h->fn_pair[0], h->fn_pair[1], h->fn_pair[2]}) {

@@ -65,9 +65,13 @@ __device__ __forceinline__ v2 rcp2(v2 a) {
 // ref_fz / feet / ref are per-robot scalars.  Force shaping: centroidal_nmpc_jax.py:377-402 then :270-314 (max / min keep
 // the BOUND for a NaN input exactly like the reference's selects); fd multiplies the masked forces by the contact flag a
 // second time (centroidal_model_jax.py:111-116, 132-135): fz explicitly, fx and fy through the masked friction limit.
+template <bool QSPARSE>
 __device__ __forceinline__ void pair_step(const DevCfg &c, v2 x[12], const float feet[12], const float ref[12], v2 f[12],
                                           const float st[4], const float st3[4], float ref_fz, float dt, v2 &cost) {
     const float must[4] = {c.mu * st[0], c.mu * st[1], c.mu * st[2], c.mu * st[3]};
+    // net force and, about the ORIGIN, the moment of the four ground reaction forces; the torque about the centre of
+    // mass is then sum (r_foot - com) x f = sum r_foot x f - com x sum f: the foot positions enter as broadcast scalars
+    // (cheaper operand form than three register pairs) and the twelve lever-arm subtractions become one cross product
     v2 lx = f2(0.f), ly = f2(0.f), lz = f2(0.f), tx = f2(0.f), ty = f2(0.f), tz = f2(0.f);
 #pragma unroll
     for (int l = 0; l < 4; ++l) {
@@ -83,14 +87,17 @@ __device__ __forceinline__ void pair_step(const DevCfg &c, v2 x[12], const float
         lx = vadd(lx, fx);
         ly = vadd(ly, fy);
         lz = vadd(lz, fz);
-        const v2 rx = vsub(f2(feet[3 * l]), x[0]), ry = vsub(f2(feet[3 * l + 1]), x[1]), rz = vsub(f2(feet[3 * l + 2]), x[2]);
-        tx = vfma(ry, fz, tx);
-        tx = vfma(vneg(rz), fy, tx);
-        ty = vfma(rz, fx, ty);
-        ty = vfma(vneg(rx), fz, ty);
-        tz = vfma(rx, fy, tz);
-        tz = vfma(vneg(ry), fx, tz);
+        const float px = feet[3 * l], py = feet[3 * l + 1], pz = feet[3 * l + 2];
+        tx = vfma(fz, py, tx);
+        tx = vfma(fy, -pz, tx);
+        ty = vfma(fx, pz, ty);
+        ty = vfma(fz, -px, ty);
+        tz = vfma(fy, px, tz);
+        tz = vfma(fx, -py, tz);
     }
+    tx = vfma(vneg(x[1]), lz, vfma(x[2], ly, tx));
+    ty = vfma(vneg(x[2]), lx, vfma(x[0], lz, ty));
+    tz = vfma(vneg(x[0]), ly, vfma(x[1], lx, tz));
     v2 sr, cr, sp, cp, sy, cy;
     sincos_fast2(x[6], sr, cr);
     sincos_fast2(x[7], sp, cp);
@@ -100,11 +107,14 @@ __device__ __forceinline__ void pair_step(const DevCfg &c, v2 x[12], const float
     const v2 yaw_rate = vmul(vfma(sr, wy, vmul(cr, wz)), rcp2(cp));
     const v2 pitch_rate = vfma(cr, wy, vneg(vmul(sr, wz)));
     const v2 roll_rate = vfma(sp, yaw_rate, wx);
-    // b_R_w @ tau (centroidal_model_jax.py:141-155)
-    const v2 srsp = vmul(sr, sp), crsp = vmul(cr, sp);
-    const v2 bx = vfma(vmul(cp, cy), tx, vfma(vmul(cp, sy), ty, vneg(vmul(sp, tz))));
-    const v2 by = vfma(vfma(srsp, cy, vneg(vmul(cr, sy))), tx, vfma(vfma(srsp, sy, vmul(cr, cy)), ty, vmul(vmul(sr, cp), tz)));
-    const v2 bz = vfma(vfma(crsp, cy, vmul(sr, sy)), tx, vfma(vfma(crsp, sy, vneg(vmul(sr, cy))), ty, vmul(vmul(cr, cp), tz)));
+    // b_R_w @ tau (centroidal_model_jax.py:141-155) as three planar rotations, yaw then pitch then roll: the same matrix
+    // product (b_R_w = Rx(roll)^T Ry(pitch)^T Rz(yaw)^T) in 12 operations instead of 26 for the nine entries + mat-vec
+    const v2 u1 = vfma(cy, tx, vmul(sy, ty));
+    const v2 v1 = vfma(cy, ty, vneg(vmul(sy, tx)));
+    const v2 bx = vfma(cp, u1, vneg(vmul(sp, tz)));
+    const v2 w2 = vfma(sp, u1, vmul(cp, tz));
+    const v2 by = vfma(cr, v1, vmul(sr, w2));
+    const v2 bz = vfma(cr, w2, vneg(vmul(sr, v1)));
     const v2 Iwx = vfma(wx, c.I[0], vfma(wy, c.I[1], vmul(wz, c.I[2])));
     const v2 Iwy = vfma(wx, c.I[3], vfma(wy, c.I[4], vmul(wz, c.I[5])));
     const v2 Iwz = vfma(wx, c.I[6], vfma(wy, c.I[7], vmul(wz, c.I[8])));
@@ -126,10 +136,16 @@ __device__ __forceinline__ void pair_step(const DevCfg &c, v2 x[12], const float
     x[9] = vfma(ax, dt, x[9]);
     x[10] = vfma(ay, dt, x[10]);
     x[11] = vfma(az, dt, x[11]);
+    // stage cost on the new state: sum q_k (x_k - ref_k)^2 over the body states (centroidal_nmpc_jax.py:450-451, 491).
+    // QSPARSE: q[0] = q[1] = q[8] = 0 as in the reference's Q (:118-130), so those three terms are not evaluated.
+    // Upstream a zero weight times a non-finite state still makes the cost NaN (-> 1e6); nothing is lost here, because
+    // x, y and yaw can only become non-finite together with vx, vy and roll (x += vx dt; yaw' and roll' share the
+    // 1 / cos(pitch) factor), whose weights the host requires to be positive before it selects a QSPARSE kernel.
 #pragma unroll
     for (int k = 0; k < 12; ++k) {
+        if (QSPARSE && (k == 0 || k == 1 || k == 8)) continue;
         const v2 e = vadd(x[k], -ref[k]);
-        cost = vfma(vmul(e, c.q[k]), e, cost);
+        cost = vfma(vmul(e, e), c.q[k], cost);
     }
 }
 
