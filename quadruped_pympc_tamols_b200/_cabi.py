@@ -12,7 +12,7 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libqpmpc_b200.so")
+LIB_PATH = os.environ.get("QPMPC_LIB") or os.path.join(_HERE, "lib", "libqpmpc_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 QPMPC_MAX_H = 32

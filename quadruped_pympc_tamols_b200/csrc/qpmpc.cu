@@ -805,118 +805,20 @@ __host__ __device__ inline int pair_smem_floats(int P, int H, int chunk, int T, 
     return pair_fixed_floats(P, H, cem) + chunk + chunk + chunk / 2 + 64 + S * P;
 }
 
-template <int MODE, int T, bool QSPARSE>
-__global__ void __launch_bounds__(T, 3) k_rollout_pair(const __grid_constant__ DevCfg c, const RolloutArgs a_,
-                                                       const __grid_constant__ InlineIn in) {
-    const RolloutArgs a = resolve_inputs(a_, in);
-    extern __shared__ __align__(16) float smem[];
+// Block partials of `cn` rollouts base .. base + cn - 1 of robot r whose costs sit in s_cost: {min, sum w, min, argmin}
+// + V[P] = sum over the live samples of w (best + eps), the rows drawn again.  All threads of the block (T = PAIR_T).
+struct PairSmem {
+    float *s_bt, *s_sg, *s_cost, *s_w, *s_red, *s_acc;
+    unsigned short *s_live;
+};
+template <int MODE>
+__device__ __forceinline__ void pair_block_partials(const DevCfg &c, const RolloutArgs &a, const PairSmem &sm, int r,
+                                                    int base, int cn, int chunk, float *part) {
+    constexpr int T = PAIR_T;
     const int P = c.P, H = c.H, t = threadIdx.x;
-    const bool cem = c.method == QPMPC_METHOD_CEM;
-    float *s_bt = smem;
-    float *s_sg = s_bt + P;
-    float *s_state = s_sg + (cem ? P : 0);
-    float *s_ref = s_state + 24;
-    float *s_st = s_ref + 12;
-    float *s_reffz = s_st + 8 * H;
-    float *s_cost = s_reffz + ((H + 3) & ~3);
-    const int chunk = a.chunk;
-    float *s_w = s_cost + chunk;
-    unsigned short *s_live = reinterpret_cast<unsigned short *>(s_w + chunk);
-    float *s_red = s_w + chunk + chunk / 2;
-    float *s_acc = s_red + 64;
-
-    const int r = blockIdx.y;
-    const int base = blockIdx.x * chunk;
-    const int cn = min(chunk, a.n - base);  // rollouts of this block
+    float *s_bt = sm.s_bt, *s_sg = sm.s_sg, *s_cost = sm.s_cost, *s_w = sm.s_w, *s_red = sm.s_red, *s_acc = sm.s_acc;
+    unsigned short *s_live = sm.s_live;
     const uint32_t robot = (uint32_t)(r + a.robot_offset);
-
-    // ---- stage the robot's problem: best / sigma transposed to step-major order (value k of step n at [12 n + k]),
-    // state, reference, contact tables.  All global loads of a thread are issued before its first store.
-    {
-        const int role = t >> 5, tl = t & 31;
-        const bool j_state = role == 1 && tl < 24, j_ref = role == 2 && tl < 12, j_tab = role == 3 && tl < H;
-        const float *cs = a.contact + (size_t)r * 4 * H;
-        float stv = 0.f, rfv = 0.f, s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-        if (j_state) stv = a.state[r * 24 + tl];
-        if (j_ref) rfv = a.reference[r * 24 + tl];
-        if (j_tab) { s0 = cs[tl]; s1 = cs[H + tl]; s2 = cs[2 * H + tl]; s3 = cs[3 * H + tl]; }
-        for (int p = t; p < P; p += T) {
-            const int k = p / H, n = p - k * H;
-            s_bt[NOISE_BLOCK * n + k] = a.costs_only ? 0.f : a.best[(size_t)r * P + p];
-            if (cem) s_sg[NOISE_BLOCK * n + k] = a.sigma ? a.sigma[(size_t)r * P + p] : 0.f;
-        }
-        if (j_state) s_state[tl] = stv;
-        if (j_ref) s_ref[tl] = rfv;
-        if (j_tab) {
-            const int n = tl;
-            s_reffz[n] = c.mg / (((s0 + s1) + s2) + s3);
-            s_st[8 * n + 0] = s0; s_st[8 * n + 1] = s1; s_st[8 * n + 2] = s2; s_st[8 * n + 3] = s3;
-            s_st[8 * n + 4] = s0 * (1.0f / 3.0f); s_st[8 * n + 5] = s1 * (1.0f / 3.0f);
-            s_st[8 * n + 6] = s2 * (1.0f / 3.0f); s_st[8 * n + 7] = s3 * (1.0f / 3.0f);
-        }
-    }
-    __syncthreads();
-
-    float feet[12], ref[12];
-#pragma unroll
-    for (int k = 0; k < 12; ++k) {
-        feet[k] = s_state[12 + k];
-        ref[k] = s_ref[k];
-    }
-
-    // ---- rollouts: pass q integrates rollouts base + 2 T q + t (A) and base + 2 T q + T + t (B)
-    for (int q0 = 0; q0 < cn; q0 += 2 * T) {
-        const int ja = q0 + t, jb = q0 + T + t;
-        const bool va = ja < cn, vb = jb < cn;
-        const int ia = base + ja, ib = base + jb;
-        v2 x[12];
-#pragma unroll
-        for (int k = 0; k < 12; ++k) x[k] = f2(s_state[k]);
-        v2 cost = f2(0.f);
-        const RowNoise rna = row_noise(c, va ? ia : 0), rnb = row_noise(c, vb ? ib : 0);
-        const float *ea = nullptr, *eb = nullptr;
-        if (MODE == 2) {
-            ea = a.eps + ((size_t)r * a.n + (va ? ia : base)) * P;
-            eb = a.eps + ((size_t)r * a.n + (vb ? ib : base)) * P;
-        }
-#pragma unroll 1
-        for (int n = 0; n < H; ++n) {
-            v2 f[NOISE_BLOCK];
-            const float4 b0 = *reinterpret_cast<const float4 *>(s_bt + NOISE_BLOCK * n);
-            const float4 b1 = *reinterpret_cast<const float4 *>(s_bt + NOISE_BLOCK * n + 4);
-            const float4 b2 = *reinterpret_cast<const float4 *>(s_bt + NOISE_BLOCK * n + 8);
-            const float bst[NOISE_BLOCK] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w};
-            if (MODE == 2) {
-#pragma unroll
-                for (int k = 0; k < NOISE_BLOCK; ++k) f[k] = vadd(f2(ea[k * H + n], eb[k * H + n]), bst[k]);
-            } else {
-                noise_block_pair<MODE == 0>(rna, rnb, a.key, n, robot, bst, f, [&](int k) { return s_sg[NOISE_BLOCK * n + k]; });
-            }
-            const float4 st4 = *reinterpret_cast<const float4 *>(s_st + 8 * n);
-            const float4 st34 = *reinterpret_cast<const float4 *>(s_st + 8 * n + 4);
-            const float st[4] = {st4.x, st4.y, st4.z, st4.w}, st3[4] = {st34.x, st34.y, st34.z, st34.w};
-            pair_step<QSPARSE>(c, x, feet, ref, f, st, st3, s_reffz[n], c.dts[n], cost);
-        }
-        if (!a.costs_only) {  // centroidal_nmpc_jax.py:686-687
-            cost.x = isnan(cost.x) ? 1000000.0f : cost.x;
-            cost.x = isinf(cost.x) ? 1000000.0f : cost.x;
-            cost.y = isnan(cost.y) ? 1000000.0f : cost.y;
-            cost.y = isinf(cost.y) ? 1000000.0f : cost.y;
-        }
-        if (va) {
-            a.costs[(size_t)r * a.n + ia] = cost.x;
-            s_cost[ja] = cost.x;
-        }
-        if (vb) {
-            a.costs[(size_t)r * a.n + ib] = cost.y;
-            s_cost[jb] = cost.y;
-        }
-    }
-    if (a.costs_only) return;
-    __syncthreads();
-
-    // ---- block partials {min, sum w, min, argmin} + V[P]
-    float *part = a.partials + ((size_t)r * a.nblk + blockIdx.x) * (PART_HDR + P);
     float bc = INFINITY;
     int bi = 0x7fffffff;
     for (int j = t; j < cn; j += T) argmin_combine(bc, bi, s_cost[j], base + j);
@@ -1029,13 +931,169 @@ __global__ void __launch_bounds__(T, 3) k_rollout_pair(const __grid_constant__ D
             part[PART_HDR + param_of(c, o / NOISE_BLOCK, o % NOISE_BLOCK)] = v;
         }
     }
-    if (!a.fused) return;
+}
+
+__host__ __device__ inline int pair_update_scratch_floats(int P, int N, int T) {
+    const int S = T / (P / NOISE_BLOCK) > 1 ? T / (P / NOISE_BLOCK) : 1;
+    return N + N + N / 2 + 1 + 64 + S * P;
+}
+__host__ __device__ inline int pair_update_smem_floats(int P, int N, int T, bool cem) {
+    return (cem ? 2 : 1) * P + pair_update_scratch_floats(P, N, T);
+}
+
+template <int MODE, int T, bool QSPARSE>
+__global__ void __launch_bounds__(T, 3) k_rollout_pair(const __grid_constant__ DevCfg c, const RolloutArgs a_,
+                                                       const __grid_constant__ InlineIn in) {
+    const RolloutArgs a = resolve_inputs(a_, in);
+    extern __shared__ __align__(16) float smem[];
+    const int P = c.P, H = c.H, t = threadIdx.x;
+    const bool cem = c.method == QPMPC_METHOD_CEM;
+    float *s_bt = smem;
+    float *s_sg = s_bt + P;
+    float *s_state = s_sg + (cem ? P : 0);
+    float *s_ref = s_state + 24;
+    float *s_st = s_ref + 12;
+    float *s_reffz = s_st + 8 * H;
+    float *s_cost = s_reffz + ((H + 3) & ~3);
+    const int chunk = a.chunk;
+    float *s_w = s_cost + chunk;
+    unsigned short *s_live = reinterpret_cast<unsigned short *>(s_w + chunk);
+    float *s_red = s_w + chunk + chunk / 2;
+    float *s_acc = s_red + 64;
+
+    const int r = blockIdx.y;
+    const int base = blockIdx.x * chunk;
+    const int cn = min(chunk, a.n - base);  // rollouts of this block
+    const uint32_t robot = (uint32_t)(r + a.robot_offset);
+
+    // ---- stage the robot's problem: best / sigma transposed to step-major order (value k of step n at [12 n + k]),
+    // state, reference, contact tables.  All global loads of a thread are issued before its first store.
+    {
+        const int role = t >> 5, tl = t & 31;
+        const bool j_state = role == 1 && tl < 24, j_ref = role == 2 && tl < 12, j_tab = role == 3 && tl < H;
+        const float *cs = a.contact + (size_t)r * 4 * H;
+        float stv = 0.f, rfv = 0.f, s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        if (j_state) stv = a.state[r * 24 + tl];
+        if (j_ref) rfv = a.reference[r * 24 + tl];
+        if (j_tab) { s0 = cs[tl]; s1 = cs[H + tl]; s2 = cs[2 * H + tl]; s3 = cs[3 * H + tl]; }
+        for (int p = t; p < P; p += T) {
+            const int k = p / H, n = p - k * H;
+            s_bt[NOISE_BLOCK * n + k] = a.costs_only ? 0.f : a.best[(size_t)r * P + p];
+            if (cem) s_sg[NOISE_BLOCK * n + k] = a.sigma ? a.sigma[(size_t)r * P + p] : 0.f;
+        }
+        if (j_state) s_state[tl] = stv;
+        if (j_ref) s_ref[tl] = rfv;
+        if (j_tab) {
+            const int n = tl;
+            s_reffz[n] = c.mg / (((s0 + s1) + s2) + s3);
+            s_st[8 * n + 0] = s0; s_st[8 * n + 1] = s1; s_st[8 * n + 2] = s2; s_st[8 * n + 3] = s3;
+            s_st[8 * n + 4] = s0 * (1.0f / 3.0f); s_st[8 * n + 5] = s1 * (1.0f / 3.0f);
+            s_st[8 * n + 6] = s2 * (1.0f / 3.0f); s_st[8 * n + 7] = s3 * (1.0f / 3.0f);
+        }
+    }
+    __syncthreads();
+
+    float feet[12], ref[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) {
+        feet[k] = s_state[12 + k];
+        ref[k] = s_ref[k];
+    }
+
+    // ---- rollouts: pass q integrates rollouts base + 2 T q + t (A) and base + 2 T q + T + t (B)
+    for (int q0 = 0; q0 < cn; q0 += 2 * T) {
+        const int ja = q0 + t, jb = q0 + T + t;
+        const bool va = ja < cn, vb = jb < cn;
+        const int ia = base + ja, ib = base + jb;
+        v2 x[12];
+#pragma unroll
+        for (int k = 0; k < 12; ++k) x[k] = f2(s_state[k]);
+        v2 cost = f2(0.f);
+        const RowNoise rna = row_noise(c, va ? ia : 0), rnb = row_noise(c, vb ? ib : 0);
+        const float *ea = nullptr, *eb = nullptr;
+        if (MODE == 2) {
+            ea = a.eps + ((size_t)r * a.n + (va ? ia : base)) * P;
+            eb = a.eps + ((size_t)r * a.n + (vb ? ib : base)) * P;
+        }
+#pragma unroll 1
+        for (int n = 0; n < H; ++n) {
+            v2 f[NOISE_BLOCK];
+            const float4 b0 = *reinterpret_cast<const float4 *>(s_bt + NOISE_BLOCK * n);
+            const float4 b1 = *reinterpret_cast<const float4 *>(s_bt + NOISE_BLOCK * n + 4);
+            const float4 b2 = *reinterpret_cast<const float4 *>(s_bt + NOISE_BLOCK * n + 8);
+            const float bst[NOISE_BLOCK] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w};
+            if (MODE == 2) {
+#pragma unroll
+                for (int k = 0; k < NOISE_BLOCK; ++k) f[k] = vadd(f2(ea[k * H + n], eb[k * H + n]), bst[k]);
+            } else {
+                noise_block_pair<MODE == 0>(rna, rnb, a.key, n, robot, bst, f, [&](int k) { return s_sg[NOISE_BLOCK * n + k]; });
+            }
+            const float4 st4 = *reinterpret_cast<const float4 *>(s_st + 8 * n);
+            const float4 st34 = *reinterpret_cast<const float4 *>(s_st + 8 * n + 4);
+            const float st[4] = {st4.x, st4.y, st4.z, st4.w}, st3[4] = {st34.x, st34.y, st34.z, st34.w};
+            pair_step<QSPARSE>(c, x, feet, ref, f, st, st3, s_reffz[n], c.dts[n], cost);
+        }
+        if (!a.costs_only) {  // centroidal_nmpc_jax.py:686-687
+            cost.x = isnan(cost.x) ? 1000000.0f : cost.x;
+            cost.x = isinf(cost.x) ? 1000000.0f : cost.x;
+            cost.y = isnan(cost.y) ? 1000000.0f : cost.y;
+            cost.y = isinf(cost.y) ? 1000000.0f : cost.y;
+        }
+        if (va) {
+            a.costs[(size_t)r * a.n + ia] = cost.x;
+            s_cost[ja] = cost.x;
+        }
+        if (vb) {
+            a.costs[(size_t)r * a.n + ib] = cost.y;
+            s_cost[jb] = cost.y;
+        }
+    }
+    if (a.costs_only || !a.fused) return;  // not fused: k_pair_update (one block per robot) does the rest from the costs
+    __syncthreads();
+    const PairSmem sm = {s_bt, s_sg, s_cost, s_w, s_red, s_acc, s_live};
+    pair_block_partials<MODE>(c, a, sm, r, base, cn, chunk, a.partials + ((size_t)r * a.nblk + blockIdx.x) * (PART_HDR + P));
     if (a.nblk > 1) {
         if (!last_block_of_robot(a.tickets + r, a.nblk)) return;
     } else {
         __syncthreads();  // the block's own partial, written above, is read back through L2 by finalize_robot
     }
     finalize_robot(c, resolve_inputs(a_, in), r, s_cost);
+}
+
+// Second launch of the throughput regime (launches many waves deep): ONE block per robot turns the robot's N costs into
+// the update -- block partials over all N rollouts, then finalize_robot with a single partial.  Splitting this off the
+// rollout kernel keeps three blocks per SM in the step loop all the time: with the fused epilogue a block spent ~30 %
+// of its residency between barriers (argmin, scan, live rows, merge, prediction) while holding a third of the SM's
+// warps (profiles/r5c_ncu_source_c5.txt: 31 % of the stall samples on 16 % of the instructions, outside the loop).
+template <int MODE>
+__global__ void __launch_bounds__(PAIR_T) k_pair_update(const __grid_constant__ DevCfg c, const RolloutArgs a_,
+                                                        const __grid_constant__ InlineIn in) {
+    RolloutArgs a = resolve_inputs(a_, in);
+    a.nblk = 1;  // this block is the robot's only partial
+    extern __shared__ __align__(16) float smem[];
+    const int P = c.P, H = c.H, t = threadIdx.x, r = blockIdx.x, N = a.n;
+    const bool cem = c.method == QPMPC_METHOD_CEM;
+    float *s_bt = smem;
+    float *s_sg = s_bt + P;
+    float *s_cost = s_sg + (cem ? P : 0);  // finalize_robot's scratch overlays everything from here on
+    float *s_w = s_cost + N;
+    unsigned short *s_live = reinterpret_cast<unsigned short *>(s_w + N);
+    float *s_red = s_w + N + N / 2 + 1;
+    float *s_acc = s_red + 64;
+    for (int p = t; p < P; p += PAIR_T) {
+        const int k = p / H, n = p - k * H;
+        s_bt[NOISE_BLOCK * n + k] = a.best[(size_t)r * P + p];
+        if (cem) s_sg[NOISE_BLOCK * n + k] = a.sigma ? a.sigma[(size_t)r * P + p] : 0.f;
+    }
+    const float *costs = a.costs + (size_t)r * N;
+    for (int j = t; j < N; j += PAIR_T) s_cost[j] = __ldcg(costs + j);
+    __syncthreads();
+    const PairSmem sm = {s_bt, s_sg, s_cost, s_w, s_red, s_acc, s_live};
+    pair_block_partials<MODE>(c, a, sm, r, 0, N, N, a.partials + (size_t)r * (PART_HDR + P));
+    __syncthreads();  // the partial, written above, is read back through L2 by finalize_robot
+    a = resolve_inputs(a_, in);
+    a.nblk = 1;
+    finalize_robot(c, a, r, s_cost);
 }
 
 // ---------------------------------------------------------------- quad rollout kernel (latency regime) ------
@@ -1433,7 +1491,7 @@ struct qpmpc_handle {
     int device;
     cudaStream_t stream;
     int num_sms;
-    rollout_fn fn128, fn64, fn32, fn_quad32, fn_quad72, fn_quad128, fn_pair[3];
+    rollout_fn fn128, fn64, fn32, fn_quad32, fn_quad72, fn_quad128, fn_pair[3], fn_pair_update[3];
     EnvSwitches env;
     size_t max_smem;
     // single-robot staging: one pinned input block, one pinned output block
@@ -1638,15 +1696,18 @@ extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     h->fn_pair[0] = qsparse ? k_rollout_pair<0, PAIR_T, true> : k_rollout_pair<0, PAIR_T, false>;
     h->fn_pair[1] = qsparse ? k_rollout_pair<1, PAIR_T, true> : k_rollout_pair<1, PAIR_T, false>;
     h->fn_pair[2] = qsparse ? k_rollout_pair<2, PAIR_T, true> : k_rollout_pair<2, PAIR_T, false>;
+    h->fn_pair_update[0] = k_pair_update<0>;
+    h->fn_pair_update[1] = k_pair_update<1>;
+    h->fn_pair_update[2] = k_pair_update<2>;
     cudaError_t e = cudaSuccess;
     size_t static_smem = 0;  // the kernels' own __shared__ variables come out of the same per-block budget
-    for (rollout_fn f : {h->fn128, h->fn64, h->fn32, h->fn_quad32, h->fn_quad72, h->fn_quad128, h->fn_pair[0], h->fn_pair[1], h->fn_pair[2]}) {
+    for (rollout_fn f : {h->fn128, h->fn64, h->fn32, h->fn_quad32, h->fn_quad72, h->fn_quad128, h->fn_pair[0], h->fn_pair[1], h->fn_pair[2], h->fn_pair_update[0], h->fn_pair_update[1], h->fn_pair_update[2]}) {
         cudaFuncAttributes fa;
         if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, (const void *)f);
         if (e == cudaSuccess && fa.sharedSizeBytes > static_smem) static_smem = fa.sharedSizeBytes;
     }
     h->max_smem -= static_smem;
-    for (rollout_fn f : {h->fn128, h->fn64, h->fn32, h->fn_quad32, h->fn_quad72, h->fn_quad128, h->fn_pair[0], h->fn_pair[1], h->fn_pair[2]})
+    for (rollout_fn f : {h->fn128, h->fn64, h->fn32, h->fn_quad32, h->fn_quad72, h->fn_quad128, h->fn_pair[0], h->fn_pair[1], h->fn_pair[2], h->fn_pair_update[0], h->fn_pair_update[1], h->fn_pair_update[2]})
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute((const void *)f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->max_smem);
     if (e != cudaSuccess) { delete h; return fail(QPMPC_E_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e)); }
@@ -1737,17 +1798,29 @@ static int launch_solve(qpmpc_handle *h, const qpmpc_batch &b, uint64_t seed, ui
     // Throughput regime (batched robots, many waves of blocks): the stand-alone k_finalize wins -- the arrival ticket
     // (fence + atomic round trip with the block's warps parked) and a last block that finalizes while two of its
     // SM's three slots wait cost more than one extra launch (C5: 3.09 -> 2.93 ms).  Latency regime: one launch.
-    // (the pair kernel with one block per robot has no ticket: it always finalizes in place)
+    // (the pair kernel with one block per robot has no ticket and overlaps its epilogue with the other blocks' step
+    // loops: fused 1.49 ms against 1.41 + 0.11 ms for rollouts + k_pair_update at C5)
     const bool deep = !pl.quad && !(pl.pair && nblk == 1) && (long long)R * nblk > 8LL * h->num_sms;
     const bool want_fused = h->env.fused < 0 ? !deep : h->env.fused != 0;
     ra.fused = finalize_smem_floats(P, nblk, K, pl.T) <= scratch && want_fused;
+    // pair kernel, not fused: k_pair_update (one block per robot over all N costs) needs them in shared memory
+    const bool cem_ = d.method == QPMPC_METHOD_CEM;
+    if (pl.pair && !ra.fused &&
+        ((size_t)pair_update_smem_floats(P, N, PAIR_T, cem_) * 4 > h->max_smem || N > 32768 ||
+         finalize_smem_floats(P, 1, K, PAIR_T) > pair_update_scratch_floats(P, N, PAIR_T)))
+        ra.fused = 1;
     ra.chunk = pl.chunk;
     if (h->profiling) CU(cudaEventRecord(h->ev[0], h->stream));
     pick_fn(h, pl, b.d_eps != nullptr)<<<dim3(nblk, R), pl.T, pl.smem, h->stream>>>(d, ra, in);
     CU(cudaGetLastError());
     if (h->profiling) CU(cudaEventRecord(h->ev[1], h->stream));
     h->launches += 1;
-    if (!ra.fused) {
+    if (!ra.fused && pl.pair) {
+        const int mode = b.d_eps != nullptr ? 2 : d.method == QPMPC_METHOD_MPPI ? 0 : 1;
+        h->fn_pair_update[mode]<<<R, PAIR_T, (size_t)pair_update_smem_floats(P, N, PAIR_T, cem_) * 4, h->stream>>>(d, ra, in);
+        CU(cudaGetLastError());
+        h->launches += 1;
+    } else if (!ra.fused) {
         // one block per robot: 512 threads when there are many rollout blocks to merge (single robot), 128 otherwise
         const int fin_threads = nblk > 16 ? FIN_THREADS_MAX : 128;
         const size_t fsmem = (size_t)finalize_smem_floats(P, nblk, K, fin_threads) * 4;
