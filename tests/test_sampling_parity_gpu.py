@@ -13,8 +13,8 @@ torch = pytest.importorskip("torch")
 
 from oracle import srbd_oracle as so  # noqa: E402  (checker only)
 from quadruped_pympc_tamols_b200 import _cabi  # noqa: E402
-from tests.util import (fixture_kwargs, oracle_tail, rel_err, sampling_fixtures, softmin_tolerance,  # noqa: E402
-                        softmin_update_f64)
+from tests.util import (fixture_kwargs, oracle_tail, record_parity, rel_err, sampling_fixtures,  # noqa: E402
+                        softmin_tolerance, softmin_update_f64)
 
 pytestmark = pytest.mark.gpu
 
@@ -174,6 +174,8 @@ def test_philox_solve_matches_oracle_on_same_noise(robot, gait, method, param, g
         r = h.solve(st, ref, seq, best, seed=42, offset=it, timing=timing, nominal_freq=nominal, optimize_swing=oswing,
                     sigma_in=sigma if method == "cem_mppi" else None)
         o = so.solve(ocfg, method, st, ref, seq, best, eps, timing=timing, freqs=freqs, fast=False)
+        if n == 10000:  # the BASELINE configs C1..C3 at full size go into the terminal summary (tests/conftest.py)
+            record_parity(f"{robot} {gait} {method} {param}{' ga' if ga else ''} N={n} it{it} [{kernel}:{h.last_kernel}]", method, r, o, eps)
         compare(r, o, method, tag=f"it{it}", eps=eps, best_in=best,
                 tail=oracle_tail(so, ocfg, st, ref, seq, r["best"], timing=timing))
         # the supplied-noise path must agree with the in-kernel path bit for bit on the costs.  (The packed pair kernel
