@@ -34,6 +34,9 @@ namespace tamols {
 constexpr int TW = 32, HALO = 4;
 constexpr int BW = TW + 2 * HALO;  // 40 cells per staged row; staged rows = TH + 2 * HALO
 constexpr int THREADS = 256;
+#ifndef TAMOLS_EXACT_LOOKUPS
+#define TAMOLS_EXACT_LOOKUPS 0  // 1: every stencil look-up through the per-point float64 nearest-cell computation (A/B)
+#endif
 
 struct Partial {
     double score;
@@ -67,13 +70,10 @@ struct Ctx {
     int pitch;
 };
 
+// height of map cell (ir, ic), clamped to the leg's window (the KD-tree upstream only holds the leg's own cells, so the
+// nearest neighbour of a point outside is the nearest border cell), + the sensor offset of FastHeightMap.get_height
 template <typename HT>
-__device__ __forceinline__ double lookup(const Args &a, const Ctx &c, const HT *s_box, double x, double y) {
-    // FastHeightMap.get_height (:31-35): nearest cell of the leg's map + 0.02
-    const double dx = x - c.ox, dy = y - c.oy;
-    const double gr = dx * c.arx + dy * c.ary;
-    const double gc = dx * c.acx + dy * c.acy;
-    int ir = __double2int_rn(gr), ic = __double2int_rn(gc);
+__device__ __forceinline__ double cell_height(const Args &a, const Ctx &c, const HT *s_box, int ir, int ic) {
     ir = min(max(ir, c.r0), c.r0 + c.nr - 1);
     ic = min(max(ic, c.c0), c.c0 + c.nc - 1);
     const int lr = ir - c.br, lc = ic - c.bc;
@@ -84,6 +84,27 @@ __device__ __forceinline__ double lookup(const Args &a, const Ctx &c, const HT *
         h = __ldg(static_cast<const HT *>(a.heights) + c.map_base + (long long)ir * c.pitch + ic);
     return (double)h + a.p.sensor_offset;
 }
+
+template <typename HT>
+__device__ __forceinline__ double lookup(const Args &a, const Ctx &c, const HT *s_box, double x, double y) {
+    // FastHeightMap.get_height (:31-35): nearest cell of the leg's map + 0.02
+    const double dx = x - c.ox, dy = y - c.oy;
+    const double gr = dx * c.arx + dy * c.ary;
+    const double gc = dx * c.acx + dy * c.acy;
+    return cell_height<HT>(a, c, s_box, __double2int_rn(gr), __double2int_rn(gc));
+}
+
+// The 3 x 3 patch of _compute_roughness_cost / _compute_edge_cost samples the map at the candidate + (i, k) * delta.
+// A candidate IS a cell centre, so in grid coordinates those nine points are the candidate's cell (R, C) plus nine
+// offsets that are the same for every candidate of the job: their nearest cells are (R + dr, C + dc) with nine integer
+// pairs computed once per block -- no float64 arithmetic per lookup (it was 4 DMUL + 2 DADD + 2 F2I for each of the 14
+// stencil look-ups of a candidate, 40 % of the kernel's FP64 instructions).  Exactly the cells the per-point
+// computation finds unless an offset sits within 1e-6 cells of a rounding tie (delta = half a cell, or such a yaw):
+// the block then keeps the per-point path (`exact`).
+struct Stencil {
+    int dr[9], dc[9];
+    int exact;
+};
 
 __device__ __forceinline__ void candidate_xy(const Args &a, const Ctx &c, int R, int C, double &x, double &y) {
     if (a.xy) {  // coordinates as stored by the sensor (:243)
@@ -96,14 +117,18 @@ __device__ __forceinline__ void candidate_xy(const Args &a, const Ctx &c, int R,
     }
 }
 
-// candidate construction (:188-196) for map cell (R, C) and _check_kinematic_feasibility (:375-395), the cheap first
-// gate of _compute_tamols_score (:287-290): most cells of a window fail it (they lie outside the leg's reach)
-template <typename HT>
-__device__ __forceinline__ bool candidate_reachable(const Args &a, const Ctx &c, const tamols_leg_job &j, const HT *s_box,
-                                                    int R, int C, double cand[3]) {
-    const tamols_params &p = a.p;
+// candidate construction (:188-196) for map cell (R, C): the cell's own coordinates and its own height (the nearest
+// cell of a cell centre is the cell) + the foot clearance
+template <typename HT, bool EXACT>
+__device__ __forceinline__ void candidate_point(const Args &a, const Ctx &c, const HT *s_box, int R, int C, double cand[3]) {
     candidate_xy(a, c, R, C, cand[0], cand[1]);
-    cand[2] = lookup(a, c, s_box, cand[0], cand[1]) + p.foot_clearance;
+    cand[2] = (EXACT ? lookup<HT>(a, c, s_box, cand[0], cand[1]) : cell_height<HT>(a, c, s_box, R, C)) + a.p.foot_clearance;
+}
+
+// _check_kinematic_feasibility (:375-395), the cheap first gate of _compute_tamols_score (:287-290): most cells of a
+// window fail it (they lie outside the leg's reach)
+__device__ __forceinline__ bool candidate_reachable(const Args &a, const Ctx &c, const tamols_leg_job &j, const double cand[3]) {
+    const tamols_params &p = a.p;
     double d0 = cand[0] - j.hip[0], d1 = cand[1] - j.hip[1], d2 = cand[2] - j.hip[2];
     const double dist_td = sqrt((d0 * d0 + d1 * d1) + d2 * d2);
     if (!(p.l_min <= dist_td && dist_td <= p.l_max)) return false;
@@ -118,9 +143,9 @@ __device__ __forceinline__ bool candidate_reachable(const Args &a, const Ctx &c,
 }
 
 // the rest of _compute_tamols_score (:291-373) for a reachable candidate
-template <typename HT>
+template <typename HT, bool EXACT>
 __device__ double score_reachable(const Args &a, const Ctx &c, const tamols_leg_job &j, const HT *s_box,
-                                  const double cand[3]) {
+                                  const double cand[3], int R, int C, const Stencil &sten) {
     const tamols_params &p = a.p;
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
     // _check_leg_collision (:397-420)
@@ -140,7 +165,11 @@ __device__ double score_reachable(const Args &a, const Ctx &c, const tamols_leg_
     for (int i = -1; i <= 1; ++i)
 #pragma unroll
         for (int k = -1; k <= 1; ++k)
-            h[(i + 1) * 3 + (k + 1)] = lookup(a, c, s_box, cand[0] + (double)i * d, cand[1] + (double)k * d);
+        {
+            const int q = (i + 1) * 3 + (k + 1);
+            h[q] = EXACT ? lookup(a, c, s_box, cand[0] + (double)i * d, cand[1] + (double)k * d)
+                         : cell_height<HT>(a, c, s_box, R + sten.dr[q], C + sten.dc[q]);
+        }
     double edge;
     {
         const double gx = fabs(h[2 * 3 + 1] - h[0 * 3 + 1]) / (2.0 * d);
@@ -162,19 +191,23 @@ __device__ double score_reachable(const Args &a, const Ctx &c, const tamols_leg_
             }
         const double s2 = 6.0 * (d * d);
         const double pa = sxh / s2, pb = syh / s2, pc = sh / 9.0;
-        double res[9], mean = 0.0;
+        // residuals are evaluated twice (mean, then spread) instead of being kept: nine fewer float64 values live
+        // across the loop, the same operations in the same order
+        double mean = 0.0;
+#pragma unroll
+        for (int i = -1; i <= 1; ++i)
+#pragma unroll
+            for (int k = -1; k <= 1; ++k)
+                mean += h[(i + 1) * 3 + (k + 1)] - ((((double)i * d) * pa + ((double)k * d) * pb) + pc);
+        mean /= 9.0;
+        double var = 0.0;
 #pragma unroll
         for (int i = -1; i <= 1; ++i)
 #pragma unroll
             for (int k = -1; k <= 1; ++k) {
-                const int q = (i + 1) * 3 + (k + 1);
-                res[q] = h[q] - ((((double)i * d) * pa + ((double)k * d) * pb) + pc);
-                mean += res[q];
+                const double res = h[(i + 1) * 3 + (k + 1)] - ((((double)i * d) * pa + ((double)k * d) * pb) + pc);
+                var += (res - mean) * (res - mean);
             }
-        mean /= 9.0;
-        double var = 0.0;
-#pragma unroll
-        for (int q = 0; q < 9; ++q) var += (res[q] - mean) * (res[q] - mean);
         rough = var / 9.0;
     }
     // deviation from the seed (:344-345)
@@ -250,6 +283,56 @@ __device__ __forceinline__ void argmin_combine(double &s, int &i, double os, int
     }
 }
 
+// The two passes over one tile (gate, then full score of the survivors), compiled once per look-up flavour.
+template <typename HT, bool EXACT, int TH>
+__device__ __forceinline__ void tile_passes(const Args &a, const Ctx &c, const tamols_leg_job &j, const HT *s_box,
+                                            const Stencil &sten, unsigned short *s_list, int *s_nlist, int job, int tile_r,
+                                            int tile_c, double &s, int &idx, int &nfin) {
+    constexpr int CPT = TW * TH / THREADS;
+    const int t = threadIdx.x;
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+    // ---- pass 1: every cell of the tile through the reachability gate; survivors are compacted into s_list so that
+    // pass 2 (collision line, edge, roughness, ...; ~10x the work) runs on full warps instead of a ragged annulus.
+    // The compaction order is arbitrary; the result is not: the reduction below is a lexicographic (score, index) min.
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) {
+        const int e = k * THREADS + t;
+        const int r = tile_r * TH + e / TW, q = tile_c * TW + e % TW;
+        bool reach = false;
+        if (r < c.nr && q < c.nc) {
+            double cand[3];
+            candidate_point<HT, EXACT>(a, c, s_box, c.r0 + r, c.c0 + q, cand);
+            reach = candidate_reachable(a, c, j, cand);
+            if (!reach && a.scores) a.scores[(long long)job * a.scores_stride + r * c.nc + q] = inf;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, reach);
+        int base = 0;
+        if ((t & 31) == 0 && m) base = atomicAdd(s_nlist, __popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (reach) s_list[base + __popc(m & ((1u << (t & 31)) - 1u))] = (unsigned short)e;
+    }
+    __syncthreads();
+    // ---- pass 2: full score of the reachable candidates
+    s = inf;
+    idx = 0x7fffffff;
+    nfin = 0;
+    const int nlist = *s_nlist;
+    for (int i = t; i < nlist; i += THREADS) {
+        const int e = s_list[i];
+        const int r = tile_r * TH + e / TW, q = tile_c * TW + e % TW;
+        double cand[3];
+        candidate_point<HT, EXACT>(a, c, s_box, c.r0 + r, c.c0 + q, cand);
+        double sc = score_reachable<HT, EXACT>(a, c, j, s_box, cand, c.r0 + r, c.c0 + q, sten);
+        const int ci = r * c.nc + q;
+        if (a.scores) a.scores[(long long)job * a.scores_stride + ci] = sc;
+        if (sc < inf) {  // NaN is never selected by the reference's `score < best_score`
+            ++nfin;
+            argmin_combine(s, idx, sc, ci);
+        }
+    }
+
+}
+
 // ---------------------------------------------------------------- the kernel ---------------------------------
 struct GridInv {
     double arx, ary, acx, acy;
@@ -257,11 +340,12 @@ struct GridInv {
 
 template <typename HT, bool USE_TMA, int TH>
 __global__ void __launch_bounds__(THREADS, TH == 32 ? 4 : 2) k_tamols_score(const __grid_constant__ CUtensorMap tmap, const Args a) {
-    constexpr int BH = TH + 2 * HALO, CPT = TW * TH / THREADS;
+    constexpr int BH = TH + 2 * HALO;
     __shared__ __align__(128) HT s_box[BH * BW];
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ __align__(8) tamols_leg_job s_job;  // the job record, read once from global memory
     __shared__ GridInv s_inv;
+    __shared__ Stencil s_sten;
     __shared__ unsigned short s_list[TW * TH];     // tile-local indices of the reachable candidates
     __shared__ int s_nlist;
     __shared__ double s_rs[THREADS / 32];
@@ -314,48 +398,28 @@ __global__ void __launch_bounds__(THREADS, TH == 32 ? 4 : 2) k_tamols_score(cons
         const double r2 = c.rax * c.rax + c.ray * c.ray, c2 = c.cax * c.cax + c.cay * c.cay;
         s_inv.arx = c.rax / r2; s_inv.ary = c.ray / r2; s_inv.acx = c.cax / c2; s_inv.acy = c.cay / c2;
     }
-    __syncthreads();  // s_bar initialised (TMA) / s_box written (plain) / s_inv written
+    if (t >= 64 && t < 73) {  // nearest-cell offsets of the nine patch points, once per block (Stencil)
+        const int q = t - 64, i = q / 3 - 1, k = q % 3 - 1;
+        const double r2 = c.rax * c.rax + c.ray * c.ray, c2 = c.cax * c.cax + c.cay * c.cay;
+        const double dx = (double)i * a.p.gradient_delta, dy = (double)k * a.p.gradient_delta;
+        const double gr = dx * (c.rax / r2) + dy * (c.ray / r2), gc = dx * (c.cax / c2) + dy * (c.cay / c2);
+        const int ir = __double2int_rn(gr), ic = __double2int_rn(gc);
+        s_sten.dr[q] = ir;
+        s_sten.dc[q] = ic;
+        const bool tie = fabs(fabs(gr - (double)ir) - 0.5) < 1e-6 || fabs(fabs(gc - (double)ic) - 0.5) < 1e-6;
+        const unsigned any = __ballot_sync(0x1ffu, tie);
+        if (q == 0) s_sten.exact = (any != 0u || TAMOLS_EXACT_LOOKUPS) ? 1 : 0;
+    }
+    __syncthreads();  // s_bar initialised (TMA) / s_box written (plain) / s_inv, s_sten written
     c.arx = s_inv.arx; c.ary = s_inv.ary; c.acx = s_inv.acx; c.acy = s_inv.acy;
+    const bool exact = s_sten.exact != 0;
     if (USE_TMA) mbar_wait(&s_bar, 0);
 
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
-    // ---- pass 1: every cell of the tile through the reachability gate; survivors are compacted into s_list so that
-    // pass 2 (collision line, edge, roughness, ...; ~10x the work) runs on full warps instead of a ragged annulus.
-    // The compaction order is arbitrary; the result is not: the reduction below is a lexicographic (score, index) min.
-#pragma unroll
-    for (int k = 0; k < CPT; ++k) {
-        const int e = k * THREADS + t;
-        const int r = tile_r * TH + e / TW, q = tile_c * TW + e % TW;
-        bool reach = false;
-        if (r < c.nr && q < c.nc) {
-            double cand[3];
-            reach = candidate_reachable<HT>(a, c, j, s_box, c.r0 + r, c.c0 + q, cand);
-            if (!reach && a.scores) a.scores[(long long)job * a.scores_stride + r * c.nc + q] = inf;
-        }
-        const unsigned m = __ballot_sync(0xffffffffu, reach);
-        int base = 0;
-        if ((t & 31) == 0 && m) base = atomicAdd(&s_nlist, __popc(m));
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (reach) s_list[base + __popc(m & ((1u << (t & 31)) - 1u))] = (unsigned short)e;
-    }
-    __syncthreads();
-    // ---- pass 2: full score of the reachable candidates
-    double s = inf;
-    int idx = 0x7fffffff, nfin = 0;
-    const int nlist = s_nlist;
-    for (int i = t; i < nlist; i += THREADS) {
-        const int e = s_list[i];
-        const int r = tile_r * TH + e / TW, q = tile_c * TW + e % TW;
-        double cand[3];
-        candidate_reachable<HT>(a, c, j, s_box, c.r0 + r, c.c0 + q, cand);
-        double sc = score_reachable<HT>(a, c, j, s_box, cand);
-        const int ci = r * c.nc + q;
-        if (a.scores) a.scores[(long long)job * a.scores_stride + ci] = sc;
-        if (sc < inf) {  // NaN is never selected by the reference's `score < best_score`
-            ++nfin;
-            argmin_combine(s, idx, sc, ci);
-        }
-    }
+    double s;
+    int idx, nfin;
+    if (exact) tile_passes<HT, true, TH>(a, c, j, s_box, s_sten, s_list, &s_nlist, job, tile_r, tile_c, s, idx, nfin);
+    else tile_passes<HT, false, TH>(a, c, j, s_box, s_sten, s_list, &s_nlist, job, tile_r, tile_c, s, idx, nfin);
 
     // ---- block reduction: lexicographic (score, index) minimum = first minimum in row-major order
 #pragma unroll
@@ -598,6 +662,8 @@ struct tamols_handle {
     std::vector<double> sensor_heights, sensor_xy;  // host scratch of tamols_score_sensors
     std::vector<tamols_leg_job> sensor_jobs;
     unsigned int seq;
+    int env_tile_rows;  // TAMOLS_TILE_ROWS (0 = automatic) and TAMOLS_ZEROCOPY, read from the environment once per
+    int env_zerocopy;   // handle: a getenv per call is measurable on a 30 us path
 };
 
 extern "C" const char *tamols_last_error(void) { return g_terr.c_str(); }
@@ -651,6 +717,12 @@ extern "C" int tamols_create(const tamols_params *params, int32_t device, int32_
     }
     memset(h->m_out, 0, 2 * (size_t)max_jobs * sizeof(tamols_result) + 64);  // sequence 0 = nothing published yet
     h->seq = 0;
+    h->env_tile_rows = 0;
+    if (const char *e = getenv("TAMOLS_TILE_ROWS")) h->env_tile_rows = atoi(e) == 32 ? 32 : 8;
+    {
+        const char *zc = getenv("TAMOLS_ZEROCOPY");
+        h->env_zerocopy = !(zc && zc[0] == '0');
+    }
     *out = h;
     return TAMOLS_OK;
 }
@@ -714,7 +786,7 @@ static int launch_score(tamols_handle *h, const void *d_heights, int dtype, int 
     // a window of at most 256 candidates that fits one 32 x 32 tile (one robot's 13 x 7 sensor maps): ONE tile per job,
     // which finishes without the partial / ticket / merge round trips
     if (max_nr <= 32 && max_nc <= TW && max_nr * max_nc <= THREADS && max_nr > 8) th = 32;
-    if (const char *e = getenv("TAMOLS_TILE_ROWS")) th = atoi(e) == 32 ? 32 : 8;
+    if (h->env_tile_rows) th = h->env_tile_rows;
     const int max_tiles = ((max_nr + th - 1) / th) * ((max_nc + TW - 1) / TW);
     const size_t need = (size_t)n_jobs * max_tiles;
     if (need > h->partial_cap) {
@@ -820,8 +892,7 @@ extern "C" int tamols_score_host(tamols_handle *h, const double *heights, int32_
     // Without per-candidate scores (the product call) the results go straight into a mapped pinned block and the last
     // finished job raises a flag there that the host spins on: no D2H copy command, no stream-synchronise wake-up.
     // With scores (tests) or TAMOLS_ZEROCOPY=0: device results + one D2H copy + cudaStreamSynchronize.
-    const char *zc = getenv("TAMOLS_ZEROCOPY");
-    const bool mapped_out = !scores && !(zc && zc[0] == '0');
+    const bool mapped_out = !scores && h->env_zerocopy;
     if (mapped_out) {
         volatile unsigned long long *pairs = reinterpret_cast<volatile unsigned long long *>(h->m_out);
         unsigned int seq = ++h->seq;
