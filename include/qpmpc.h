@@ -218,6 +218,33 @@ int qpmpc_gait_run(qpmpc_handle *h, const qpmpc_gait_batch *g, double dt);
 int qpmpc_stance_torques(qpmpc_handle *h, int32_t num_robots, const qpmpc_result *d_result, const double *d_feet_jac,
                          double *d_tau);
 
+/* ---- SURVEY.md 8(f) N4, second half: dataset rows for a batch of robots, packed on the device.
+ * Replaces MatLogger.record_step (simulation/simulation.py:241-304) looped in Python over robots: one float64 row
+ *   [time, observable 0 flattened, observable 1 flattened, ...]
+ * per robot and step, the observables being the controller's (quadruped_pympc_wrapper.py:205-243: nmpc_GRFs from the
+ * qpmpc_result records, reference height / angles / feet from the reference rows, phase signal from the gait clocks,
+ * ...) and whatever state arrays the simulator side keeps on the device.  Each observable is a SEGMENT: a device array
+ * with one row per robot (any of four element types, any row stride -- e.g. the grf field of qpmpc_result with a stride
+ * of sizeof(qpmpc_result) / 4), flattened row-major and cast to float64 exactly like MatLogger._flatten_value (:119-148).
+ * d_rows [num_robots, num_columns] receives the rows of this step; the caller lays the steps out as it likes (the
+ * Python writer uses [steps, robots, columns] and saves MatLogger's {header, data} table per robot).
+ * Asynchronous on the handle's stream. */
+#define QPMPC_MAX_OBS_SEGMENTS 24
+enum { QPMPC_OBS_F32 = 0, QPMPC_OBS_F64 = 1, QPMPC_OBS_I32 = 2, QPMPC_OBS_U8 = 3 };
+typedef struct qpmpc_obs_segment {
+    const void *d_src;    /* device array, one row per robot */
+    int64_t robot_stride; /* elements between the rows of consecutive robots */
+    int32_t dtype;        /* QPMPC_OBS_* */
+    int32_t count;        /* values per robot = columns this observable contributes */
+} qpmpc_obs_segment;
+typedef struct qpmpc_obs_layout {
+    int32_t num_segments;
+    int32_t num_columns;  /* 1 (time) + sum of the segment counts (checked) */
+    qpmpc_obs_segment seg[QPMPC_MAX_OBS_SEGMENTS];
+} qpmpc_obs_layout;
+int qpmpc_pack_observables(qpmpc_handle *h, const qpmpc_obs_layout *layout, int32_t num_robots, double time,
+                           double *d_rows);
+
 #ifdef __cplusplus
 }
 #endif

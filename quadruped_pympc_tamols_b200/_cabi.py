@@ -66,10 +66,22 @@ class QpmpcGaitBatch(C.Structure):  # include/qpmpc.h: qpmpc_gait_batch
                 ("d_full_stance", C.c_void_p), ("step_dts", C.c_double * MAX_H), ("d_contact", C.c_void_p)]
 
 
+QPMPC_MAX_OBS_SEGMENTS = 24
+OBS_DTYPE = {"float32": 0, "float64": 1, "int32": 2, "uint8": 3}
+
+
+class QpmpcObsSegment(C.Structure):  # include/qpmpc.h: qpmpc_obs_segment
+    _fields_ = [("d_src", C.c_void_p), ("robot_stride", C.c_int64), ("dtype", C.c_int32), ("count", C.c_int32)]
+
+
+class QpmpcObsLayout(C.Structure):  # include/qpmpc.h: qpmpc_obs_layout
+    _fields_ = [("num_segments", C.c_int32), ("num_columns", C.c_int32), ("seg", QpmpcObsSegment * QPMPC_MAX_OBS_SEGMENTS)]
+
+
 EXPORTS = ["qpmpc_create", "qpmpc_destroy", "qpmpc_num_params", "qpmpc_last_error", "qpmpc_version", "qpmpc_stream",
            "qpmpc_launch_count", "qpmpc_last_kernel", "qpmpc_solve", "qpmpc_solve_iterated", "qpmpc_copy_costs", "qpmpc_solve_batched", "qpmpc_rollout_costs", "qpmpc_generate_noise", "qpmpc_set_profiling", "qpmpc_profile_last",
            "qpmpc_measure_fp32_peak", "qpmpc_contact_sequences", "qpmpc_gait_run",
-           "qpmpc_stance_torques"]
+           "qpmpc_stance_torques", "qpmpc_pack_observables"]
 
 
 def build(force=False):
@@ -118,6 +130,7 @@ def lib():
         L.qpmpc_contact_sequences.argtypes = [vp, C.POINTER(QpmpcGaitBatch)]
         L.qpmpc_gait_run.argtypes = [vp, C.POINTER(QpmpcGaitBatch), C.c_double]
         L.qpmpc_stance_torques.argtypes = [vp, C.c_int32, vp, vp, vp]
+        L.qpmpc_pack_observables.argtypes = [vp, C.POINTER(QpmpcObsLayout), C.c_int32, C.c_double, vp]
         _LIB = L
     return _LIB
 
@@ -344,6 +357,10 @@ class Handle:
     def stance_torques(self, num_robots, d_result, d_feet_jac, d_tau):
         """tau[R,4,3] = -J^T f from the device result records (wb_interface.py:368-371); device addresses."""
         check(lib().qpmpc_stance_torques(self._h, int(num_robots), d_result, d_feet_jac, d_tau))
+
+    def pack_observables(self, layout: QpmpcObsLayout, num_robots, time, d_rows):
+        """One float64 dataset row per robot for this step (MatLogger.record_step, simulation.py:241-304); device addresses."""
+        check(lib().qpmpc_pack_observables(self._h, C.byref(layout), int(num_robots), float(time), d_rows))
 
     def rollout_costs(self, state, reference, contact_sequence, d_params, n, d_costs, timing=None, d_freqs=None):
         st, rf, cs = _f32(state).reshape(24), _f32(reference).reshape(24), _f32(contact_sequence)

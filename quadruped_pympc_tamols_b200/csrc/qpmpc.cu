@@ -2191,6 +2191,54 @@ extern "C" int qpmpc_stance_torques(qpmpc_handle *h, int32_t num_robots, const q
     return QPMPC_OK;
 }
 
+// dataset rows (MatLogger.record_step, simulation/simulation.py:241-304) for a batch of robots.  One
+// thread per (robot, column): column 0 is the time, the others are gathered from the observables' device arrays and
+// widened to float64 (exact for every source type).
+namespace qp {
+__global__ void k_pack_observables(const __grid_constant__ qpmpc_obs_layout L, int num_robots, double time, double *rows) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)num_robots * L.num_columns) return;
+    const int r = (int)(idx / L.num_columns);
+    int col = (int)(idx - (long long)r * L.num_columns);
+    double v = time;
+    if (col > 0) {
+        --col;
+        int s = 0;
+        while (col >= L.seg[s].count) col -= L.seg[s++].count;
+        const qpmpc_obs_segment &g = L.seg[s];
+        const long long e = (long long)r * g.robot_stride + col;
+        v = g.dtype == QPMPC_OBS_F32   ? (double)static_cast<const float *>(g.d_src)[e]
+            : g.dtype == QPMPC_OBS_F64 ? static_cast<const double *>(g.d_src)[e]
+            : g.dtype == QPMPC_OBS_I32 ? (double)static_cast<const int32_t *>(g.d_src)[e]
+                                       : (double)static_cast<const uint8_t *>(g.d_src)[e];
+    }
+    rows[idx] = v;
+}
+}  // namespace qp
+
+extern "C" int qpmpc_pack_observables(qpmpc_handle *h, const qpmpc_obs_layout *layout, int32_t num_robots, double time,
+                                      double *d_rows) {
+    if (!h || !layout || !d_rows) return fail(QPMPC_E_ARG, "null argument");
+    if (num_robots < 1) return fail(QPMPC_E_ARG, "num_robots must be >= 1");
+    if (layout->num_segments < 0 || layout->num_segments > QPMPC_MAX_OBS_SEGMENTS)
+        return fail(QPMPC_E_ARG, "num_segments out of range [0, 24]");
+    int cols = 1;
+    for (int k = 0; k < layout->num_segments; ++k) {
+        const qpmpc_obs_segment &g = layout->seg[k];
+        if (!g.d_src || g.count < 1 || g.dtype < 0 || g.dtype > QPMPC_OBS_U8)
+            return fail(QPMPC_E_ARG, "observable segment " + std::to_string(k) + ": null source, empty or unknown dtype");
+        cols += g.count;
+    }
+    if (cols != layout->num_columns) return fail(QPMPC_E_ARG, "num_columns must be 1 + the sum of the segment counts");
+    CU(cudaSetDevice(h->device));
+    const long long total = (long long)num_robots * cols;
+    const int threads = 256;
+    k_pack_observables<<<(unsigned)((total + threads - 1) / threads), threads, 0, h->stream>>>(*layout, num_robots, time, d_rows);
+    CU(cudaGetLastError());
+    h->launches += 1;
+    return QPMPC_OK;
+}
+
 extern "C" int qpmpc_gait_run(qpmpc_handle *h, const qpmpc_gait_batch *g, double dt) {
     if (int rc = gait_check(h, g)) return rc;
     CU(cudaSetDevice(h->device));

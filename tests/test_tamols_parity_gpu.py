@@ -162,12 +162,14 @@ def test_host_call_mapped_results_equal_copied_results(tc, monkeypatch):
     rng = np.random.default_rng(2)
     scenes = [sy.robot_scene("hyqreal1", rng, "stepping_stones") for _ in range(3)]
     p = tc.make_params(sy.tamols_params_for("hyqreal1"), "hyqreal1")
+    monkeypatch.delenv("TAMOLS_ZEROCOPY", raising=False)
     h = tc.Handle(p, max_jobs=4)
+    monkeypatch.setenv("TAMOLS_ZEROCOPY", "0")  # read once per handle (tamols_create)
+    h0 = tc.Handle(p, max_jobs=4)
     for s in scenes:
-        monkeypatch.delenv("TAMOLS_ZEROCOPY", raising=False)
         a, _ = h.score_host(s["heights"], s["jobs"], xy=s["xy"])
         b, _ = h.score_host(s["heights"], s["jobs"], xy=s["xy"], want_scores=True)
-        monkeypatch.setenv("TAMOLS_ZEROCOPY", "0")
-        c, _ = h.score_host(s["heights"], s["jobs"], xy=s["xy"])
+        c, _ = h0.score_host(s["heights"], s["jobs"], xy=s["xy"])
         assert a.tobytes() == b.tobytes() == c.tobytes()
     h.close()
+    h0.close()
