@@ -28,6 +28,14 @@
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
+
+/* -DORACLE_ALT_TRIG: a second implementation of the transcendentals (double-precision libm rounded to float, i.e.
+ * correctly rounded in practice) for tools/fp32_envelope.py, which measures how far two faithful float32
+ * implementations of the reference drift apart.  Never defined in the checker or the timed builds. */
+#ifdef ORACLE_ALT_TRIG
+#define sinf(x) ((float)sin((double)(x)))
+#define cosf(x) ((float)cos((double)(x)))
+#endif
 #ifdef _OPENMP
 #include <omp.h>
 #endif

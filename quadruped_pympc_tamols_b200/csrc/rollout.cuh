@@ -10,8 +10,8 @@
 //   controllers/sampling/centroidal_nmpc_jax_gait_adaptive.py:326-501, helpers/periodic_gait_generator_jax.py:68-89.
 // Deviations from the reference's operation order, all at float32 round-off level (DESIGN.md "Numerics"):
 //   * the Euler-rate division and the per-sample-gait chunk position use the SFU reciprocal (2 ulp);
-//   * fd's second multiplication of the already masked forces by the contact flag is dropped for fx, fy (an exact
-//     identity there) and kept for fz (a non-zero grf_min makes the clamp lift a swing leg's fz);
+//   * fd's second multiplication of the already masked forces by the contact flag is explicit for fz (a non-zero
+//     grf_min makes the clamp lift a swing leg's fz) and folded into the friction limit for fx, fy (shape_leg);
 //   * sin/cos are sincos_fast (srbd.cuh): the library sincosf's accuracy class (1.6 ulp) without its slow-path
 //     branch; the SFU versions (5e-7 absolute) moved costs by ~1e-6 relative, which the temperature-1 softmin of
 //     the update amplifies beyond the 1e-3 bar.
@@ -26,7 +26,9 @@ __device__ __forceinline__ void shape_leg(const DevCfg &c, float f[3], float st,
     float fz = (ref_fz + f[2]) * st;
     float fx = f[0] * st3, fy = f[1] * st3;
     fz = fminf(fmaxf(fz, c.fzmin), c.fzmax);
-    const float lim = c.mu * fz;
+    // friction limit masked by the contact flag: a swing leg clamps to [-0, 0], which is what fd's second multiplication
+    // of fx, fy by the flag gives upstream -- also for a NaN parameter or a negative grf_min (lim = mu fz < 0 there)
+    const float lim = (c.mu * st) * fz;
     f[0] = fminf(fmaxf(fx, -lim), lim);
     f[1] = fminf(fmaxf(fy, -lim), lim);
     f[2] = fz;

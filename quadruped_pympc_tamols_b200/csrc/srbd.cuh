@@ -24,8 +24,12 @@ constexpr int MAX_SPLINES = 16;
 // library sincosf; checked by tests/test_sincos_fast.py on the host arithmetic and by the GPU parity tests).
 // The library sincosf carries an out-of-line Payne-Hanek path behind a branch: three of them per step cut the step
 // body into seven basic blocks and cost BSSY/BSYNC plus instruction-fetch stalls (profiles/r4a_ncu_source_c5.txt).
-// |a| >= 105615 (the library's own switch point), NaN and Inf are evaluated at 0: such a rollout is already lost --
-// the angle itself stays in the state, its cost term is > 2e12 or NaN (-> 1e6 by the saturation).
+// |a| >= 105615 (the library's own switch point), NaN and Inf are evaluated at 0.  For roll and pitch such a rollout
+// is already lost -- the angle itself stays in the state, its cost term (weights 500) is > 5e12 or NaN (-> 1e6 by the
+// saturation).  Yaw has weight 0 in the reference's Q: a rollout whose yaw alone runs past 1e5 rad keeps a finite cost
+// computed with sin = 0, cos = 1 where the library's Payne-Hanek path would still be exact.  Reaching 1e5 rad in a
+// 0.24 s horizon takes a yaw rate of 4e5 rad/s, i.e. angular-velocity cost terms (weights 20..50) above 1e12: not a
+// rollout any update listens to, but a documented divergence.
 __device__ __forceinline__ void sincos_fast(float a, float *sp, float *cp) {
     const float b = fabsf(a) < 105615.0f ? a : 0.0f;
     const int q = __float2int_rn(b * 0.636619772f);

@@ -415,6 +415,13 @@ def test_quad_block_sizes_agree(monkeypatch, method):
     ("random_sampling", "linear_spline", True, 8, 3, 2000),
     ("cem_mppi", "cubic_spline", False, 16, 4, 3000),  # P = 192
     ("mppi", "cubic_spline", True, 5, 1, 10000),       # short horizon, full-size sample count (one wave of quad blocks)
+    # fixed gait with a horizon that is NOT a multiple of 4: the float4 step tables of the thread kernel must stay
+    # 16-byte aligned (s_basis sat at s_st + 9 H floats), and the pair kernel takes any horizon
+    ("mppi", "linear_spline", False, 10, 2, 3000),
+    ("random_sampling", "cubic_spline", False, 5, 1, 2500),
+    ("cem_mppi", "cubic_spline", False, 15, 3, 2000),
+    ("mppi", "zero_order", False, 10, 1, 4100),
+    ("cem_mppi", "zero_order", False, 7, 1, 1500),
 ])
 def test_other_horizons_and_spline_counts(method, param, ga, horizon, splines, n, kernel):
     """mpc_params['horizon'] and ['num_splines'] away from the defaults (12, 2): every kernel, chained over two
