@@ -227,6 +227,30 @@ def test_noise_statistics_and_structure():
         h.close()
 
 
+@pytest.mark.parametrize("method", ["mppi", "cem_mppi", "random_sampling"])
+@pytest.mark.parametrize("param", ["zero_order", "cubic_spline"])
+def test_packed_generator_equals_scalar_generator(monkeypatch, method, param):
+    """The two noise generators of csrc/noise.cuh -- scalar (any kernel, finalize, dump) and packed (two rows per thread,
+    k_rollout_pair) -- produce the same values: QPMPC_DUMP=pair makes qpmpc_generate_noise overwrite the dump with the
+    packed generator's rows.  Bit for bit, except that row 0 may be -0.0 where the scalar one writes +0.0."""
+    mass, inertia, _, _ = ROBOTS["aliengo"]
+    n = 4097
+    outs = []
+    for mode in ("", "pair"):
+        monkeypatch.setenv("QPMPC_DUMP", mode)
+        h = _cabi.Handle(_cabi.make_config(mass=mass, inertia=inertia, sampling_method=method, parametrization=param,
+                                           num_parallel_computations=n))
+        d = torch.empty((n, h.P), dtype=torch.float32, device="cuda")
+        sig = np.linspace(0.5, 4.0, h.P).astype(np.float32)
+        h.generate_noise(42, 5, d.data_ptr(), sigma_in=sig if method == "cem_mppi" else None, robot=3)
+        outs.append(d.cpu().numpy())
+        h.close()
+    a, b = outs
+    assert np.all(a[0] == 0) and np.all(b[0] == 0)
+    assert np.array_equal(a[1:].view(np.uint32), b[1:].view(np.uint32))
+    assert np.std(a[1:]) > 0.1
+
+
 @pytest.mark.parametrize("param,ga", [("zero_order", False), ("linear_spline", True), ("cubic_spline", False), ("cubic_spline", True)])
 def test_rollout_costs_matches_oracle(param, ga, kernel):
     """jit_vectorized_rollout: explicit parameter matrix -> raw costs, incl. a diverging (non-finite) rollout."""
