@@ -114,6 +114,30 @@ int tamols_score_device(tamols_handle *h, const void *d_heights, int32_t height_
                         int32_t max_nr, int32_t max_nc, tamols_result *d_results, double *d_scores,
                         int64_t scores_stride);
 
+/*
+ * tamols_score_device for callers that cannot tolerate a device allocation inside the call (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments, same kernel and bit-identical results; the only difference is
+ * where the kernel's scratch lives.  tamols_score_device keeps the per-tile partial results and the arrival tickets
+ * in buffers of the handle and grows the partial buffer with cudaFree + cudaMalloc when a launch needs more; this
+ * entry point uses a file-scope `static __device__` array of the library instead (tickets + partials,
+ * TAMOLS_STATIC_SCRATCH_BYTES per GPU that loads the library, held until the process exits) and calls no cudaMalloc,
+ * cudaFree or other allocating routine.  Limits: n_jobs <= TAMOLS_STATIC_MAX_JOBS and n_jobs * tiles per job <=
+ * TAMOLS_STATIC_MAX_PARTIALS (tiles per job = ceil(max_nr / th) * ceil(max_nc / 32), th = 8 or 32 as chosen by the
+ * library; always safe: n_jobs * ceil(max_nr / 8) * ceil(max_nc / 32)); anything larger returns TAMOLS_E_ARG with
+ * the numbers in tamols_last_error().  The array is shared by EVERY call on that GPU, whatever the handle or stream:
+ * the tickets are cleared on the handle's stream before each launch (a memset node, no allocation), the partials are
+ * written before they are read, and two such calls that overlap on the GPU (different streams or handles, no
+ * ordering between them) race on it -- serialise them.  The handle's own buffers are not touched.
+ */
+#define TAMOLS_STATIC_MAX_JOBS 4096
+#define TAMOLS_STATIC_MAX_PARTIALS 65536
+#define TAMOLS_STATIC_SCRATCH_BYTES (((TAMOLS_STATIC_MAX_JOBS + 1) * 4 + 255) / 256 * 256 + TAMOLS_STATIC_MAX_PARTIALS * 16)
+int tamols_score_device_static(tamols_handle *h, const void *d_heights, int32_t height_dtype, int32_t num_maps,
+                               int32_t rows, int32_t cols, int32_t pitch, const double *d_xy,
+                               const tamols_leg_job *d_jobs, int32_t n_jobs, int32_t max_nr, int32_t max_nc,
+                               tamols_result *d_results, double *d_scores, int64_t scores_stride);
+
 /* Same with HOST buffers (what the Python class calls): copies heights (f64, [num_maps, rows, cols] dense), optional
  * xy and the jobs to the device, runs the launch, copies results (and scores when not NULL) back, synchronises. */
 int tamols_score_host(tamols_handle *h, const double *heights, int32_t num_maps, int32_t rows, int32_t cols,

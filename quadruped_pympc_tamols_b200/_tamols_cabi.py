@@ -66,8 +66,10 @@ class TamolsSeedBatch(C.Structure):  # include/tamols.h: tamols_seed_batch
                 ("map_origin", C.c_double * 2), ("map_row_axis", C.c_double * 2), ("map_col_axis", C.c_double * 2)]
 
 
+STATIC_MAX_JOBS, STATIC_MAX_PARTIALS = 4096, 65536  # include/tamols.h TAMOLS_STATIC_MAX_*
+
 EXPORTS = ["tamols_create", "tamols_destroy", "tamols_set_params", "tamols_last_error", "tamols_stream",
-           "tamols_launch_count", "tamols_score_device", "tamols_score_host", "tamols_seed_jobs", "tamols_fit_grid", "tamols_score_sensors"]
+           "tamols_launch_count", "tamols_score_device", "tamols_score_device_static", "tamols_score_host", "tamols_seed_jobs", "tamols_fit_grid", "tamols_score_sensors"]
 
 
 def make_params(tamols_params=None, robot_name="aliengo"):
@@ -132,6 +134,7 @@ def lib():
         L.tamols_launch_count.restype = C.c_int64
         L.tamols_score_device.argtypes = [vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp, vp,
                                           C.c_int32, C.c_int32, C.c_int32, vp, vp, C.c_int64]
+        L.tamols_score_device_static.argtypes = L.tamols_score_device.argtypes
         L.tamols_score_host.argtypes = [vp, vp, C.c_int32, C.c_int32, C.c_int32, vp, vp, C.c_int32, vp, vp, C.c_int64]
         L.tamols_seed_jobs.argtypes = [vp, C.POINTER(TamolsSeedBatch)]
         L.tamols_fit_grid.argtypes = [vp, C.c_int32, C.c_int32, vp, vp, vp]
@@ -223,3 +226,11 @@ class Handle:
         check(lib().tamols_score_device(self._h, d_heights, int(height_dtype), int(num_maps), int(rows), int(cols),
                                         int(pitch), d_xy, d_jobs, int(n_jobs), int(max_nr), int(max_nc), d_results,
                                         d_scores, int(scores_stride)))
+
+    def score_device_static(self, d_heights, height_dtype, num_maps, rows, cols, pitch, d_jobs, n_jobs, max_nr, max_nc,
+                            d_results, d_xy=None, d_scores=None, scores_stride=0):
+        """score_device with the kernel's scratch in the library's static device array: no allocation inside the call
+        (include/tamols.h: limits STATIC_MAX_JOBS / STATIC_MAX_PARTIALS, calls that overlap on the GPU race)."""
+        check(lib().tamols_score_device_static(self._h, d_heights, int(height_dtype), int(num_maps), int(rows), int(cols),
+                                               int(pitch), d_xy, d_jobs, int(n_jobs), int(max_nr), int(max_nc),
+                                               d_results, d_scores, int(scores_stride)))

@@ -20,6 +20,7 @@
 #include <cstdint>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -834,6 +835,92 @@ extern "C" int tamols_score_device(tamols_handle *h, const void *d_heights, int3
     TCU(cudaSetDevice(h->device));
     return launch_score(h, d_heights, height_dtype, num_maps, rows, cols, pitch, d_xy, d_jobs, n_jobs, max_nr, max_nc,
                         d_results, d_scores, scores_stride);
+}
+
+// ---------------------------------------------------------------- tamols_score_device_static (include/tamols.h)
+// The scratch of k_tamols_score (arrival tickets + per-tile partials) in a file-scope device array instead of the
+// handle's cudaMalloc'ed buffers: the entry point allocates nothing.  Every GPU that loads the library holds its own
+// copy of the array until the process exits.  In HOST code `g_static_scratch` is only the symbol's host-side stand-in,
+// never a device address: the address a kernel may use comes from cudaGetSymbolAddress, resolved once per device with
+// that device current (static_scratch below) and handed to the kernel through Args like any other pointer.
+constexpr size_t STATIC_TICKET_BYTES = ((size_t)(TAMOLS_STATIC_MAX_JOBS + 1) * sizeof(unsigned int) + 255) / 256 * 256;
+static_assert(sizeof(Partial) == 16, "TAMOLS_STATIC_SCRATCH_BYTES in include/tamols.h assumes 16-byte partials");
+static_assert(STATIC_TICKET_BYTES + (size_t)TAMOLS_STATIC_MAX_PARTIALS * sizeof(Partial) == TAMOLS_STATIC_SCRATCH_BYTES,
+              "scratch layout and TAMOLS_STATIC_SCRATCH_BYTES disagree");
+static __device__ __align__(256) unsigned char g_static_scratch[TAMOLS_STATIC_SCRATCH_BYTES];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+static std::mutex g_static_mu;
+static void *g_static_ptr[STATIC_MAX_DEVICES];  // device address of g_static_scratch on device d, nullptr = not resolved yet
+
+// device address of the array on `device`, which must be the CURRENT device (the symbol resolves per context)
+static int static_scratch(int device, unsigned char **out) {
+    if (device < 0 || device >= STATIC_MAX_DEVICES) return tfail(TAMOLS_E_ARG, "device ordinal beyond the static scratch table");
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[device]) {
+        void *p = nullptr;
+        TCU(cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p || ((uintptr_t)p & 255)) return tfail(TAMOLS_E_CUDA, "cudaGetSymbolAddress returned an unusable address");
+        g_static_ptr[device] = p;
+    }
+    *out = static_cast<unsigned char *>(g_static_ptr[device]);
+    return TAMOLS_OK;
+}
+
+extern "C" int tamols_score_device_static(tamols_handle *h, const void *d_heights, int32_t height_dtype, int32_t num_maps,
+                                          int32_t rows, int32_t cols, int32_t pitch, const double *d_xy,
+                                          const tamols_leg_job *d_jobs, int32_t n_jobs, int32_t max_nr, int32_t max_nc,
+                                          tamols_result *d_results, double *d_scores, int64_t scores_stride) {
+    if (!h || !d_heights || !d_jobs || !d_results) return tfail(TAMOLS_E_ARG, "null argument");
+    if (height_dtype != TAMOLS_F64 && height_dtype != TAMOLS_F32) return tfail(TAMOLS_E_ARG, "unknown height_dtype");
+    if (num_maps < 1 || rows < 1 || cols < 1 || pitch < cols) return tfail(TAMOLS_E_ARG, "bad map shape");
+    if (n_jobs < 1) return tfail(TAMOLS_E_ARG, "n_jobs must be >= 1");
+    if (n_jobs > TAMOLS_STATIC_MAX_JOBS)
+        return tfail(TAMOLS_E_ARG, "tamols_score_device_static: n_jobs = " + std::to_string(n_jobs) +
+                                       " exceeds TAMOLS_STATIC_MAX_JOBS = " + std::to_string(TAMOLS_STATIC_MAX_JOBS) +
+                                       " (use tamols_score_device, which allocates)");
+    if (max_nr < 1 || max_nc < 1 || max_nr > rows || max_nc > cols) return tfail(TAMOLS_E_ARG, "bad window bound");
+    if (d_scores && scores_stride < (int64_t)max_nr * max_nc) return tfail(TAMOLS_E_ARG, "scores_stride too small");
+    // tile height: the rule of launch_score, restated here so that the existing path stays untouched
+    const long long tiles32 = (long long)n_jobs * ((max_nr + 31) / 32) * ((max_nc + TW - 1) / TW);
+    int th = tiles32 >= (long long)h->num_sms ? 32 : 8;
+    if (max_nr <= 32 && max_nc <= TW && max_nr * max_nc <= THREADS && max_nr > 8) th = 32;
+    if (h->env_tile_rows) th = h->env_tile_rows;
+    const int max_tiles = ((max_nr + th - 1) / th) * ((max_nc + TW - 1) / TW);
+    const long long need = (long long)n_jobs * max_tiles;
+    if (need > TAMOLS_STATIC_MAX_PARTIALS)
+        return tfail(TAMOLS_E_ARG, "tamols_score_device_static: " + std::to_string(n_jobs) + " jobs x " +
+                                       std::to_string(max_tiles) + " tiles = " + std::to_string(need) +
+                                       " partials exceed TAMOLS_STATIC_MAX_PARTIALS = " +
+                                       std::to_string(TAMOLS_STATIC_MAX_PARTIALS) + " (use tamols_score_device, which allocates)");
+    TCU(cudaSetDevice(h->device));
+    unsigned char *scratch = nullptr;
+    if (int rc = static_scratch(h->device, &scratch)) return rc;
+    Args a;
+    a.p = h->p;
+    a.heights = d_heights; a.xy = d_xy; a.jobs = d_jobs; a.results = d_results; a.scores = d_scores;
+    a.scores_stride = scores_stride;
+    a.tickets = reinterpret_cast<unsigned int *>(scratch);
+    a.partials = reinterpret_cast<Partial *>(scratch + STATIC_TICKET_BYTES);
+    a.rows = rows; a.cols = cols; a.pitch = pitch; a.max_tiles = max_tiles;
+    a.host_flag = nullptr; a.flag_value = 0; a.n_jobs = n_jobs;
+    // the array keeps whatever the last call (any handle, any stream, possibly one that aborted) left: the tickets must
+    // start at zero, the partials are written by every tile before the merge reads them
+    TCU(cudaMemsetAsync(a.tickets, 0, ((size_t)n_jobs + 1) * sizeof(unsigned int), h->stream));
+    const bool tma = get_tensor_map(h, d_heights, height_dtype, num_maps, rows, cols, pitch, th);
+    const dim3 grid(max_tiles, n_jobs);
+#define TAMOLS_LAUNCH(HT, TMA, TH_) k_tamols_score<HT, TMA, TH_><<<grid, THREADS, 0, h->stream>>>(h->tmap, a)
+    if (height_dtype == TAMOLS_F64) {
+        if (th == 32) { if (tma) TAMOLS_LAUNCH(double, true, 32); else TAMOLS_LAUNCH(double, false, 32); }
+        else { if (tma) TAMOLS_LAUNCH(double, true, 8); else TAMOLS_LAUNCH(double, false, 8); }
+    } else {
+        if (th == 32) { if (tma) TAMOLS_LAUNCH(float, true, 32); else TAMOLS_LAUNCH(float, false, 32); }
+        else { if (tma) TAMOLS_LAUNCH(float, true, 8); else TAMOLS_LAUNCH(float, false, 8); }
+    }
+#undef TAMOLS_LAUNCH
+    TCU(cudaGetLastError());
+    h->launches += 1;
+    return TAMOLS_OK;
 }
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
