@@ -36,8 +36,21 @@ def save(name, robot, tp, heights, xy, jobs, contact=None):
     print(f"tamols_{name}: best {ref['best_index'].tolist()} finite {fin.tolist()}")
 
 
+def multi_tile():
+    """One 96 x 96 candidate window per leg on a 128 x 128 @ 0.02 m map: 36 tiles of 8 x 32 or 9 tiles of 32 x 32 per
+    job in k_tamols_score, so the per-tile partials, the arrival ticket and the merge of the last block are pinned on
+    the reference's own loop (visual_foothold_adaptation.py:188-206), not only on the oracle.  36,864 candidates
+    through the reference's Python loop: about a minute."""
+    rng = np.random.default_rng(500)
+    sc = sy.sweep_scene("go2", rng, "stepping_stones_tall", window=96, map_rows=128, map_cols=128, res=0.02, seed=5)
+    xy = sy.grid_xy(sc["origin"], sc["row_axis"], sc["col_axis"], 128, 128)[None]
+    save("c4_go2_stepping_stones_tall_w96", "go2", sy.tamols_params_for("go2"), sc["heights"], xy, sc["jobs"])
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if "--multi-tile-only" in sys.argv:
+        return multi_tile()
     # C3-T: hyqreal on stepping stones, 13 x 7 @ 0.04 m per-leg maps, trot apex (SURVEY 8(d))
     for k in range(3):
         rng = np.random.default_rng(100 + k)
@@ -81,6 +94,7 @@ def main():
         sc = sy.sweep_scene("go2", rng, kind, window=32, map_rows=96, map_cols=96, res=0.02, seed=k)
         xy = sy.grid_xy(sc["origin"], sc["row_axis"], sc["col_axis"], 96, 96)[None]
         save(f"c4_go2_{kind}_w32", "go2", sy.tamols_params_for("go2"), sc["heights"], xy, sc["jobs"])
+    multi_tile()
 
 
 if __name__ == "__main__":

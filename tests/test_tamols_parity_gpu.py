@@ -104,6 +104,23 @@ def test_cuda_matches_oracle_on_sweep_windows(tc, kind, window):
         assert res["best_index"][k] == (int(np.argmin(scores[k])) if fin.any() else -1)
 
 
+def test_cuda_multi_tile_merge_matches_reference_run(tc, tile_rows):
+    """The 96 x 96-window fixture produced by the reference's own loop (oracle/make_golden_tamols.py multi_tile):
+    36 (8-row) or 9 (32-row) tiles per job, so partials, arrival ticket and last-block merge are pinned on the
+    reference itself; device API, f64 and TMA / plain staging, and the winners sit in different tiles than tile 0."""
+    path = [f for f in tamols_fixtures() if f.endswith("_w96.npz")]
+    assert len(path) == 1
+    p, heights, xy, jobs, g = load_tamols_fixture(path[0])
+    assert int(jobs["nr"].max()) == 96 and int(jobs["nc"].max()) == 96
+    th = 32 if tile_rows == "32" else 8  # auto: 4 jobs x 9 tiles < SM count -> 8-row tiles
+    for pitch in (128, 129):
+        res, scores, launches = _device_run(tc, p, heights, jobs, pitch=pitch)
+        assert launches == 1
+        check_tamols_against_reference(res, scores, g)
+        tiles = {(int(b) // 96 // th, int(b) % 96 // 32) for b in res["best_index"]}
+        assert (0, 0) not in tiles and len(tiles) >= 1
+
+
 def test_cuda_plain_staging_equals_tma_staging(tc):
     """Odd row pitch (no tensor map possible) takes the plain-load kernel: identical results."""
     from oracle import tamols_oracle as to
