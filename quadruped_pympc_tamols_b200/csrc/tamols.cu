@@ -45,8 +45,26 @@ struct Partial {
     int32_t nfinite;
 };
 
+// A divisor that is the same for every candidate of a launch, with its IEEE reciprocal (div_exact below).
+struct Recip {
+    double b, y;  // y = 1.0 / b, correctly rounded (computed by the host's IEEE division)
+};
+
+// Constants derived from tamols_params once per launch on the host (derive_constants): the kernel's FP64 diet.
+struct Derived {
+    Recip two_delta;   // 2.0 * gradient_delta: _compute_edge_cost's central differences (:452-455)
+    Recip six_delta2;  // 6.0 * (delta * delta): the plane fit of _compute_roughness_cost (:497-503)
+    Recip nine;        // 9.0: mean height, mean residual, variance (:503, :511-516)
+    // _check_kinematic_feasibility (:375-395) without the square root: for x >= 0, l_min <= sqrt(x) <= l_max with the
+    // correctly rounded sqrt is the same predicate as reach_lo2 <= x <= reach_hi2, where reach_lo2 is the smallest
+    // double whose rounded root reaches l_min and reach_hi2 the largest whose rounded root stays within l_max
+    // (sqrt is monotonic; the host finds both by stepping ulps around l * l with its own IEEE sqrt)
+    double reach_lo2, reach_hi2;
+};
+
 struct Args {
     tamols_params p;
+    Derived k;
     const void *heights;
     const double *xy;
     const tamols_leg_job *jobs;
@@ -126,19 +144,42 @@ __device__ __forceinline__ void candidate_point(const Args &a, const Ctx &c, con
     cand[2] = (EXACT ? lookup<HT>(a, c, s_box, cand[0], cand[1]) : cell_height<HT>(a, c, s_box, R, C)) + a.p.foot_clearance;
 }
 
+// a / k.b, bit-identical to the IEEE division, from the precomputed reciprocal: q = RN(a y) is within 2 ulp of a / b;
+// one residual step r = a - b q (exact in an FMA), q + r y brings it within half an ulp plus 2^-100, and a second step
+// is then Markstein's correction (q faithful, y = RN(1/b)  =>  RN(q + r y) = RN(a / b)).  Five FP64 instructions in
+// place of the ~25 of div.rn.f64, and no call: nvcc's division takes an out-of-line slow path whenever the NUMERATOR
+// is zero -- which on flat ground (stepping stones, stairs, floors) is every gradient, every plane coefficient and
+// every variance, seven calls per candidate, 14 % of the kernel's executed instructions (profiles/r5_ncu_source_tamols).
+// Outside 1e-290 < |a| < 1e290 (intermediate underflow / overflow, infinities, NaN) the true division is used; zero
+// is returned as a * y, which has the sign a / b has (b > 0).  Explicit FMAs: this file is compiled with -fmad=false.
+__device__ __forceinline__ double div_exact(double a, const Recip &k) {
+    const double m = fabs(a);
+    if (m > 1e-290 && m < 1e290) {
+        double q = a * k.y;
+        double r = __fma_rn(-k.b, q, a);
+        q = __fma_rn(r, k.y, q);
+        r = __fma_rn(-k.b, q, a);
+        return __fma_rn(r, k.y, q);
+    }
+    if (m == 0.0) return a * k.y;
+    return a / k.b;
+}
+// sqrt(x) with the zero case answered at once (sqrt.rn.f64 also leaves its fast path for a zero operand)
+__device__ __forceinline__ double sqrt_z(double x) { return x == 0.0 ? x : sqrt(x); }
+
 // _check_kinematic_feasibility (:375-395), the cheap first gate of _compute_tamols_score (:287-290): most cells of a
 // window fail it (they lie outside the leg's reach)
 __device__ __forceinline__ bool candidate_reachable(const Args &a, const Ctx &c, const tamols_leg_job &j, const double cand[3]) {
     const tamols_params &p = a.p;
     double d0 = cand[0] - j.hip[0], d1 = cand[1] - j.hip[1], d2 = cand[2] - j.hip[2];
-    const double dist_td = sqrt((d0 * d0 + d1 * d1) + d2 * d2);
-    if (!(p.l_min <= dist_td && dist_td <= p.l_max)) return false;
+    const double td2 = (d0 * d0 + d1 * d1) + d2 * d2;  // l_min <= sqrt(td2) <= l_max, see Derived
+    if (!(a.k.reach_lo2 <= td2 && td2 <= a.k.reach_hi2)) return false;
     if (c.flags & TAMOLS_FLAG_HAS_VELOCITY) {
         d0 = cand[0] - (j.hip[0] + j.vel[0] * p.stance_duration);
         d1 = cand[1] - (j.hip[1] + j.vel[1] * p.stance_duration);
         d2 = cand[2] - (j.hip[2] + j.vel[2] * p.stance_duration);
-        const double dist_lo = sqrt((d0 * d0 + d1 * d1) + d2 * d2);
-        if (!(p.l_min <= dist_lo && dist_lo <= p.l_max)) return false;
+        const double lo2 = (d0 * d0 + d1 * d1) + d2 * d2;
+        if (!(a.k.reach_lo2 <= lo2 && lo2 <= a.k.reach_hi2)) return false;
     }
     return true;
 }
@@ -146,7 +187,7 @@ __device__ __forceinline__ bool candidate_reachable(const Args &a, const Ctx &c,
 // the rest of _compute_tamols_score (:291-373) for a reachable candidate
 template <typename HT, bool EXACT>
 __device__ double score_reachable(const Args &a, const Ctx &c, const tamols_leg_job &j, const HT *s_box,
-                                  const double cand[3], int R, int C, const Stencil &sten) {
+                                  const double cand[3], int R, int C, const Stencil &sten, bool moving) {
     const tamols_params &p = a.p;
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
     // _check_leg_collision (:397-420)
@@ -173,9 +214,9 @@ __device__ double score_reachable(const Args &a, const Ctx &c, const tamols_leg_
         }
     double edge;
     {
-        const double gx = fabs(h[2 * 3 + 1] - h[0 * 3 + 1]) / (2.0 * d);
-        const double gy = fabs(h[1 * 3 + 2] - h[1 * 3 + 0]) / (2.0 * d);
-        const double g = sqrt(gx * gx + gy * gy);
+        const double gx = div_exact(fabs(h[2 * 3 + 1] - h[0 * 3 + 1]), a.k.two_delta);
+        const double gy = div_exact(fabs(h[1 * 3 + 2] - h[1 * 3 + 0]), a.k.two_delta);
+        const double g = sqrt_z(gx * gx + gy * gy);
         edge = g <= p.slope_threshold ? 0.0 : g - p.slope_threshold;
     }
     double rough;
@@ -190,8 +231,7 @@ __device__ double score_reachable(const Args &a, const Ctx &c, const tamols_leg_
                 syh += ((double)k * d) * v;
                 sh += v;
             }
-        const double s2 = 6.0 * (d * d);
-        const double pa = sxh / s2, pb = syh / s2, pc = sh / 9.0;
+        const double pa = div_exact(sxh, a.k.six_delta2), pb = div_exact(syh, a.k.six_delta2), pc = div_exact(sh, a.k.nine);
         // residuals are evaluated twice (mean, then spread) instead of being kept: nine fewer float64 values live
         // across the loop, the same operations in the same order
         double mean = 0.0;
@@ -200,7 +240,7 @@ __device__ double score_reachable(const Args &a, const Ctx &c, const tamols_leg_
 #pragma unroll
             for (int k = -1; k <= 1; ++k)
                 mean += h[(i + 1) * 3 + (k + 1)] - ((((double)i * d) * pa + ((double)k * d) * pb) + pc);
-        mean /= 9.0;
+        mean = div_exact(mean, a.k.nine);
         double var = 0.0;
 #pragma unroll
         for (int i = -1; i <= 1; ++i)
@@ -209,7 +249,7 @@ __device__ double score_reachable(const Args &a, const Ctx &c, const tamols_leg_
                 const double res = h[(i + 1) * 3 + (k + 1)] - ((((double)i * d) * pa + ((double)k * d) * pb) + pc);
                 var += (res - mean) * (res - mean);
             }
-        rough = var / 9.0;
+        rough = div_exact(var, a.k.nine);
     }
     // deviation from the seed (:344-345)
     const double e0 = cand[0] - j.seed[0], e1 = cand[1] - j.seed[1], e2 = cand[2] - j.seed[2];
@@ -226,8 +266,8 @@ __device__ double score_reachable(const Args &a, const Ctx &c, const tamols_leg_
     if (!(c.flags & TAMOLS_FLAG_HAS_VELOCITY)) {
         trk = e0 < 0.0 ? e0 * e0 : 0.0;
     } else {
-        const double vm = sqrt(j.vel[0] * j.vel[0] + j.vel[1] * j.vel[1]);
-        if (!(vm < 0.01) && ((j.vel[0] > 0.0 && e0 < 0.0) || (j.vel[0] < 0.0 && e0 > 0.0))) trk = e0 * e0;
+        // moving = !(sqrt(vx^2 + vy^2) < 0.01), a property of the job: evaluated once per thread by the caller
+        if (moving && ((j.vel[0] > 0.0 && e0 < 0.0) || (j.vel[0] < 0.0 && e0 > 0.0))) trk = e0 * e0;
     }
     // _compute_stability_cost (:611-714)
     double stab = 0.0;
@@ -318,12 +358,13 @@ __device__ __forceinline__ void tile_passes(const Args &a, const Ctx &c, const t
     idx = 0x7fffffff;
     nfin = 0;
     const int nlist = *s_nlist;
+    const bool moving = !(sqrt(j.vel[0] * j.vel[0] + j.vel[1] * j.vel[1]) < 0.01);  // :567-571
     for (int i = t; i < nlist; i += THREADS) {
         const int e = s_list[i];
         const int r = tile_r * TH + e / TW, q = tile_c * TW + e % TW;
         double cand[3];
         candidate_point<HT, EXACT>(a, c, s_box, c.r0 + r, c.c0 + q, cand);
-        double sc = score_reachable<HT, EXACT>(a, c, j, s_box, cand, c.r0 + r, c.c0 + q, sten);
+        double sc = score_reachable<HT, EXACT>(a, c, j, s_box, cand, c.r0 + r, c.c0 + q, sten, moving);
         const int ci = r * c.nc + q;
         if (a.scores) a.scores[(long long)job * a.scores_stride + ci] = sc;
         if (sc < inf) {  // NaN is never selected by the reference's `score < best_score`
@@ -639,12 +680,45 @@ static int tfail(int code, const std::string &msg) {
             return tfail(TAMOLS_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));        \
     } while (0)
 
+// Derived (above) from the handle's parameters.  Host IEEE arithmetic = the device's div.rn / sqrt.rn.
+static double sqrt_threshold(double l, bool lower) {
+    // lower: smallest x >= 0 with sqrt(x) >= l; else: largest x with sqrt(x) <= l  (sqrt correctly rounded, monotonic)
+    if (!(l > 0.0) || !std::isfinite(l)) {  // degenerate limits keep the comparison's meaning
+        if (l != l) return l;               // NaN: every comparison false, as upstream
+        if (l <= 0.0) return lower ? 0.0 : (l == 0.0 ? 0.0 : -1.0);  // sqrt(x) >= l always; sqrt(x) <= l only for x = 0 (l = 0) / never
+        return l;                           // +inf
+    }
+    double x = l * l;
+    if (lower) {
+        while (std::sqrt(x) >= l) x = std::nextafter(x, 0.0);
+        while (std::sqrt(x) < l) x = std::nextafter(x, INFINITY);
+    } else {
+        while (std::sqrt(x) <= l) x = std::nextafter(x, INFINITY);
+        while (std::sqrt(x) > l) x = std::nextafter(x, 0.0);
+    }
+    return x;
+}
+static Derived derive_constants(const tamols_params &p) {
+    Derived k;
+    const double d = p.gradient_delta;
+    k.two_delta.b = 2.0 * d;
+    k.six_delta2.b = 6.0 * (d * d);
+    k.nine.b = 9.0;
+    k.two_delta.y = 1.0 / k.two_delta.b;
+    k.six_delta2.y = 1.0 / k.six_delta2.b;
+    k.nine.y = 1.0 / k.nine.b;
+    k.reach_lo2 = sqrt_threshold(p.l_min, true);
+    k.reach_hi2 = sqrt_threshold(p.l_max, false);
+    return k;
+}
+
 typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                     const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
                                     CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 struct tamols_handle {
     tamols_params p;
+    Derived derived;  // derive_constants(p), refreshed with p
     int device, max_jobs, num_sms;
     cudaStream_t stream;
     encode_tiled_fn encode;
@@ -697,6 +771,7 @@ extern "C" int tamols_create(const tamols_params *params, int32_t device, int32_
     if (!h) return tfail(TAMOLS_E_ARG, "out of host memory");
     memset(h, 0, sizeof *h);
     h->p = *params;
+    h->derived = derive_constants(h->p);
     h->device = device;
     h->max_jobs = max_jobs;
     h->num_sms = prop.multiProcessorCount;
@@ -748,6 +823,7 @@ extern "C" int tamols_set_params(tamols_handle *h, const tamols_params *params) 
     if (!h) return tfail(TAMOLS_E_ARG, "null argument");
     if (int rc = check_params(params)) return rc;
     h->p = *params;
+    h->derived = derive_constants(h->p);
     return TAMOLS_OK;
 }
 
@@ -802,6 +878,7 @@ static int launch_score(tamols_handle *h, const void *d_heights, int dtype, int 
     }
     Args a;
     a.p = h->p;
+    a.k = h->derived;
     a.heights = d_heights; a.xy = d_xy; a.jobs = d_jobs; a.results = d_results; a.scores = d_scores;
     a.scores_stride = scores_stride; a.partials = h->d_partials; a.tickets = h->d_tickets;
     a.rows = rows; a.cols = cols; a.pitch = pitch; a.max_tiles = max_tiles;
@@ -898,6 +975,7 @@ extern "C" int tamols_score_device_static(tamols_handle *h, const void *d_height
     if (int rc = static_scratch(h->device, &scratch)) return rc;
     Args a;
     a.p = h->p;
+    a.k = h->derived;
     a.heights = d_heights; a.xy = d_xy; a.jobs = d_jobs; a.results = d_results; a.scores = d_scores;
     a.scores_stride = scores_stride;
     a.tickets = reinterpret_cast<unsigned int *>(scratch);

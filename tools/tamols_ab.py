@@ -21,4 +21,6 @@ with torch.cuda.stream(stream):
         e1.record(stream); e1.synchronize()
         if it >= 3: ms.append(e0.elapsed_time(e1))
 res = np.frombuffer(d_res.cpu().numpy().tobytes(), tc.RESULT_DTYPE)
-print(os.environ.get("QPMPC_LIB", "default"), "median ms", np.median(ms), "nfinite mean", res["num_finite"].mean(), "checksum", int(res["best_index"].astype(np.int64).sum()))
+print(os.environ.get("QPMPC_LIB", "default"), "median ms", np.median(ms), "nfinite mean", res["num_finite"].mean(), "checksum", int(res["best_index"].astype(np.int64).sum()),
+      "score bits", hex(int(np.bitwise_xor.reduce(res["best_score"].view(np.uint64)))), "score sum", repr(float(res["best_score"].sum())))
+h.close()
