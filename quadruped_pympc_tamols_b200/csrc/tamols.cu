@@ -91,26 +91,27 @@ struct Ctx {
 
 // height of map cell (ir, ic), clamped to the leg's window (the KD-tree upstream only holds the leg's own cells, so the
 // nearest neighbour of a point outside is the nearest border cell), + the sensor offset of FastHeightMap.get_height
-template <typename HT>
+// BOX = false: no staged box (k_tamols_window, the result record), every cell through the read-only path (L1 / L2)
+template <typename HT, bool BOX = true>
 __device__ __forceinline__ double cell_height(const Args &a, const Ctx &c, const HT *s_box, int ir, int ic) {
     ir = min(max(ir, c.r0), c.r0 + c.nr - 1);
     ic = min(max(ic, c.c0), c.c0 + c.nc - 1);
     const int lr = ir - c.br, lc = ic - c.bc;
     HT h;
-    if ((unsigned)lr < (unsigned)c.bh && (unsigned)lc < (unsigned)BW)
+    if (BOX && (unsigned)lr < (unsigned)c.bh && (unsigned)lc < (unsigned)BW)
         h = s_box[lr * BW + lc];
     else
         h = __ldg(static_cast<const HT *>(a.heights) + c.map_base + (long long)ir * c.pitch + ic);
     return (double)h + a.p.sensor_offset;
 }
 
-template <typename HT>
+template <typename HT, bool BOX = true>
 __device__ __forceinline__ double lookup(const Args &a, const Ctx &c, const HT *s_box, double x, double y) {
     // FastHeightMap.get_height (:31-35): nearest cell of the leg's map + 0.02
     const double dx = x - c.ox, dy = y - c.oy;
     const double gr = dx * c.arx + dy * c.ary;
     const double gc = dx * c.acx + dy * c.acy;
-    return cell_height<HT>(a, c, s_box, __double2int_rn(gr), __double2int_rn(gc));
+    return cell_height<HT, BOX>(a, c, s_box, __double2int_rn(gr), __double2int_rn(gc));
 }
 
 // The 3 x 3 patch of _compute_roughness_cost / _compute_edge_cost samples the map at the candidate + (i, k) * delta.
@@ -138,10 +139,10 @@ __device__ __forceinline__ void candidate_xy(const Args &a, const Ctx &c, int R,
 
 // candidate construction (:188-196) for map cell (R, C): the cell's own coordinates and its own height (the nearest
 // cell of a cell centre is the cell) + the foot clearance
-template <typename HT, bool EXACT>
+template <typename HT, bool EXACT, bool BOX = true>
 __device__ __forceinline__ void candidate_point(const Args &a, const Ctx &c, const HT *s_box, int R, int C, double cand[3]) {
     candidate_xy(a, c, R, C, cand[0], cand[1]);
-    cand[2] = (EXACT ? lookup<HT>(a, c, s_box, cand[0], cand[1]) : cell_height<HT>(a, c, s_box, R, C)) + a.p.foot_clearance;
+    cand[2] = (EXACT ? lookup<HT, BOX>(a, c, s_box, cand[0], cand[1]) : cell_height<HT, BOX>(a, c, s_box, R, C)) + a.p.foot_clearance;
 }
 
 // a / k.b, bit-identical to the IEEE division, from the precomputed reciprocal: q = RN(a y) is within 2 ulp of a / b;
@@ -185,7 +186,7 @@ __device__ __forceinline__ bool candidate_reachable(const Args &a, const Ctx &c,
 }
 
 // the rest of _compute_tamols_score (:291-373) for a reachable candidate
-template <typename HT, bool EXACT>
+template <typename HT, bool EXACT, bool BOX = true>
 __device__ double score_reachable(const Args &a, const Ctx &c, const tamols_leg_job &j, const HT *s_box,
                                   const double cand[3], int R, int C, const Stencil &sten, bool moving) {
     const tamols_params &p = a.p;
@@ -197,7 +198,7 @@ __device__ double score_reachable(const Args &a, const Ctx &c, const tamols_leg_
         const double px = be * j.hip[0] + al * cand[0];
         const double py = be * j.hip[1] + al * cand[1];
         const double pz = be * j.hip[2] + al * cand[2];
-        const double h_ground = lookup(a, c, s_box, px, py) - p.sensor_offset;
+        const double h_ground = lookup<HT, BOX>(a, c, s_box, px, py) - p.sensor_offset;
         if (pz < h_ground + p.collision_margin) return inf;
     }
     const double d = p.gradient_delta;
@@ -209,8 +210,8 @@ __device__ double score_reachable(const Args &a, const Ctx &c, const tamols_leg_
         for (int k = -1; k <= 1; ++k)
         {
             const int q = (i + 1) * 3 + (k + 1);
-            h[q] = EXACT ? lookup(a, c, s_box, cand[0] + (double)i * d, cand[1] + (double)k * d)
-                         : cell_height<HT>(a, c, s_box, R + sten.dr[q], C + sten.dc[q]);
+            h[q] = EXACT ? lookup<HT, BOX>(a, c, s_box, cand[0] + (double)i * d, cand[1] + (double)k * d)
+                         : cell_height<HT, BOX>(a, c, s_box, R + sten.dr[q], C + sten.dc[q]);
         }
     double edge;
     {
@@ -375,6 +376,45 @@ __device__ __forceinline__ void tile_passes(const Args &a, const Ctx &c, const t
 
 }
 
+// The result record of one job from its (score, index, count) -- best candidate, constraint box (:206-228) -- by one thread.
+template <typename HT>
+__device__ __forceinline__ void write_result(const Args &a, const Ctx &c, int job, double s, int idx, int nfin) {
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+    // host-buffer call: the record is built locally and leaves as {word, sequence} pairs (below)
+    tamols_result local;
+    tamols_result &out = a.host_flag != nullptr ? local : a.results[job];
+    out.num_finite = nfin;
+    out.best_score = s;
+    double xyz[3] = {0.0, 0.0, 0.0};
+    if (s < inf) {
+        out.best_index = idx;
+        candidate_xy(a, c, c.r0 + idx / c.nc, c.c0 + idx % c.nc, xyz[0], xyz[1]);
+        xyz[2] = lookup<HT, false>(a, c, nullptr, xyz[0], xyz[1]) + a.p.foot_clearance;  // no staged box: through L2
+    } else {
+        out.best_index = -1;
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        out.best_xyz[k] = xyz[k];
+        out.vertex1[k] = xyz[k];
+        out.vertex2[k] = xyz[k];
+    }
+    out.vertex1[0] -= a.p.constraint_box_dx;
+    out.vertex1[1] -= a.p.constraint_box_dy;
+    out.vertex2[0] += a.p.constraint_box_dx;
+    out.vertex2[1] += a.p.constraint_box_dy;
+    if (a.host_flag != nullptr) {
+        // Results go to mapped host memory as 8-byte {word, sequence} stores: every pair carries its own arrival
+        // flag, so neither a system-wide fence nor a job counter is needed; the host waits for each pair.
+        constexpr int RW = (int)(sizeof(tamols_result) / 4);
+        const uint32_t *w = reinterpret_cast<const uint32_t *>(&local);
+        uint2 *dst = reinterpret_cast<uint2 *>(a.host_flag) + (size_t)job * RW;
+#pragma unroll
+        for (int k = 0; k < RW; ++k)
+            asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(dst + k), "r"(w[k]), "r"(a.flag_value) : "memory");
+    }
+}
+
 // ---------------------------------------------------------------- the kernel ---------------------------------
 struct GridInv {
     double arx, ary, acx, acy;
@@ -529,44 +569,142 @@ __global__ void __launch_bounds__(THREADS, TH == 32 ? 4 : 2) k_tamols_score(cons
             }
         }
     }
-    if (t == 0) {  // write the result
-        // host-buffer call: the record is built locally and leaves as {word, sequence} pairs (below)
-        tamols_result local;
-        tamols_result &out = a.host_flag != nullptr ? local : a.results[job];
-        out.num_finite = nfin;
-        out.best_score = s;
-        double xyz[3] = {0.0, 0.0, 0.0};
-        if (s < inf) {
-            out.best_index = idx;
-            Ctx g = c;
-            g.bh = 0;            // no staged box for this lookup: read the map through L2
-            g.bc = -0x40000000;
-            candidate_xy(a, g, c.r0 + idx / c.nc, c.c0 + idx % c.nc, xyz[0], xyz[1]);
-            xyz[2] = lookup<HT>(a, g, s_box, xyz[0], xyz[1]) + a.p.foot_clearance;
-        } else {
-            out.best_index = -1;
-        }
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            out.best_xyz[k] = xyz[k];
-            out.vertex1[k] = xyz[k];
-            out.vertex2[k] = xyz[k];
-        }
-        out.vertex1[0] -= a.p.constraint_box_dx;
-        out.vertex1[1] -= a.p.constraint_box_dy;
-        out.vertex2[0] += a.p.constraint_box_dx;
-        out.vertex2[1] += a.p.constraint_box_dy;
+    if (t == 0) {
+        write_result<HT>(a, c, job, s, idx, nfin);
         if (ntiles > 1) a.tickets[job] = 0;  // ready for the next launch on this stream
-        if (a.host_flag != nullptr) {
-            // Results go to mapped host memory as 8-byte {word, sequence} stores: every pair carries its own arrival
-            // flag, so neither a system-wide fence nor a job counter is needed; the host waits for each pair.
-            constexpr int RW = (int)(sizeof(tamols_result) / 4);
-            const uint32_t *w = reinterpret_cast<const uint32_t *>(&local);
-            uint2 *dst = reinterpret_cast<uint2 *>(a.host_flag) + (size_t)job * RW;
-#pragma unroll
-            for (int k = 0; k < RW; ++k)
-                asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(dst + k), "r"(w[k]), "r"(a.flag_value) : "memory");
+    }
+}
+
+// ---------------------------------------------------------------- the throughput kernel ----------------------
+// One block of WTHREADS threads per JOB, the whole candidate window: the batched regime (thousands of jobs in one
+// launch), where a job does not need to be spread over SMs.  Same per-candidate code as k_tamols_score (gate,
+// score_reachable), same lexicographic (score, index) minimum, hence the same result bits; what changes is the shape
+// of the work:
+//   * no staged box -- every height comes through the read-only path (pass 1 reads the window row-major, coalesced;
+//     the stencil and collision look-ups of pass 2 hit L1 / L2: the map's window region is a few tens of KB);
+//   * ONE compacted list per band of at most WBAND cells (the whole window when it has <= WBAND cells): with ~830
+//     reachable candidates of a 64 x 64 window and 128 threads a thread scores 6.5 candidates, so the ragged last round
+//     costs 1 / 7 of pass 2 instead of the 20 % (205 candidates on 256 threads) .. 50 % (257+) of a 32 x 32 tile;
+//   * no per-tile partials, arrival tickets or merge, a third of the block barriers per candidate.
+// 64 registers x 128 threads: up to 8 blocks per SM (the tile kernel: 4 x 256 threads with one to two idle warps each).
+constexpr int WTHREADS = 128;
+constexpr int WBAND = 8192;  // cells per band: the list holds 16-bit cell offsets inside the band (16 KB of shared memory)
+
+template <typename HT, bool EXACT>
+__device__ __forceinline__ void window_passes(const Args &a, const Ctx &c, const tamols_leg_job &j, const Stencil &sten,
+                                              unsigned short *s_list, int *s_nlist, int job, double &s, int &idx, int &nfin) {
+    const int t = threadIdx.x;
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+    const int cells = c.nr * c.nc;
+    const bool moving = !(sqrt(j.vel[0] * j.vel[0] + j.vel[1] * j.vel[1]) < 0.01);  // :567-571
+    s = inf;
+    idx = 0x7fffffff;
+    nfin = 0;
+    for (int band = 0; band < cells; band += WBAND) {
+        const int n = min(WBAND, cells - band);
+        // ---- pass 1: the reachability gate on every cell of the band, survivors compacted (order arbitrary, result not)
+        for (int e0 = 0; e0 < n; e0 += WTHREADS) {
+            const int e = e0 + t;
+            bool reach = false;
+            if (e < n) {
+                const int ci = band + e, r = ci / c.nc, q = ci - r * c.nc;
+                double cand[3];
+                candidate_point<HT, EXACT, false>(a, c, nullptr, c.r0 + r, c.c0 + q, cand);
+                reach = candidate_reachable(a, c, j, cand);
+                if (!reach && a.scores) a.scores[(long long)job * a.scores_stride + ci] = inf;
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, reach);
+            int base = 0;
+            if ((t & 31) == 0 && m) base = atomicAdd(s_nlist, __popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (reach) s_list[base + __popc(m & ((1u << (t & 31)) - 1u))] = (unsigned short)e;
         }
+        __syncthreads();
+        // ---- pass 2: full score of the reachable candidates
+        const int nlist = *s_nlist;
+        for (int i = t; i < nlist; i += WTHREADS) {
+            const int ci = band + s_list[i], r = ci / c.nc, q = ci - r * c.nc;
+            double cand[3];
+            candidate_point<HT, EXACT, false>(a, c, nullptr, c.r0 + r, c.c0 + q, cand);
+            const double sc = score_reachable<HT, EXACT, false>(a, c, j, nullptr, cand, c.r0 + r, c.c0 + q, sten, moving);
+            if (a.scores) a.scores[(long long)job * a.scores_stride + ci] = sc;
+            if (sc < inf) {  // NaN is never selected by the reference's `score < best_score`
+                ++nfin;
+                argmin_combine(s, idx, sc, ci);
+            }
+        }
+        __syncthreads();  // every thread is done with this band's list
+        if (t == 0) *s_nlist = 0;
+        __syncthreads();
+    }
+}
+
+template <typename HT>
+__global__ void __launch_bounds__(WTHREADS, 8) k_tamols_window(const Args a) {
+    __shared__ __align__(8) tamols_leg_job s_job;
+    __shared__ GridInv s_inv;
+    __shared__ Stencil s_sten;
+    __shared__ unsigned short s_list[WBAND];
+    __shared__ int s_nlist;
+    __shared__ double s_rs[WTHREADS / 32];
+    __shared__ int s_ri[WTHREADS / 32], s_rn[WTHREADS / 32];
+    const int job = blockIdx.x, t = threadIdx.x;
+    {
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(a.jobs + job);
+        if (t < (int)(sizeof(tamols_leg_job) / 4)) reinterpret_cast<uint32_t *>(&s_job)[t] = __ldg(src + t);
+        if (t == 0) s_nlist = 0;
+    }
+    __syncthreads();
+    const tamols_leg_job &j = s_job;
+    Ctx c;
+    c.map = j.map; c.r0 = j.r0; c.c0 = j.c0; c.nr = j.nr; c.nc = j.nc; c.flags = j.flags;
+    c.br = 0; c.bc = 0; c.bh = 0;  // no staged box
+    c.pitch = a.pitch;
+    c.map_base = (long long)c.map * a.rows * a.pitch;
+    c.ox = j.origin[0]; c.oy = j.origin[1];
+    c.rax = j.row_axis[0]; c.ray = j.row_axis[1]; c.cax = j.col_axis[0]; c.cay = j.col_axis[1];
+    if (t == 32) {
+        const double r2 = c.rax * c.rax + c.ray * c.ray, c2 = c.cax * c.cax + c.cay * c.cay;
+        s_inv.arx = c.rax / r2; s_inv.ary = c.ray / r2; s_inv.acx = c.cax / c2; s_inv.acy = c.cay / c2;
+    }
+    if (t >= 64 && t < 73) {  // nearest-cell offsets of the nine patch points (Stencil), as in k_tamols_score
+        const int q = t - 64, i = q / 3 - 1, k = q % 3 - 1;
+        const double r2 = c.rax * c.rax + c.ray * c.ray, c2 = c.cax * c.cax + c.cay * c.cay;
+        const double dx = (double)i * a.p.gradient_delta, dy = (double)k * a.p.gradient_delta;
+        const double gr = dx * (c.rax / r2) + dy * (c.ray / r2), gc = dx * (c.cax / c2) + dy * (c.cay / c2);
+        const int ir = __double2int_rn(gr), ic = __double2int_rn(gc);
+        s_sten.dr[q] = ir;
+        s_sten.dc[q] = ic;
+        const bool tie = fabs(fabs(gr - (double)ir) - 0.5) < 1e-6 || fabs(fabs(gc - (double)ic) - 0.5) < 1e-6;
+        const unsigned any = __ballot_sync(0x1ffu, tie);
+        if (q == 0) s_sten.exact = (any != 0u || TAMOLS_EXACT_LOOKUPS) ? 1 : 0;
+    }
+    __syncthreads();
+    c.arx = s_inv.arx; c.ary = s_inv.ary; c.acx = s_inv.acx; c.acy = s_inv.acy;
+    double s;
+    int idx, nfin;
+    if (s_sten.exact != 0) window_passes<HT, true>(a, c, j, s_sten, s_list, &s_nlist, job, s, idx, nfin);
+    else window_passes<HT, false>(a, c, j, s_sten, s_list, &s_nlist, job, s, idx, nfin);
+    // ---- block reduction: lexicographic (score, index) minimum = first minimum in row-major order
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double os = __shfl_xor_sync(0xffffffffu, s, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+        argmin_combine(s, idx, os, oi);
+        nfin += __shfl_xor_sync(0xffffffffu, nfin, o);
+    }
+    if ((t & 31) == 0) {
+        s_rs[t >> 5] = s;
+        s_ri[t >> 5] = idx;
+        s_rn[t >> 5] = nfin;
+    }
+    __syncthreads();
+    if (t == 0) {
+        for (int w = 1; w < WTHREADS / 32; ++w) {
+            argmin_combine(s, idx, s_rs[w], s_ri[w]);
+            nfin += s_rn[w];
+        }
+        write_result<HT>(a, c, job, s, idx, nfin);
     }
 }
 
@@ -739,6 +877,7 @@ struct tamols_handle {
     unsigned int seq;
     int env_tile_rows;  // TAMOLS_TILE_ROWS (0 = automatic) and TAMOLS_ZEROCOPY, read from the environment once per
     int env_zerocopy;   // handle: a getenv per call is measurable on a 30 us path
+    int env_kernel;     // TAMOLS_KERNEL: 0 automatic, 1 "tile" (k_tamols_score), 2 "window" (k_tamols_window)
 };
 
 extern "C" const char *tamols_last_error(void) { return g_terr.c_str(); }
@@ -795,6 +934,7 @@ extern "C" int tamols_create(const tamols_params *params, int32_t device, int32_
     h->seq = 0;
     h->env_tile_rows = 0;
     if (const char *e = getenv("TAMOLS_TILE_ROWS")) h->env_tile_rows = atoi(e) == 32 ? 32 : 8;
+    if (const char *e = getenv("TAMOLS_KERNEL")) h->env_kernel = !strcmp(e, "tile") ? 1 : !strcmp(e, "window") ? 2 : 0;
     {
         const char *zc = getenv("TAMOLS_ZEROCOPY");
         h->env_zerocopy = !(zc && zc[0] == '0');
@@ -853,6 +993,20 @@ static bool get_tensor_map(tamols_handle *h, const void *d_heights, int dtype, i
     return true;
 }
 
+// k_tamols_window (one block per job) once the jobs alone fill the GPU several times over; k_tamols_score (a job's
+// window split into tiles over many SMs) for the latency regime.  Same results either way.
+static bool use_window_kernel(const tamols_handle *h, int n_jobs) {
+    if (h->env_kernel) return h->env_kernel == 2;
+    return n_jobs >= 4 * h->num_sms;
+}
+static int launch_window(tamols_handle *h, const Args &a, int dtype) {
+    if (dtype == TAMOLS_F64) k_tamols_window<double><<<a.n_jobs, WTHREADS, 0, h->stream>>>(a);
+    else k_tamols_window<float><<<a.n_jobs, WTHREADS, 0, h->stream>>>(a);
+    TCU(cudaGetLastError());
+    h->launches += 1;
+    return TAMOLS_OK;
+}
+
 static int launch_score(tamols_handle *h, const void *d_heights, int dtype, int maps, int rows, int cols, int pitch,
                         const double *d_xy, const tamols_leg_job *d_jobs, int n_jobs, int max_nr, int max_nc,
                         tamols_result *d_results, double *d_scores, int64_t scores_stride,
@@ -864,6 +1018,16 @@ static int launch_score(tamols_handle *h, const void *d_heights, int dtype, int 
     // which finishes without the partial / ticket / merge round trips
     if (max_nr <= 32 && max_nc <= TW && max_nr * max_nc <= THREADS && max_nr > 8) th = 32;
     if (h->env_tile_rows) th = h->env_tile_rows;
+    if (use_window_kernel(h, n_jobs)) {  // no tiles: no partials, tickets or tensor map
+        Args a;
+        a.p = h->p;
+        a.k = h->derived;
+        a.heights = d_heights; a.xy = d_xy; a.jobs = d_jobs; a.results = d_results; a.scores = d_scores;
+        a.scores_stride = scores_stride; a.partials = nullptr; a.tickets = nullptr;
+        a.rows = rows; a.cols = cols; a.pitch = pitch; a.max_tiles = 0;
+        a.host_flag = host_flag; a.flag_value = flag_value; a.n_jobs = n_jobs;
+        return launch_window(h, a, dtype);
+    }
     const int max_tiles = ((max_nr + th - 1) / th) * ((max_nc + TW - 1) / TW);
     const size_t need = (size_t)n_jobs * max_tiles;
     if (need > h->partial_cap) {

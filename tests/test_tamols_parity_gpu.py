@@ -16,12 +16,16 @@ from tests.util import check_tamols_against_reference, load_tamols_fixture, tamo
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(params=["auto", "8", "32"], autouse=True)
+@pytest.fixture(params=["auto", "8", "32", "window"], autouse=True)
 def tile_rows(request, monkeypatch):
-    """Both tile shapes of k_tamols_score at every size (the library otherwise picks by launch size)."""
-    if request.param == "auto":
-        monkeypatch.delenv("TAMOLS_TILE_ROWS", raising=False)
-    else:
+    """Both tile shapes of k_tamols_score and the one-block-per-job k_tamols_window at every size (the library otherwise
+    picks by launch size; the environment is read once per handle)."""
+    monkeypatch.delenv("TAMOLS_TILE_ROWS", raising=False)
+    monkeypatch.delenv("TAMOLS_KERNEL", raising=False)
+    if request.param == "window":
+        monkeypatch.setenv("TAMOLS_KERNEL", "window")
+    elif request.param != "auto":
+        monkeypatch.setenv("TAMOLS_KERNEL", "tile")
         monkeypatch.setenv("TAMOLS_TILE_ROWS", request.param)
     return request.param
 
@@ -112,13 +116,32 @@ def test_cuda_multi_tile_merge_matches_reference_run(tc, tile_rows):
     assert len(path) == 1
     p, heights, xy, jobs, g = load_tamols_fixture(path[0])
     assert int(jobs["nr"].max()) == 96 and int(jobs["nc"].max()) == 96
-    th = 32 if tile_rows == "32" else 8  # auto: 4 jobs x 9 tiles < SM count -> 8-row tiles
+    th = 32 if tile_rows == "32" else 8  # auto: 4 jobs x 9 tiles < SM count -> 8-row tiles ("window": no tiles, 2 bands)
     for pitch in (128, 129):
         res, scores, launches = _device_run(tc, p, heights, jobs, pitch=pitch)
         assert launches == 1
         check_tamols_against_reference(res, scores, g)
         tiles = {(int(b) // 96 // th, int(b) % 96 // 32) for b in res["best_index"]}
         assert (0, 0) not in tiles and len(tiles) >= 1
+
+
+@pytest.mark.parametrize("kind", ["noise", "stepping_stones_tall", "flat", "stairs"])
+def test_cuda_scores_have_the_oracles_bits(tc, kind):
+    """div_exact (csrc/tamols.cu: divisions by 2 delta, 6 delta^2 and 9 through the precomputed reciprocal with two
+    residual steps), the zero-guarded sqrt and the squared reachability thresholds are claimed bit-identical to IEEE
+    div / sqrt: every per-candidate score must then carry the bits of the strict (-ffp-contract=off) C oracle, which
+    divides and takes roots with the host's IEEE instructions.  'noise' exercises the residual steps (non-zero
+    numerators everywhere), the flat terrains the zero path, the window border the reachability thresholds."""
+    from oracle import tamols_oracle as to
+    rng = np.random.default_rng(21)
+    sc = sy.sweep_scene("go2", rng, kind, window=64, map_rows=256, map_cols=256, res=0.02, seed=6, robots=6)
+    p = tc.make_params(sy.tamols_params_for("go2"), "go2")
+    res, scores, _ = _device_run(tc, p, sc["heights"], sc["jobs"])
+    ores, oscores = to.score(p, sc["heights"], sc["jobs"], fast=False)
+    assert np.isfinite(oscores).sum() > 1000
+    assert np.array_equal(scores.view(np.uint64), oscores.view(np.uint64))
+    assert np.array_equal(res["best_index"], ores["best_index"]) and np.array_equal(res["num_finite"], ores["num_finite"])
+    assert np.array_equal(res["best_score"].view(np.uint64), ores["best_score"].view(np.uint64))
 
 
 def test_cuda_plain_staging_equals_tma_staging(tc):
