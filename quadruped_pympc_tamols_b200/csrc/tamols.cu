@@ -23,6 +23,7 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "../../include/tamols.h"
@@ -124,6 +125,8 @@ __device__ __forceinline__ double lookup(const Args &a, const Ctx &c, const HT *
 struct Stencil {
     int dr[9], dc[9];
     int exact;
+    int off[9];      // dr * pitch + dc: the nine cells relative to the candidate's own (k_tamols_window)
+    int rmax, cmax;  // max |dr|, max |dc|: a candidate at least that far inside its window needs no clamping
 };
 
 __device__ __forceinline__ void candidate_xy(const Args &a, const Ctx &c, int R, int C, double &x, double &y) {
@@ -210,9 +213,22 @@ __device__ double score_reachable(const Args &a, const Ctx &c, const tamols_leg_
         for (int k = -1; k <= 1; ++k)
         {
             const int q = (i + 1) * 3 + (k + 1);
-            h[q] = EXACT ? lookup<HT, BOX>(a, c, s_box, cand[0] + (double)i * d, cand[1] + (double)k * d)
-                         : cell_height<HT, BOX>(a, c, s_box, R + sten.dr[q], C + sten.dc[q]);
+            if (EXACT) h[q] = lookup<HT, BOX>(a, c, s_box, cand[0] + (double)i * d, cand[1] + (double)k * d);
+            else if (BOX) h[q] = cell_height<HT, true>(a, c, s_box, R + sten.dr[q], C + sten.dc[q]);
         }
+    if (!EXACT && !BOX) {
+        // no staged box: a candidate whose whole patch lies inside its window (all but a border strip) reads the nine
+        // cells at fixed offsets from its own -- no clamps, one address each; the same cells, the same values
+        const int ir = R - c.r0, ic = C - c.c0;
+        if (ir >= sten.rmax && c.nr - 1 - ir >= sten.rmax && ic >= sten.cmax && c.nc - 1 - ic >= sten.cmax) {
+            const HT *own = static_cast<const HT *>(a.heights) + c.map_base + (long long)R * c.pitch + C;
+#pragma unroll
+            for (int q = 0; q < 9; ++q) h[q] = (double)__ldg(own + sten.off[q]) + p.sensor_offset;
+        } else {
+#pragma unroll
+            for (int q = 0; q < 9; ++q) h[q] = cell_height<HT, false>(a, c, s_box, R + sten.dr[q], C + sten.dc[q]);
+        }
+    }
     double edge;
     {
         const double gx = div_exact(fabs(h[2 * 3 + 1] - h[0 * 3 + 1]), a.k.two_delta);
@@ -488,9 +504,15 @@ __global__ void __launch_bounds__(THREADS, TH == 32 ? 4 : 2) k_tamols_score(cons
         const int ir = __double2int_rn(gr), ic = __double2int_rn(gc);
         s_sten.dr[q] = ir;
         s_sten.dc[q] = ic;
+        s_sten.off[q] = ir * a.pitch + ic;
         const bool tie = fabs(fabs(gr - (double)ir) - 0.5) < 1e-6 || fabs(fabs(gc - (double)ic) - 0.5) < 1e-6;
         const unsigned any = __ballot_sync(0x1ffu, tie);
-        if (q == 0) s_sten.exact = (any != 0u || TAMOLS_EXACT_LOOKUPS) ? 1 : 0;
+        const int rmax = __reduce_max_sync(0x1ffu, abs(ir)), cmax = __reduce_max_sync(0x1ffu, abs(ic));
+        if (q == 0) {
+            s_sten.exact = (any != 0u || TAMOLS_EXACT_LOOKUPS) ? 1 : 0;
+            s_sten.rmax = rmax;
+            s_sten.cmax = cmax;
+        }
     }
     __syncthreads();  // s_bar initialised (TMA) / s_box written (plain) / s_inv, s_sten written
     c.arx = s_inv.arx; c.ary = s_inv.ary; c.acx = s_inv.acx; c.acy = s_inv.acy;
@@ -587,43 +609,95 @@ __global__ void __launch_bounds__(THREADS, TH == 32 ? 4 : 2) k_tamols_score(cons
 //     costs 1 / 7 of pass 2 instead of the 20 % (205 candidates on 256 threads) .. 50 % (257+) of a 32 x 32 tile;
 //   * no per-tile partials, arrival tickets or merge, a third of the block barriers per candidate.
 // 64 registers x 128 threads: up to 8 blocks per SM (the tile kernel: 4 x 256 threads with one to two idle warps each).
-constexpr int WTHREADS = 128;
 constexpr int WBAND = 8192;  // cells per band: the list holds 16-bit cell offsets inside the band (16 KB of shared memory)
 
-template <typename HT, bool EXACT>
+// candidate_reachable with the job's constants in registers: hip, hip + vel * stance_duration (the same product and
+// sum, rounded once per job instead of once per cell)
+struct Gate {
+    double h0, h1, h2, v0, v1, v2;
+    bool has_vel;
+};
+__device__ __forceinline__ bool gate_reachable(const Args &a, const Gate &g, const double cand[3]) {
+    double d0 = cand[0] - g.h0, d1 = cand[1] - g.h1, d2 = cand[2] - g.h2;
+    const double td2 = (d0 * d0 + d1 * d1) + d2 * d2;
+    if (!(a.k.reach_lo2 <= td2 && td2 <= a.k.reach_hi2)) return false;
+    if (g.has_vel) {
+        d0 = cand[0] - g.v0;
+        d1 = cand[1] - g.v1;
+        d2 = cand[2] - g.v2;
+        const double lo2 = (d0 * d0 + d1 * d1) + d2 * d2;
+        if (!(a.k.reach_lo2 <= lo2 && lo2 <= a.k.reach_hi2)) return false;
+    }
+    return true;
+}
+
+template <typename HT, bool EXACT, int WTHREADS>
 __device__ __forceinline__ void window_passes(const Args &a, const Ctx &c, const tamols_leg_job &j, const Stencil &sten,
                                               unsigned short *s_list, int *s_nlist, int job, double &s, int &idx, int &nfin) {
-    const int t = threadIdx.x;
+    constexpr int NW = WTHREADS / 32;
+    const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
-    const int cells = c.nr * c.nc;
     const bool moving = !(sqrt(j.vel[0] * j.vel[0] + j.vel[1] * j.vel[1]) < 0.01);  // :567-571
     s = inf;
     idx = 0x7fffffff;
     nfin = 0;
-    for (int band = 0; band < cells; band += WBAND) {
-        const int n = min(WBAND, cells - band);
-        // ---- pass 1: the reachability gate on every cell of the band, survivors compacted (order arbitrary, result not)
-        for (int e0 = 0; e0 < n; e0 += WTHREADS) {
-            const int e = e0 + t;
-            bool reach = false;
-            if (e < n) {
-                const int ci = band + e, r = ci / c.nc, q = ci - r * c.nc;
-                double cand[3];
-                candidate_point<HT, EXACT, false>(a, c, nullptr, c.r0 + r, c.c0 + q, cand);
-                reach = candidate_reachable(a, c, j, cand);
-                if (!reach && a.scores) a.scores[(long long)job * a.scores_stride + ci] = inf;
+    // bands of whole rows, at most WBAND cells each (the host sends windows wider than WBAND to the tile kernel)
+    const int band_rows = max(1, WBAND / c.nc);
+    for (int rb = 0; rb < c.nr; rb += band_rows) {
+        const int nrb = min(band_rows, c.nr - rb);
+        Gate g;  // built per band: twelve registers that pass 2 does not have to carry
+        g.h0 = j.hip[0]; g.h1 = j.hip[1]; g.h2 = j.hip[2];
+        g.v0 = j.hip[0] + j.vel[0] * a.p.stance_duration;
+        g.v1 = j.hip[1] + j.vel[1] * a.p.stance_duration;
+        g.v2 = j.hip[2] + j.vel[2] * a.p.stance_duration;
+        g.has_vel = (c.flags & TAMOLS_FLAG_HAS_VELOCITY) != 0;
+        const HT *hmap = static_cast<const HT *>(a.heights) + c.map_base;
+        // ---- pass 1: the reachability gate on every cell of the band, a warp per row (coalesced, no index division),
+        // survivors compacted as 16-bit offsets inside the band (order arbitrary, result not)
+        // (two copies of the loop: the plain one -- grid coordinates, no per-candidate score output, what a batched
+        // launch runs -- keeps the two pointer tests and their address arithmetic out of the 30-odd instructions a cell costs)
+        auto pass1 = [&](auto plain_tag) {
+            constexpr bool PLAIN = decltype(plain_tag)::value;
+            for (int r = rb + wid; r < rb + nrb; r += NW) {
+                const int R = c.r0 + r;
+                const double xr = c.ox + (double)R * c.rax, yr = c.oy + (double)R * c.ray;  // candidate_xy's first sum
+                const HT *hrow = hmap + (long long)R * c.pitch + c.c0;
+                for (int q0 = 0; q0 < c.nc; q0 += 32) {
+                    const int q = q0 + lane;
+                    bool reach = false;
+                    if (q < c.nc) {
+                        double cand[3];
+                        if (!PLAIN && a.xy) candidate_xy(a, c, R, c.c0 + q, cand[0], cand[1]);
+                        else {
+                            cand[0] = xr + (double)(c.c0 + q) * c.cax;
+                            cand[1] = yr + (double)(c.c0 + q) * c.cay;
+                        }
+                        // the cell's own height (the nearest cell of a cell centre is the cell) + offset + clearance
+                        cand[2] = (EXACT ? lookup<HT, false>(a, c, nullptr, cand[0], cand[1])
+                                         : (double)__ldg(hrow + q) + a.p.sensor_offset) + a.p.foot_clearance;
+                        reach = gate_reachable(a, g, cand);
+                        if (!PLAIN && !reach && a.scores) a.scores[(long long)job * a.scores_stride + r * c.nc + q] = inf;
+                    }
+                    const unsigned m = __ballot_sync(0xffffffffu, reach);
+                    if (m) {  // warp-uniform
+                        // one shared-memory atomic per warp and trip, issued as PTX: atomicAdd() under `lane == 0` makes
+                        // nvcc wrap its own warp aggregation (vote, find-leader, shuffle: ~25 instructions) around it
+                        unsigned base = 0;
+                        if (lane == 0)
+                            asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(base) : "r"(smem_u32(s_nlist)), "r"(__popc(m)) : "memory");
+                        base = __shfl_sync(0xffffffffu, base, 0);
+                        if (reach) s_list[base + __popc(m & ((1u << lane) - 1u))] = (unsigned short)((r - rb) * c.nc + q);
+                    }
+                }
             }
-            const unsigned m = __ballot_sync(0xffffffffu, reach);
-            int base = 0;
-            if ((t & 31) == 0 && m) base = atomicAdd(s_nlist, __popc(m));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (reach) s_list[base + __popc(m & ((1u << (t & 31)) - 1u))] = (unsigned short)e;
-        }
+        };
+        if (a.xy == nullptr && a.scores == nullptr) pass1(std::true_type{});
+        else pass1(std::false_type{});
         __syncthreads();
         // ---- pass 2: full score of the reachable candidates
         const int nlist = *s_nlist;
         for (int i = t; i < nlist; i += WTHREADS) {
-            const int ci = band + s_list[i], r = ci / c.nc, q = ci - r * c.nc;
+            const int e = s_list[i], rl = e / c.nc, q = e - rl * c.nc, r = rb + rl, ci = r * c.nc + q;
             double cand[3];
             candidate_point<HT, EXACT, false>(a, c, nullptr, c.r0 + r, c.c0 + q, cand);
             const double sc = score_reachable<HT, EXACT, false>(a, c, j, nullptr, cand, c.r0 + r, c.c0 + q, sten, moving);
@@ -639,8 +713,8 @@ __device__ __forceinline__ void window_passes(const Args &a, const Ctx &c, const
     }
 }
 
-template <typename HT>
-__global__ void __launch_bounds__(WTHREADS, 8) k_tamols_window(const Args a) {
+template <typename HT, int WTHREADS>
+__global__ void __launch_bounds__(WTHREADS, 1024 / WTHREADS) k_tamols_window(const Args a) {
     __shared__ __align__(8) tamols_leg_job s_job;
     __shared__ GridInv s_inv;
     __shared__ Stencil s_sten;
@@ -663,28 +737,34 @@ __global__ void __launch_bounds__(WTHREADS, 8) k_tamols_window(const Args a) {
     c.map_base = (long long)c.map * a.rows * a.pitch;
     c.ox = j.origin[0]; c.oy = j.origin[1];
     c.rax = j.row_axis[0]; c.ray = j.row_axis[1]; c.cax = j.col_axis[0]; c.cay = j.col_axis[1];
-    if (t == 32) {
+    if (t == 0) {
         const double r2 = c.rax * c.rax + c.ray * c.ray, c2 = c.cax * c.cax + c.cay * c.cay;
         s_inv.arx = c.rax / r2; s_inv.ary = c.ray / r2; s_inv.acx = c.cax / c2; s_inv.acy = c.cay / c2;
     }
-    if (t >= 64 && t < 73) {  // nearest-cell offsets of the nine patch points (Stencil), as in k_tamols_score
-        const int q = t - 64, i = q / 3 - 1, k = q % 3 - 1;
+    if (t >= 32 && t < 41) {  // nearest-cell offsets of the nine patch points (Stencil), as in k_tamols_score
+        const int q = t - 32, i = q / 3 - 1, k = q % 3 - 1;
         const double r2 = c.rax * c.rax + c.ray * c.ray, c2 = c.cax * c.cax + c.cay * c.cay;
         const double dx = (double)i * a.p.gradient_delta, dy = (double)k * a.p.gradient_delta;
         const double gr = dx * (c.rax / r2) + dy * (c.ray / r2), gc = dx * (c.cax / c2) + dy * (c.cay / c2);
         const int ir = __double2int_rn(gr), ic = __double2int_rn(gc);
         s_sten.dr[q] = ir;
         s_sten.dc[q] = ic;
+        s_sten.off[q] = ir * a.pitch + ic;
         const bool tie = fabs(fabs(gr - (double)ir) - 0.5) < 1e-6 || fabs(fabs(gc - (double)ic) - 0.5) < 1e-6;
         const unsigned any = __ballot_sync(0x1ffu, tie);
-        if (q == 0) s_sten.exact = (any != 0u || TAMOLS_EXACT_LOOKUPS) ? 1 : 0;
+        const int rmax = __reduce_max_sync(0x1ffu, abs(ir)), cmax = __reduce_max_sync(0x1ffu, abs(ic));
+        if (q == 0) {
+            s_sten.exact = (any != 0u || TAMOLS_EXACT_LOOKUPS) ? 1 : 0;
+            s_sten.rmax = rmax;
+            s_sten.cmax = cmax;
+        }
     }
     __syncthreads();
     c.arx = s_inv.arx; c.ary = s_inv.ary; c.acx = s_inv.acx; c.acy = s_inv.acy;
     double s;
     int idx, nfin;
-    if (s_sten.exact != 0) window_passes<HT, true>(a, c, j, s_sten, s_list, &s_nlist, job, s, idx, nfin);
-    else window_passes<HT, false>(a, c, j, s_sten, s_list, &s_nlist, job, s, idx, nfin);
+    if (s_sten.exact != 0) window_passes<HT, true, WTHREADS>(a, c, j, s_sten, s_list, &s_nlist, job, s, idx, nfin);
+    else window_passes<HT, false, WTHREADS>(a, c, j, s_sten, s_list, &s_nlist, job, s, idx, nfin);
     // ---- block reduction: lexicographic (score, index) minimum = first minimum in row-major order
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -995,13 +1075,16 @@ static bool get_tensor_map(tamols_handle *h, const void *d_heights, int dtype, i
 
 // k_tamols_window (one block per job) once the jobs alone fill the GPU several times over; k_tamols_score (a job's
 // window split into tiles over many SMs) for the latency regime.  Same results either way.
-static bool use_window_kernel(const tamols_handle *h, int n_jobs) {
+static bool use_window_kernel(const tamols_handle *h, int n_jobs, int max_nc) {
+    if (max_nc > WBAND) return false;  // a band is at least one whole row of 16-bit offsets
     if (h->env_kernel) return h->env_kernel == 2;
     return n_jobs >= 4 * h->num_sms;
 }
 static int launch_window(tamols_handle *h, const Args &a, int dtype) {
-    if (dtype == TAMOLS_F64) k_tamols_window<double><<<a.n_jobs, WTHREADS, 0, h->stream>>>(a);
-    else k_tamols_window<float><<<a.n_jobs, WTHREADS, 0, h->stream>>>(a);
+    // 128 threads, 8 blocks per SM.  Measured alternatives (8192 jobs, 64 x 64 windows, B200): 64 threads 530 us,
+    // 128 threads at 6 / 8 / 10 blocks per SM (80 / 64 / 48 registers) 487 / 436 / 435 us.
+    if (dtype == TAMOLS_F64) k_tamols_window<double, 128><<<a.n_jobs, 128, 0, h->stream>>>(a);
+    else k_tamols_window<float, 128><<<a.n_jobs, 128, 0, h->stream>>>(a);
     TCU(cudaGetLastError());
     h->launches += 1;
     return TAMOLS_OK;
@@ -1018,7 +1101,7 @@ static int launch_score(tamols_handle *h, const void *d_heights, int dtype, int 
     // which finishes without the partial / ticket / merge round trips
     if (max_nr <= 32 && max_nc <= TW && max_nr * max_nc <= THREADS && max_nr > 8) th = 32;
     if (h->env_tile_rows) th = h->env_tile_rows;
-    if (use_window_kernel(h, n_jobs)) {  // no tiles: no partials, tickets or tensor map
+    if (use_window_kernel(h, n_jobs, max_nc)) {  // no tiles: no partials, tickets or tensor map
         Args a;
         a.p = h->p;
         a.k = h->derived;

@@ -11,7 +11,7 @@ tools/ubench > $out/${tag}_ubench.txt 2>&1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $out/${tag}_launches_bench.csv python bench.py --steps 5 --warmup 3 --no-cpu --no-parity > $out/${tag}_ncu_launch.log 2>&1
 for what in c2 c5 tamols; do
   python tools/profile_target.py $what 3 > /dev/null 2>&1 || echo "profile target $what failed"
-  ncu --set full --clock-control none --import-source on -k regex:"k_rollout|k_tamols_score" -s 2 -c 1 -o $out/${tag}_$what -f python tools/profile_target.py $what 3 > $out/${tag}_ncu_$what.log 2>&1
+  ncu --set full --clock-control none --import-source on -k regex:"k_rollout|k_tamols_" -s 2 -c 1 -o $out/${tag}_$what -f python tools/profile_target.py $what 3 > $out/${tag}_ncu_$what.log 2>&1
   ncu -i $out/${tag}_$what.ncu-rep --page details > $out/${tag}_ncu_details_$what.txt
   ncu -i $out/${tag}_$what.ncu-rep --page raw --csv > $out/${tag}_ncu_raw_$what.csv
   ncu -i $out/${tag}_$what.ncu-rep --page source --csv --print-source=sass > $out/${tag}_source_$what.csv
