@@ -46,7 +46,7 @@ HYQREAL1 = dict(mass=108.40, inertia=np.array([[4.55031444e+00, 2.75249434e-03, 
 N_ROLLOUTS = 10000
 FLOP_PER_ROLLOUT = {"zero_order": 4380, "linear_spline": 4956, "cubic_spline": 7260, "cubic_spline_ga": 7550}
 WORKLOAD = "C2: go2 bound, MPPI, cubic_spline (P=96), per-sample step-frequency adaptation, 10000 rollouts x horizon 12"
-PROFILE_TAG = "r5"  # profiles/<tag>_ncu_raw_{c2,c5,tamols}.csv: the ncu captures roofline.traffic is read from
+PROFILE_TAG = "r6"  # profiles/<tag>_ncu_raw_{c2,c5,tamols}.csv: the ncu captures roofline.traffic is read from
 
 # BASELINE.json configs[0..2]: robot constants, body height, hip offsets, gait (offsets, freq, duty)
 CONFIGS = {
@@ -109,6 +109,16 @@ def ncu_traffic(what):
         return int(total), os.path.relpath(path, ROOT)
     except Exception:  # noqa: BLE001
         return None, None
+
+
+def ncu_metrics(what, names):
+    """{metric: value} of ONE launch from the committed ncu capture (same file as ncu_traffic), {} when it is absent."""
+    path = os.path.join(ROOT, "profiles", f"{PROFILE_TAG}_ncu_raw_{what}.csv")
+    try:
+        rows = list(csv.reader(open(path)))
+        return {k: float(rows[2][rows[0].index(k)]) for k in names if k in rows[0]}
+    except Exception:  # noqa: BLE001
+        return {}
 
 
 # ------------------------------------------------------------------------------------------- reference arm (CPU)
@@ -739,6 +749,8 @@ def run_tamols(torch, dev, local_rank, rank, world, barrier, max_over_ranks, wit
     ms = timed(h, lambda: h.score_device(d_h.data_ptr(), tc.F64, 1, 2048, 2048, 2048, d_jobs.data_ptr(), 4 * R, w, w,
                                          d_res.data_ptr()), 20)
     launches = h.launch_count
+    tamols_kernel = {"window": "k_tamols_window<double,128> (one block per job, whole window)",
+                     "tile32": "k_tamols_score<double,TMA,32-row tiles>", "tile8": "k_tamols_score<double,TMA,8-row tiles>"}[h.last_kernel]
     # ---- robot states -> seed footholds -> job records -> scores, all on the device (two launches)
     from quadruped_pympc_tamols_b200.helpers.foothold_reference_generator import FootholdReferenceGenerator
     prng = np.random.default_rng(17 + rank)
@@ -780,10 +792,14 @@ def run_tamols(torch, dev, local_rank, rank, world, barrier, max_over_ranks, wit
                       "candidates_per_s": cand / (step_ms * 1e-3), "scaling": "strong", "gpu_launches_per_step": 1,
                       "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
                                    "traffic": traffic, "traffic_source": tsrc and f"{tsrc} (dram read + write bytes per launch: the 2048x2048 f64 map once)",
-                                   "kernel": "k_tamols_score<double,TMA,32-row tiles>", "launch_ms": float(ms.mean()),
+                                   "kernel": tamols_kernel, "launch_ms": float(ms.mean()),
+                                   "ncu": dict(ncu_metrics("tamols", ["sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active",
+                                                                      "smsp__issue_active.avg.pct_of_peak_sustained_active",
+                                                                      "smsp__inst_executed.sum"]),
+                                               source=f"profiles/{PROFILE_TAG}_ncu_raw_tamols.csv (one launch under ncu --set full)"),
                                    "ms_per_step": step_ms, "n_gpus": world, "candidates_per_s": cand / (step_ms * 1e-3),
                                    "algorithmic_bytes_per_candidate": 8, "peak_source": peak_src,
-                                   "note": "FP64 arithmetic binds long before HBM (windows overlap in L2: measured dram traffic is 8x below the algorithmic bytes); see DESIGN.md"}}
+                                   "note": "FP64 arithmetic binds long before HBM (windows overlap in L2: measured dram traffic is 8x below the algorithmic bytes): the binding resource is in `ncu` (FP64 pipe and issue slots, % of peak); see DESIGN.md"}}
     out["launch_count_check"] = int(launches)
 
     # ---- e2e: one compute_adaptation-sized call (C3-T: 4 legs x 13 x 7 sensor maps) through tamols_score_host

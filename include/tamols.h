@@ -96,6 +96,11 @@ int tamols_set_params(tamols_handle *h, const tamols_params *params);
 const char *tamols_last_error(void);
 void *tamols_stream(tamols_handle *h);
 int64_t tamols_launch_count(const tamols_handle *h);
+/* Which kernel the last scoring launch of this handle ran: "window" (k_tamols_window, one block per job: batched
+ * launches of at least 4 jobs per SM), "tile32" / "tile8" (k_tamols_score, a job's window split into 32- or 8-row tiles
+ * over many SMs: the latency regime), "" before the first launch.  Measurement hook (bench.py, tests); TAMOLS_KERNEL =
+ * tile | window in the environment overrides the choice when the handle is created.  Same result bits either way. */
+const char *tamols_last_kernel(const tamols_handle *h);
 
 /*
  * The candidate loop of compute_adaptation (:164-228) for n_jobs legs in ONE launch, device buffers in and out,

@@ -69,7 +69,7 @@ class TamolsSeedBatch(C.Structure):  # include/tamols.h: tamols_seed_batch
 STATIC_MAX_JOBS, STATIC_MAX_PARTIALS = 4096, 65536  # include/tamols.h TAMOLS_STATIC_MAX_*
 
 EXPORTS = ["tamols_create", "tamols_destroy", "tamols_set_params", "tamols_last_error", "tamols_stream",
-           "tamols_launch_count", "tamols_score_device", "tamols_score_device_static", "tamols_score_host", "tamols_seed_jobs", "tamols_fit_grid", "tamols_score_sensors"]
+           "tamols_launch_count", "tamols_last_kernel", "tamols_score_device", "tamols_score_device_static", "tamols_score_host", "tamols_seed_jobs", "tamols_fit_grid", "tamols_score_sensors"]
 
 
 def make_params(tamols_params=None, robot_name="aliengo"):
@@ -132,6 +132,8 @@ def lib():
         L.tamols_stream.restype = vp
         L.tamols_launch_count.argtypes = [vp]
         L.tamols_launch_count.restype = C.c_int64
+        L.tamols_last_kernel.argtypes = [vp]
+        L.tamols_last_kernel.restype = C.c_char_p
         L.tamols_score_device.argtypes = [vp, vp, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, vp, vp,
                                           C.c_int32, C.c_int32, C.c_int32, vp, vp, C.c_int64]
         L.tamols_score_device_static.argtypes = L.tamols_score_device.argtypes
@@ -171,6 +173,10 @@ class Handle:
     @property
     def launch_count(self):
         return lib().tamols_launch_count(self._h)
+
+    @property
+    def last_kernel(self):
+        return lib().tamols_last_kernel(self._h).decode()
 
     def set_params(self, params: TamolsParams):
         self.params = params

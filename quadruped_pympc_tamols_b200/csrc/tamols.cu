@@ -957,12 +957,14 @@ struct tamols_handle {
     unsigned int seq;
     int env_tile_rows;  // TAMOLS_TILE_ROWS (0 = automatic) and TAMOLS_ZEROCOPY, read from the environment once per
     int env_zerocopy;   // handle: a getenv per call is measurable on a 30 us path
+    const char *last_kernel;  // "window" | "tile32" | "tile8": what the last scoring launch ran (tamols_last_kernel)
     int env_kernel;     // TAMOLS_KERNEL: 0 automatic, 1 "tile" (k_tamols_score), 2 "window" (k_tamols_window)
 };
 
 extern "C" const char *tamols_last_error(void) { return g_terr.c_str(); }
 extern "C" void *tamols_stream(tamols_handle *h) { return h ? (void *)h->stream : nullptr; }
 extern "C" int64_t tamols_launch_count(const tamols_handle *h) { return h ? h->launches : 0; }
+extern "C" const char *tamols_last_kernel(const tamols_handle *h) { return h && h->last_kernel ? h->last_kernel : ""; }
 
 static int check_params(const tamols_params *p) {
     if (!p) return tfail(TAMOLS_E_ARG, "null params");
@@ -1087,6 +1089,7 @@ static int launch_window(tamols_handle *h, const Args &a, int dtype) {
     else k_tamols_window<float, 128><<<a.n_jobs, 128, 0, h->stream>>>(a);
     TCU(cudaGetLastError());
     h->launches += 1;
+    h->last_kernel = "window";
     return TAMOLS_OK;
 }
 
@@ -1143,6 +1146,7 @@ static int launch_score(tamols_handle *h, const void *d_heights, int dtype, int 
 #undef TAMOLS_LAUNCH
     TCU(cudaGetLastError());
     h->launches += 1;
+    h->last_kernel = th == 32 ? "tile32" : "tile8";
     return TAMOLS_OK;
 }
 
@@ -1245,6 +1249,7 @@ extern "C" int tamols_score_device_static(tamols_handle *h, const void *d_height
 #undef TAMOLS_LAUNCH
     TCU(cudaGetLastError());
     h->launches += 1;
+    h->last_kernel = th == 32 ? "tile32" : "tile8";
     return TAMOLS_OK;
 }
 
