@@ -511,7 +511,7 @@ def run_cuda(args):
                 "steps": K, "warmup": W, "ms_per_step": float(total_ms / K), "p50_latency_ms": float(np.median(dev_ms)),
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": line_config(),
-                "notes": {"noise": "in-kernel: Philox4x32-7 seed + xoshiro128+ burst per 12 values, Box-Muller on the SFU (stream v2)",
+                "notes": {"noise": "in-kernel: one Philox4x32-7 seed per 24 values + xoroshiro64+ bursts of 12, Box-Muller on the SFU (stream v3)",
                           "scaling": "the headline is one C2 robot per rank (weak); roofline.c5 carries the sharded 8192-robot step (strong) at this N"},
                 "e2e": {"value": e2e_value, "unit": "rollouts/s", "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": out_bytes,
                         "p50_latency_ms": float(np.median(e2e) * 1e3), "p99_latency_ms": float(np.percentile(e2e, 99) * 1e3),

@@ -9,7 +9,7 @@ jax-CPU, :43-48).
 
 Differences a caller can observe, all forced by the absence of jax: arrays come back as numpy float32 instead of jax
 arrays; `master_key` is a (seed, offset) Philox key instead of a threefry key (any object works upstream as long as
-`with_newkey` advances it); the random stream is Philox4x32-10, so individual samples differ from jax's while their
+`with_newkey` advances it); the random stream is this library's own (Philox4x32-7 seeds + xoroshiro64+ bursts, csrc/philox.cuh), so individual samples differ from jax's while their
 distribution is the same (parity is checked by feeding identical noise to both sides, tests/test_sampling_parity_gpu.py).
 """
 import sys

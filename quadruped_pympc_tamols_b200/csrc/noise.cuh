@@ -1,4 +1,4 @@
-// additional_random_parameters of the sampling controllers, drawn in blocks of 12 values (philox.cuh, stream v2).
+// additional_random_parameters of the sampling controllers, drawn in blocks of 12 values (philox.cuh, stream v3).
 //   random_sampling centroidal_nmpc_jax.py:647-677 (the two Gaussian thirds share ONE key upstream, hence the same
 //   normals scaled by sigma[0] and sigma[1]; the last third is U(-sigma[2], sigma[2]));
 //   mppi :806-812; cem_mppi :951-958 (normals * sigma vector).  Row 0 is always zero.
@@ -96,12 +96,24 @@ typedef float2 v2;
 // The last multiplication of a value and the addition of `best` are ONE fused multiply-add, written out: ptxas
 // contracts mul.rn.f32x2 + add.rn.f32x2 pairs regardless of the rounding modifier (12.9), so leaving them apart would
 // not keep them apart.  par therefore carries one rounding fewer than best + eps of the dumped noise (<= 1 ulp of par).
+// carry (optional, two elements): a caller that draws blocks 0, 1, 2, ... of the two rows IN ORDER passes the same
+// array every time; the even block seeds both blocks of its pair and leaves the odd one's seed there (one Philox per
+// 24 values instead of one per 12).
 template <bool NS, class SigmaAt>
 __device__ __forceinline__ void noise_block_pair(const RowNoise &ra, const RowNoise &rb, const NoiseKey &nk, int b,
                                                  uint32_t robot, const float best[NOISE_BLOCK], v2 par[NOISE_BLOCK],
-                                                 SigmaAt sigma_at) {
-    BlockRng ga = block_rng(nk, ra.stream, (uint32_t)b, ra.sample, robot);
-    BlockRng gb = block_rng(nk, rb.stream, (uint32_t)b, rb.sample, robot);
+                                                 SigmaAt sigma_at, BlockRng *carry = nullptr) {
+    BlockRng ga, gb;
+    if (carry == nullptr) {
+        ga = block_rng(nk, ra.stream, (uint32_t)b, ra.sample, robot);
+        gb = block_rng(nk, rb.stream, (uint32_t)b, rb.sample, robot);
+    } else if ((b & 1) == 0) {
+        block_rng_both(nk, ra.stream, (uint32_t)b >> 1, ra.sample, robot, ga, carry[0]);
+        block_rng_both(nk, rb.stream, (uint32_t)b >> 1, rb.sample, robot, gb, carry[1]);
+    } else {
+        ga = carry[0];
+        gb = carry[1];
+    }
     const float2 k2 = f2(ra.k, rb.k);
     const bool ua = ra.mode == 1, ub = rb.mode == 1;
     const float2 wid = f2(__fmul_rn(2.0f, ra.k), __fmul_rn(2.0f, rb.k)), lo = f2(-ra.k, -rb.k);

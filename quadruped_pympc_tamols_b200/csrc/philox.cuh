@@ -1,21 +1,26 @@
-// Random bits of the sampling controllers: Philox4x32 (counter-based) seeds, xoshiro128+ bursts, Box-Muller on the SFU.
+// Random bits of the sampling controllers: Philox4x32 (counter-based) seeds, xoroshiro64+ bursts, Box-Muller on the SFU.
 //
 // Replaces the reference's jax.random.normal / uniform / choice draws
 // (quadruped_pympc/controllers/sampling/centroidal_nmpc_jax.py:647-677, 806-812, 951-958 and
 //  centroidal_nmpc_jax_gait_adaptive.py:687-692, 834-838, 994-999).  jax's threefry bit stream cannot be
 // reproduced without jax, so parity is checked by handing the SAME noise to the oracle (qpmpc_generate_noise).
 //
-// Noise stream "v2" (this repo's own definition; qpmpc_version() carries the tag).  The P parameters of a rollout are
-// drawn in BLOCKS of 12 values (P is a multiple of 12 for every parametrisation: 12 H, 12 (S + 1), 48 S).  Block b of
-// sample i of robot r under key (seed, offset) is
-//     state = Philox4x32-7(counter = (b | stream << 28, i, r, offset), key = seed)      -- random access, 128 bits
-//     w_0 .. w_11 = the first 12 outputs of xoshiro128+ started from that state          -- a short sequential burst
-// and pair m of the block is the Box-Muller transform of (w_2m, w_2m+1) (uniform rows: value j from w_j).
-// Why not one Philox block per four values as in v1: measured on B200 (tools/ubench.cu, profiles/r5_ubench.txt) the
-// 32 x 32 -> 64 multiply IMAD.WIDE issues once per ~4.5 cycles per scheduler and sits on the SAME pipe as the FP32
-// work; Philox4x32-10 per four values cost 90 FMA-pipe cycles per group, 3,240 per zero-order rollout, about as much
-// as the whole SRBD integration.  Seven rounds (the Crush-resistant minimum of the Random123 paper) once per TWELVE
-// values cost 63; the xoshiro steps are LOP3 / SHF / IADD on the otherwise lightly loaded ALU pipe.
+// Noise stream "v3" (this repo's own definition; qpmpc_version() carries the tag).  The P parameters of a rollout are
+// drawn in BLOCKS of 12 values (P is a multiple of 12 for every parametrisation: 12 H, 12 (S + 1), 48 S).  Blocks 2 m
+// and 2 m + 1 of sample i of robot r under key (seed, offset) share ONE counter-based seed,
+//     (a, b, c, d) = Philox4x32-7(counter = (m | stream << 28, i, r, offset), key = seed)   -- random access, 128 bits
+// block 2 m starts the 64-bit generator xoroshiro64+ from (a, b), block 2 m + 1 from (c, d), and
+//     w_0 .. w_11 = its first 12 outputs                                                     -- a short sequential burst
+// pair j of the block is the Box-Muller transform of (w_2j, w_2j+1) (uniform rows: value j from w_j).
+// Why: measured on B200 (tools/ubench.cu, profiles/r5_ubench.txt) the 32 x 32 -> 64 multiply IMAD.WIDE issues once
+// per ~4.5 cycles per scheduler and sits on the SAME pipe as the FP32 work; v1 (Philox4x32-10 per four values) cost 90
+// FMA-pipe cycles per group, 3,240 per zero-order rollout, about as much as the whole SRBD integration.  Seven rounds
+// (the Crush-resistant minimum of the Random123 paper) once per TWENTY-FOUR values cost 63 (v2 seeded every twelve);
+// the generator steps are LOP3 / SHF / IADD on the otherwise lightly loaded ALU pipe, six per word (xoroshiro64: the
+// 2 x 32-bit engine of Blackman & Vigna, constants 26 / 9 / 13, with the '+' output -- the weak low bits of a '+'
+// scrambler are the ones the 24-bit float conversion rounds away; v2's xoshiro128+ took seven and four state registers
+// per row).  A rollout that walks its blocks in order (k_rollout_pair) keeps the second half of the seed for the odd
+// block; everything else (parameter columns of the small kernels, re-drawn rows) seeds per block and discards a half.
 // Everything below uses explicit _rn intrinsics and SFU instructions only: nothing depends on the compiler's FMA
 // contraction choices, so the scalar and the packed (two rollouts per thread, f32x2) generators are bit-identical.
 #pragma once
@@ -52,27 +57,30 @@ __device__ __forceinline__ uint4 draw(const NoiseKey &nk, uint32_t stream, uint3
     return philox4x32<10>(ctr, key);
 }
 
-// xoshiro128+ (Blackman & Vigna) on the state a Philox4x32-7 block left: 7 ALU instructions per 32-bit word
+// xoroshiro64+ on one half of the state a Philox4x32-7 block left: 6 ALU instructions per 32-bit word
 struct BlockRng {
-    uint32_t s0, s1, s2, s3;
+    uint32_t s0, s1;
 };
-__device__ __forceinline__ BlockRng block_rng(const NoiseKey &nk, uint32_t stream, uint32_t block, uint32_t sample,
-                                              uint32_t robot) {
-    const uint4 ctr = make_uint4(block | (stream << 28), sample, robot, (uint32_t)nk.offset);
+// the seeds of blocks 2 m (first) and 2 m + 1 (second)
+__device__ __forceinline__ void block_rng_both(const NoiseKey &nk, uint32_t stream, uint32_t m, uint32_t sample, uint32_t robot,
+                                               BlockRng &first, BlockRng &second) {
+    const uint4 ctr = make_uint4(m | (stream << 28), sample, robot, (uint32_t)nk.offset);
     const uint2 key = make_uint2((uint32_t)nk.seed, (uint32_t)(nk.seed >> 32) ^ (uint32_t)(nk.offset >> 32));
     const uint4 s = philox4x32<7>(ctr, key);
-    return BlockRng{s.x, s.y, s.z, s.w};
+    first = BlockRng{s.x, s.y};
+    second = BlockRng{s.z, s.w};
+}
+__device__ __forceinline__ BlockRng block_rng(const NoiseKey &nk, uint32_t stream, uint32_t block, uint32_t sample,
+                                              uint32_t robot) {
+    BlockRng first, second;
+    block_rng_both(nk, stream, block >> 1, sample, robot, first, second);
+    return (block & 1u) ? second : first;
 }
 __device__ __forceinline__ uint32_t rng_next(BlockRng &g) {
-    const uint32_t out = g.s0 + g.s3;
-    const uint32_t t = g.s1 << 9;
-    const uint32_t x3 = g.s3 ^ g.s1;
-    const uint32_t n1 = g.s1 ^ g.s2 ^ g.s0;
-    const uint32_t n0 = g.s0 ^ x3;
-    g.s2 = g.s2 ^ g.s0 ^ t;
-    g.s3 = __funnelshift_l(x3, x3, 11);
-    g.s1 = n1;
-    g.s0 = n0;
+    const uint32_t out = g.s0 + g.s1;
+    const uint32_t x = g.s1 ^ g.s0;
+    g.s0 = __funnelshift_l(g.s0, g.s0, 26) ^ x ^ (x << 9);
+    g.s1 = __funnelshift_l(x, x, 13);
     return out;
 }
 

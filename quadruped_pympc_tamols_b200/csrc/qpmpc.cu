@@ -1088,6 +1088,7 @@ __global__ void __launch_bounds__(T, 3) k_rollout_pair(const __grid_constant__ D
             ea = a.eps + ((size_t)r * a.n + (va ? ia : base)) * P;
             eb = a.eps + ((size_t)r * a.n + (vb ? ib : base)) * P;
         }
+        BlockRng carry[2] = {{0u, 0u}, {0u, 0u}};  // seeds of the odd block of the current pair (noise.cuh)
 #pragma unroll 1
         for (int n = 0; n < H; ++n) {
             v2 f[NOISE_BLOCK];
@@ -1099,7 +1100,7 @@ __global__ void __launch_bounds__(T, 3) k_rollout_pair(const __grid_constant__ D
 #pragma unroll
                 for (int k = 0; k < NOISE_BLOCK; ++k) f[k] = vadd(f2(ea[k * H + n], eb[k * H + n]), bst[k]);
             } else {
-                noise_block_pair<MODE == 0>(rna, rnb, a.key, n, robot, bst, f, [&](int k) { return s_sg[NOISE_BLOCK * n + k]; });
+                noise_block_pair<MODE == 0>(rna, rnb, a.key, n, robot, bst, f, [&](int k) { return s_sg[NOISE_BLOCK * n + k]; }, carry);
             }
             const float4 st4 = *reinterpret_cast<const float4 *>(s_st + 8 * n);
             const float4 st34 = *reinterpret_cast<const float4 *>(s_st + 8 * n + 4);
@@ -1696,7 +1697,7 @@ static rollout_fn pick_fn(qpmpc_handle *h, const LaunchPlan &pl, bool eps) {
 extern "C" const char *qpmpc_last_error(void) { return g_err.c_str(); }
 #define QPMPC_STR2(x) #x
 #define QPMPC_STR(x) QPMPC_STR2(x)
-extern "C" const char *qpmpc_version(void) { return "qpmpc-b200 0.2 noise-v2 (sm_100a, cudart " QPMPC_STR(CUDART_VERSION) ")"; }
+extern "C" const char *qpmpc_version(void) { return "qpmpc-b200 0.2 noise-v3 (sm_100a, cudart " QPMPC_STR(CUDART_VERSION) ")"; }
 
 extern "C" int qpmpc_create(const qpmpc_config *cfg, qpmpc_handle **out) {
     if (!cfg || !out) return fail(QPMPC_E_ARG, "null argument");

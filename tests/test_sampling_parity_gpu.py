@@ -227,6 +227,33 @@ def test_noise_statistics_and_structure():
         h.close()
 
 
+def test_noise_stream_independence():
+    """Stream v3 (csrc/philox.cuh) seeds the blocks 2 m and 2 m + 1 of a row from the two halves of ONE Philox4x32-7
+    output and runs a 64-bit generator for twelve words from each: the values of a row must still be independent of
+    each other (also across the two blocks of a pair), consecutive rows independent, and the marginal normal."""
+    from scipy import stats
+    mass, inertia, _, _ = ROBOTS["aliengo"]
+    n = 20001
+    h = _cabi.Handle(_cabi.make_config(mass=mass, inertia=inertia, sampling_method="mppi", parametrization="zero_order",
+                                       num_parallel_computations=n))
+    d_eps = torch.empty((n, h.P), dtype=torch.float32, device="cuda")
+    h.generate_noise(11, 5, d_eps.data_ptr())
+    z = d_eps.cpu().numpy().astype(np.float64)[1:] / 3.0
+    h.close()
+    m = z.shape[0]
+    corr = np.corrcoef(z.T)
+    off = np.abs(corr - np.eye(h.P)).max()
+    assert off < 5.5 / np.sqrt(m), off  # 10,296 pairs: the expected maximum is 4.3 / sqrt(m)
+    lag = max(abs(np.corrcoef(z[:-1, p], z[1:, p])[0, 1]) for p in range(h.P))
+    assert lag < 5.0 / np.sqrt(m), lag
+    sq = np.abs(np.corrcoef((z ** 2).T) - np.eye(h.P)).max()  # dependence the linear correlation would miss
+    assert sq < 5.5 / np.sqrt(m), sq
+    d_all = stats.kstest(z.ravel(), "norm").statistic
+    assert d_all < 1.95 / np.sqrt(z.size), d_all  # the 0.1 % critical value of the pooled 2.9 M values
+    worst = min(stats.kstest(z[:, p], "norm").pvalue for p in range(h.P))
+    assert worst > 1e-5, worst  # 144 columns: the smallest p-value of 144 uniform draws is ~0.007
+
+
 @pytest.mark.parametrize("method", ["mppi", "cem_mppi", "random_sampling"])
 @pytest.mark.parametrize("param", ["zero_order", "cubic_spline"])
 def test_packed_generator_equals_scalar_generator(monkeypatch, method, param):
