@@ -268,6 +268,23 @@ class SolveBench:
             (barrier or torch.cuda.synchronize)()
         return np.array([a.elapsed_time(b) for a, b in ev]), self.h.launch_count - launches0
 
+    def event_floor(self, K, flush):
+        """What the device-timing method itself reads for a kernel that does nothing: the same event pair on the same
+        stream, the same L2 flush ahead of it, around a one-block torch kernel (launch + event record latencies)."""
+        torch = self.torch
+        one = torch.zeros(32, device=self.dev)
+        with torch.cuda.stream(self.stream):
+            ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+            for it in range(K + 10):
+                flush.fill_(it & 0xFF)
+                if it >= 10:
+                    ev[it - 10][0].record(self.stream)
+                one.add_(1.0)
+                if it >= 10:
+                    ev[it - 10][1].record(self.stream)
+            torch.cuda.synchronize()
+        return float(np.median([a.elapsed_time(b) for a, b in ev]))
+
     def time_e2e(self, K, W):
         """qpmpc_solve / qpmpc_solve_iterated with host buffers, wall clock around the Python-level call."""
         best = np.zeros(self.P, np.float32)
@@ -384,6 +401,7 @@ def run_cuda(args):
     total_ms = max_over_ranks(float(dev_ms.sum()))
     value = N_ROLLOUTS * K * world / (total_ms * 1e-3)
     c2_kernel = h.last_kernel
+    floor_ms = c2.event_floor(min(K, 100), flush)
 
     # roofline of the dominant kernel: events around each kernel inside the solve
     h.set_profiling(True)
@@ -509,6 +527,10 @@ def run_cuda(args):
                     "c5": batched and batched["roofline_c5"], "tamols": tamols and tamols["batched"]["roofline"]}
         line = {"metric": "rollouts/sec at 10k samples (one MPPI solve)", "value": value, "unit": "rollouts/s", "n_gpus": world,
                 "steps": K, "warmup": W, "ms_per_step": float(total_ms / K), "p50_latency_ms": float(np.median(dev_ms)),
+                "device_timing": {"event_pair_floor_p50_ms": floor_ms,
+                                  "solve_p50_minus_floor_ms": float(np.median(dev_ms)) - floor_ms,
+                                  "note": "floor = the same CUDA-event pair, stream and L2 flush around a one-block kernel: launch + "
+                                          "event-record latency that every device-timed step carries; value / ms_per_step include it"},
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": line_config(),
                 "notes": {"noise": "in-kernel: one Philox4x32-7 seed per 24 values + xoroshiro64+ bursts of 12, Box-Muller on the SFU (stream v3)",
