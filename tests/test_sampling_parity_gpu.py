@@ -196,6 +196,57 @@ def test_philox_solve_matches_oracle_on_same_noise(robot, gait, method, param, g
     h.close()
 
 
+@pytest.mark.parametrize("case", ["ties_at_the_threshold", "all_costs_saturated", "few_blocks"])
+def test_cem_elite_selection_ties_and_fallback(case, kernel):
+    """The CEM elites are argsort(costs)[:10] with a STABLE sort (centroidal_nmpc_jax.py:1075): ties go to the lower
+    index.  finalize_robot first bounds the 10th smallest cost by the 10th smallest block minimum and ranks the few
+    costs below that bound; it falls back to the radix select when there are fewer blocks than elites or too many
+    candidates.  Supplied noise builds the hard cases: the row of rank 6 copied into 40 rows of 40 different blocks (the
+    common cost straddles rank 10), every cost saturated at 1e6 (NaN state: the elites are rows 0..9, through the fallback's tie
+    bisection), and a solve of 300 rollouts (fewer blocks than elites)."""
+    rng = np.random.default_rng({"ties_at_the_threshold": 1, "all_costs_saturated": 2, "few_blocks": 3}[case])
+    mass, inertia, _, _ = ROBOTS["hyqreal1"]
+    n = 300 if case == "few_blocks" else 10000
+    kw = dict(mass=mass, inertia=np.array(inertia), parametrization="cubic_spline", gait_adaptive=False)
+    h = _cabi.Handle(_cabi.make_config(sampling_method="cem_mppi", num_parallel_computations=n, **kw))
+    ocfg = so.make_cfg(**kw)
+    P = h.P
+    st, ref, seq, timing, nominal = synth_problem("hyqreal1", "pace", rng)
+    best = np.zeros(P, np.float32)
+    sigma = np.full(P, 3.0, np.float32)
+    eps = (rng.normal(size=(n, P)) * sigma).astype(np.float32)
+    eps[0] = 0
+    if case == "ties_at_the_threshold":
+        # the row of rank 6 copied into 40 more rows, in 40 different rollout blocks: 41 equal costs on ranks 6..46
+        o0 = so.solve(ocfg, "cem_mppi", st, ref, seq, best, eps, timing=timing, fast=False)
+        src = int(np.argsort(o0["costs"], kind="stable")[6])
+        dst = np.arange(40) * 211 + 7
+        dst = dst[dst != src]
+        eps[dst] = eps[src]
+    if case == "all_costs_saturated":
+        st = st.copy()
+        st[2] = np.nan
+    d_eps = dev(eps)
+    r = h.solve(st, ref, seq, best, seed=0, offset=0, timing=timing, nominal_freq=nominal, sigma_in=sigma, d_eps=d_eps.data_ptr())
+    o = so.solve(ocfg, "cem_mppi", st, ref, seq, best, eps, timing=timing, fast=False)
+    order = np.argsort(o["costs"], kind="stable")[:10]
+    if case == "ties_at_the_threshold":
+        tied = np.flatnonzero(o["costs"] == o["costs"][src])
+        below = int(np.sum(o["costs"] < o["costs"][src]))
+        assert len(tied) >= 40 and below < 10 < below + len(tied), (len(tied), below)  # the tie group straddles rank 10
+        assert np.array_equal(r["costs"][tied], np.full(len(tied), r["costs"][src]))  # ... on the GPU as well
+    if case == "all_costs_saturated":
+        assert np.all(r["costs"] == 1e6) and np.all(o["costs"] == 1e6) and np.array_equal(order, np.arange(10))
+    else:
+        assert rel_err(r["costs"], o["costs"]) < COST_RTOL
+    # sigma from exactly the oracle's elite rows (float64 restatement of :1075-1081: cov of the rows, sqrt, clip)
+    rows = eps[order].astype(np.float64)
+    want = np.clip(np.sqrt(rows.var(axis=0, ddof=1) + 1e-8), 0.2, 5.0)
+    assert rel_err(r["sigma"], want) < 1e-4
+    assert rel_err(r["sigma"], o["sigma"]) < 1e-3
+    h.close()
+
+
 def test_noise_statistics_and_structure():
     mass, inertia, _, _ = ROBOTS["aliengo"]
     n = 9001
