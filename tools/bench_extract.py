@@ -22,7 +22,7 @@ for f in sys.argv[1:]:
                   f"(whole step {c5.get('frac_whole_step'):.4f}) kernel {c5.get('kernel')}")
             e = (d.get('e2e') or {}).get('c5') or {}
             b = d.get('batched') or {}
-            print(f"  C5 e2e {e.get('ms_per_step')} ms; cpu {(b.get('cpu_baseline') or {}).get('ms_per_step_extrapolated')} ms (extrapolated)")
+            print(f"  C5 e2e {e.get('ms_per_step')} ms (serial {e.get('serial_ms_per_step')}); cpu {(b.get('cpu_baseline') or {}).get('ms_per_step_extrapolated')} ms (extrapolated)")
         if tm:
             print(f"  TAMOLS batched {tm.get('launch_ms'):.4f} ms frac {tm.get('frac'):.4f}")
         for k, v in (d.get('configs') or {}).items():
