@@ -621,10 +621,10 @@ def run_batched(torch, _cabi, dev, local_rank, rank, world, barrier, max_over_ra
     # on) is destroyed: the allocator records an event on that stream when a block is freed
     del p_in, p_res, p_best
     serial_s = max_over_ranks(float(np.mean(wall)))
-    # the same step through the package's host-buffer solver: robots in 8 chunks alternating between two handles /
+    # the same step through the package's host-buffer solver: robots in up to 8 chunks (at least 1,024 robots each) alternating between two handles /
     # streams, chunk k's copies overlapping chunk k - 1's rollouts (quadruped_pympc_tamols_b200/batched_host.py)
     from quadruped_pympc_tamols_b200.batched_host import BatchedHostSolver
-    hs = BatchedHostSolver(R, chunks=8, device=local_rank, robot_offset=lo, sampling_method="mppi", parametrization="zero_order",
+    hs = BatchedHostSolver(R, device=local_rank, robot_offset=lo, sampling_method="mppi", parametrization="zero_order",
                            num_parallel_computations=n, **ALIENGO)
     hs.np_in["state"][...], hs.np_in["reference"][...], hs.np_in["contact"][...] = h_state, h_ref, h_seq
     wall = []
@@ -638,13 +638,14 @@ def run_batched(torch, _cabi, dev, local_rank, rank, world, barrier, max_over_ra
             wall.append(time.perf_counter() - t0)
     barrier()
     h2d_b, d2h_b = hs.io_bytes()
+    hs_chunks = len(hs.bounds)
     hs_launches = hs.launch_count // (3 + steps)
     hs.close()
     e2e_s = max_over_ranks(float(np.mean(wall)))
     e2e = {"workload": f"C5 through host buffers: {robots_total} robots x {n} rollouts; {R} robots per rank",
            "value": robots_total * n / e2e_s, "unit": "rollouts/s", "ms_per_step": e2e_s * 1e3,
            "h2d_bytes_per_step": int(h2d_b), "d2h_bytes_per_step": int(d2h_b), "gpu_launches_per_step": int(hs_launches),
-           "api": "BatchedHostSolver.solve: page-locked host arrays, 8 chunks of robots alternating between two handles / streams "
+           "api": f"BatchedHostSolver.solve: page-locked host arrays, {hs_chunks} chunk(s) of robots alternating between two handles / streams "
                   "(H2D copy, qpmpc_solve_batched, D2H copy per chunk), one synchronise per stream and step",
            "serial_ms_per_step": serial_s * 1e3,
            "serial_api": "one stream: H2D copies -> one qpmpc_solve_batched launch over all robots -> D2H copies -> synchronise"}

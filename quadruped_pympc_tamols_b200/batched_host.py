@@ -22,12 +22,16 @@ from .sharding import shard_bounds
 class BatchedHostSolver:
     """R robots of one configuration.  solve() returns views of pinned host arrays that the next solve() overwrites."""
 
-    def __init__(self, num_robots, chunks=8, device=0, robot_offset=0, **config):
+    def __init__(self, num_robots, chunks=None, device=0, robot_offset=0, **config):
         import torch
         if not torch.cuda.is_available():
             raise _cabi.QpmpcError("BatchedHostSolver needs a CUDA device: this package has no CPU fallback")
         self.torch, self.R, self.robot_offset = torch, int(num_robots), int(robot_offset)
         self.dev = torch.device("cuda", int(device))
+        if chunks is None:
+            # at most 8 chunks of at least 1,024 robots: a chunk's launch should still fill the GPU a few times over
+            # (8 GPUs x 1,024 robots each, 8 chunks of 128: 0.83 ms per step against 0.37 ms unchunked)
+            chunks = min(8, self.R // 1024)
         chunks = max(1, min(int(chunks), self.R))
         self.bounds = [shard_bounds(self.R, chunks, k) for k in range(chunks)]
         cap = max(hi - lo for lo, hi in self.bounds)
