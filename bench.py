@@ -121,6 +121,38 @@ def ncu_metrics(what, names):
         return {}
 
 
+def c_client_latency(_cabi, key, st, ref, seq, timing, nominal, device, solves=2000, warmup=200):
+    """qpmpc_solve timed from a plain C client (tools/c_latency.c, built here with gcc): the C ABI's own end-to-end
+    latency with host buffers, without the ctypes call and the Python-side packing that `e2e` includes.  None when
+    gcc is missing or anything fails (the figure is an annotation, never the headline)."""
+    import shutil
+    import subprocess
+    import tempfile
+    try:
+        if shutil.which("gcc") is None:
+            return None
+        c = CONFIGS[key]
+        cfg = _cabi.make_config(sampling_method=c["method"], parametrization=c["param"], gait_adaptive=c["ga"],
+                                num_parallel_computations=N_ROLLOUTS, device=device, **c["robot"])
+        libdir = os.path.dirname(_cabi.LIB_PATH)
+        with tempfile.TemporaryDirectory() as tmp:
+            exe, prob = os.path.join(tmp, "c_latency"), os.path.join(tmp, "problem.bin")
+            subprocess.run(["gcc", "-std=c99", "-O2", "-I", os.path.join(ROOT, "include"), os.path.join(ROOT, "tools", "c_latency.c"),
+                            "-o", exe, "-L", libdir, "-lqpmpc_b200", "-lm", "-Wl,-rpath," + libdir], check=True, capture_output=True)
+            P = (c["param"] == "zero_order") * 144 + (c["param"] != "zero_order") * 96
+            with open(prob, "wb") as f:
+                f.write(bytes(cfg))
+                for a in (st, ref, seq, np.zeros(P, np.float32), timing, np.array([nominal, 1.0], np.float32)):
+                    f.write(np.ascontiguousarray(a, np.float32).tobytes())
+            r = subprocess.run([exe, prob, str(solves), str(warmup)], check=True, capture_output=True, text=True, timeout=120)
+        p50, p90, p99, lo = (float(x) for x in r.stdout.split())
+        return {"p50_latency_ms": p50 * 1e-3, "p90_latency_ms": p90 * 1e-3, "p99_latency_ms": p99 * 1e-3, "min_latency_ms": lo * 1e-3,
+                "solves": solves, "api": "qpmpc_solve called from plain C (tools/c_latency.c), CLOCK_MONOTONIC around each call"}
+    except Exception as e:  # noqa: BLE001
+        stage(f"C client latency unavailable: {e!r}"[:300])
+        return None
+
+
 # ------------------------------------------------------------------------------------------- reference arm (CPU)
 def cpu_solve_loop(key, steps, warmup, seed=0):
     """The CPU port of compute_control_* on one BASELINE config: noise generation + 10k rollouts + update per solve
@@ -423,6 +455,7 @@ def run_cuda(args):
     in_bytes, out_bytes = c2.io_bytes()
     st, ref, seq, timing, nominal = c2.st, c2.ref, c2.seq, c2.timing, c2.nominal
     best = np.zeros(P, np.float32)
+    c_client = c_client_latency(_cabi, "c2", st, ref, seq, timing, nominal, local_rank) if rank == 0 else None
 
     # ---- num_sampling_iterations = 3 chained on the device (qpmpc_solve_iterated) against three
     # host-level calls (the upstream interface loop)
@@ -537,7 +570,7 @@ def run_cuda(args):
                           "scaling": "the headline is one C2 robot per rank (weak); roofline.c5 carries the sharded 8192-robot step (strong) at this N"},
                 "e2e": {"value": e2e_value, "unit": "rollouts/s", "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": out_bytes,
                         "p50_latency_ms": float(np.median(e2e) * 1e3), "p99_latency_ms": float(np.percentile(e2e, 99) * 1e3),
-                        "class_call_p50_latency_ms": class_p50,
+                        "class_call_p50_latency_ms": class_p50, "c_client": c_client,
                         "api": "qpmpc_solve (host buffers; costs[N] left on the device as upstream)",
                         "transfers": "inputs in the kernel parameter block (host -> device with the launch); results stored by the kernel into mapped pinned host memory as {word, sequence} pairs",
                         "c5": batched and batched["e2e"]},

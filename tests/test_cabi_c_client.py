@@ -39,3 +39,16 @@ def test_c_client_solves_on_gpu(tmp_path):
     r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "best_cost=" in r.stdout and "launches=1" in r.stdout
+
+
+def test_c_latency_client_builds(tmp_path):
+    """tools/c_latency.c (bench.py's e2e.c_client: qpmpc_solve timed from plain C) compiles as strict C99 against the
+    public header and links against the library alone."""
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    if not os.path.exists(os.path.join(LIBDIR, "libqpmpc_b200.so")):
+        import __graft_entry__
+        __graft_entry__.build()
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"),
+                    os.path.join(ROOT, "tools", "c_latency.c"), "-o", str(tmp_path / "c_latency"), "-L", LIBDIR,
+                    "-lqpmpc_b200", "-lm", "-Wl,-rpath," + LIBDIR], check=True, capture_output=True, text=True)

@@ -14,6 +14,9 @@ for f in sys.argv[1:]:
         print(f"{f}: n_gpus {d.get('n_gpus')} impl {d.get('impl', 'cuda')}")
         print(f"  C2 device p50 {d.get('p50_latency_ms')} ms, value {d.get('value'):.4g}, e2e p50 {d['e2e'].get('p50_latency_ms')} ms, "
               f"class {d['e2e'].get('class_call_p50_latency_ms')}, frac {rf.get('frac')}")
+        cc = d['e2e'].get('c_client')
+        if cc:
+            print(f"  C2 e2e from a plain C client: p50 {cc['p50_latency_ms'] * 1e3:.2f} us, p99 {cc['p99_latency_ms'] * 1e3:.2f} us")
         dt = d.get('device_timing')
         if dt:
             print(f"  device timing floor {dt['event_pair_floor_p50_ms'] * 1e3:.2f} us, C2 solve minus floor {dt['solve_p50_minus_floor_ms'] * 1e3:.2f} us")
