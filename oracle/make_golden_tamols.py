@@ -47,10 +47,25 @@ def multi_tile():
     save("c4_go2_stepping_stones_tall_w96", "go2", sy.tamols_params_for("go2"), sc["heights"], xy, sc["jobs"])
 
 
+def half_cell_delta():
+    """gradient_delta = half the cell size on the sensor's (yaw-rotated, offset) 13 x 7 @ 0.04 m maps: the nine patch
+    points sit half a cell from the candidate, so the kernel's tie detection sends the block down the per-point
+    look-up path (Stencil.exact).  On such grids no query is exactly equidistant from two cells and the analytic
+    nearest cell is the KD-tree's.  (On an AXIS-ALIGNED grid with this delta the queries are exactly equidistant; the
+    reference's answer then depends on float64 round-off of the two squared distances and, when those are equal too --
+    61 % of the cases measured -- on scipy's tree traversal: not reproducible by any rule)"""
+    rng = np.random.default_rng(600)
+    sc = sy.robot_scene("go2", rng, "noise", speed=0.4, seed=21, map_offset_sigma=0.05)
+    save("go2_noise_halfcell_delta", "go2", sy.tamols_params_for("go2", gradient_delta=0.02), sc["heights"], sc["xy"],
+         sc["jobs"], sc["contact"])
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     if "--multi-tile-only" in sys.argv:
         return multi_tile()
+    if "--half-cell-only" in sys.argv:
+        return half_cell_delta()
     # C3-T: hyqreal on stepping stones, 13 x 7 @ 0.04 m per-leg maps, trot apex (SURVEY 8(d))
     for k in range(3):
         rng = np.random.default_rng(100 + k)
@@ -95,6 +110,7 @@ def main():
         xy = sy.grid_xy(sc["origin"], sc["row_axis"], sc["col_axis"], 96, 96)[None]
         save(f"c4_go2_{kind}_w32", "go2", sy.tamols_params_for("go2"), sc["heights"], xy, sc["jobs"])
     multi_tile()
+    half_cell_delta()
 
 
 if __name__ == "__main__":
