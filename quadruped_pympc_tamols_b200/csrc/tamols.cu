@@ -617,6 +617,10 @@ struct Gate {
     double h0, h1, h2, v0, v1, v2;
     bool has_vel;
 };
+// window-relative rows / columns outside of which no cell can pass the gate (k_tamols_window's setup)
+struct WinBox {
+    int r0, r1, c0, c1;
+};
 __device__ __forceinline__ bool gate_reachable(const Args &a, const Gate &g, const double cand[3]) {
     double d0 = cand[0] - g.h0, d1 = cand[1] - g.h1, d2 = cand[2] - g.h2;
     const double td2 = (d0 * d0 + d1 * d1) + d2 * d2;
@@ -633,7 +637,8 @@ __device__ __forceinline__ bool gate_reachable(const Args &a, const Gate &g, con
 
 template <typename HT, bool EXACT, int WTHREADS>
 __device__ __forceinline__ void window_passes(const Args &a, const Ctx &c, const tamols_leg_job &j, const Stencil &sten,
-                                              unsigned short *s_list, int *s_nlist, int job, double &s, int &idx, int &nfin) {
+                                              const WinBox &box, unsigned short *s_list, int *s_nlist, int job, double &s,
+                                              int &idx, int &nfin) {
     constexpr int NW = WTHREADS / 32;
     const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
@@ -656,13 +661,19 @@ __device__ __forceinline__ void window_passes(const Args &a, const Ctx &c, const
         // survivors compacted as 16-bit offsets inside the band (order arbitrary, result not)
         // (two copies of the loop: the plain one -- grid coordinates, no per-candidate score output, what a batched
         // launch runs -- keeps the two pointer tests and their address arithmetic out of the 30-odd instructions a cell costs)
+        // plain loop only: rows and 32-cell segments outside the reach circles' bounding box are not visited
+        const int box_r0 = box.r0, box_r1 = box.r1, box_c0 = box.c0, box_c1 = box.c1;  // computed once per job (k_tamols_window)
+        const int seg0 = box_c0 & ~31;  // first 32-cell segment that touches the box
         auto pass1 = [&](auto plain_tag) {
             constexpr bool PLAIN = decltype(plain_tag)::value;
-            for (int r = rb + wid; r < rb + nrb; r += NW) {
+            const int r_first = PLAIN ? max(rb, box_r0) : rb, r_last = PLAIN ? min(rb + nrb - 1, box_r1) : rb + nrb - 1;
+            const int q_first = PLAIN ? seg0 : 0, q_end = PLAIN ? min(c.nc, box_c1 + 1) : c.nc;
+            // (row r of the band goes to warp (r - rb) % NW whatever the box: the compaction order stays arbitrary)
+            for (int r = r_first + ((wid - (r_first - rb)) % NW + NW) % NW; r <= r_last; r += NW) {
                 const int R = c.r0 + r;
                 const double xr = c.ox + (double)R * c.rax, yr = c.oy + (double)R * c.ray;  // candidate_xy's first sum
                 const HT *hrow = hmap + (long long)R * c.pitch + c.c0;
-                for (int q0 = 0; q0 < c.nc; q0 += 32) {
+                for (int q0 = q_first; q0 < q_end; q0 += 32) {
                     const int q = q0 + lane;
                     bool reach = false;
                     if (q < c.nc) {
@@ -718,6 +729,7 @@ __global__ void __launch_bounds__(WTHREADS, 1024 / WTHREADS) k_tamols_window(con
     __shared__ __align__(8) tamols_leg_job s_job;
     __shared__ GridInv s_inv;
     __shared__ Stencil s_sten;
+    __shared__ WinBox s_wbox;
     __shared__ unsigned short s_list[WBAND];
     __shared__ int s_nlist;
     __shared__ double s_rs[WTHREADS / 32];
@@ -739,7 +751,28 @@ __global__ void __launch_bounds__(WTHREADS, 1024 / WTHREADS) k_tamols_window(con
     c.rax = j.row_axis[0]; c.ray = j.row_axis[1]; c.cax = j.col_axis[0]; c.cay = j.col_axis[1];
     if (t == 0) {
         const double r2 = c.rax * c.rax + c.ray * c.ray, c2 = c.cax * c.cax + c.cay * c.cay;
-        s_inv.arx = c.rax / r2; s_inv.ary = c.ray / r2; s_inv.acx = c.cax / c2; s_inv.acy = c.cay / c2;
+        const double arx = c.rax / r2, ary = c.ray / r2, acx = c.cax / c2, acy = c.cay / c2;
+        s_inv.arx = arx; s_inv.ary = ary; s_inv.acx = acx; s_inv.acy = acy;
+        // The cells that can pass the reachability gate lie in the bounding box, in grid coordinates, of the reach
+        // circle(s) -- horizontal distance to the hip (and to hip + vel * stance) at most sqrt(reach_hi2) -- widened by
+        // one cell for the round-off of this estimate: pass 1 of a batched launch does not visit rows and 32-cell
+        // segments outside it (they fail the exact gate, whose verdict is all pass 1 records).  Orthogonal axes
+        // (include/tamols.h), so the circle's extent along an axis is radius / |axis|.
+        WinBox b = {0, c.nr - 1, 0, c.nc - 1};
+        const double rad = sqrt(a.k.reach_hi2);
+        const double er = rad * sqrt(arx * arx + ary * ary) + 1.0, ec = rad * sqrt(acx * acx + acy * acy) + 1.0;
+        auto clampd = [](double v) { return fmin(fmax(v, -1.0e9), 1.0e9); };
+        auto shrink = [&](double px, double py) {
+            const double gr = (px - c.ox) * arx + (py - c.oy) * ary, gc = (px - c.ox) * acx + (py - c.oy) * acy;
+            b.r0 = max(b.r0, (int)clampd(floor(gr - er)) - c.r0);
+            b.r1 = min(b.r1, (int)clampd(ceil(gr + er)) - c.r0);
+            b.c0 = max(b.c0, (int)clampd(floor(gc - ec)) - c.c0);
+            b.c1 = min(b.c1, (int)clampd(ceil(gc + ec)) - c.c0);
+        };
+        shrink(j.hip[0], j.hip[1]);
+        if (c.flags & TAMOLS_FLAG_HAS_VELOCITY)
+            shrink(j.hip[0] + j.vel[0] * a.p.stance_duration, j.hip[1] + j.vel[1] * a.p.stance_duration);
+        s_wbox = b;
     }
     if (t >= 32 && t < 41) {  // nearest-cell offsets of the nine patch points (Stencil), as in k_tamols_score
         const int q = t - 32, i = q / 3 - 1, k = q % 3 - 1;
@@ -763,8 +796,8 @@ __global__ void __launch_bounds__(WTHREADS, 1024 / WTHREADS) k_tamols_window(con
     c.arx = s_inv.arx; c.ary = s_inv.ary; c.acx = s_inv.acx; c.acy = s_inv.acy;
     double s;
     int idx, nfin;
-    if (s_sten.exact != 0) window_passes<HT, true, WTHREADS>(a, c, j, s_sten, s_list, &s_nlist, job, s, idx, nfin);
-    else window_passes<HT, false, WTHREADS>(a, c, j, s_sten, s_list, &s_nlist, job, s, idx, nfin);
+    if (s_sten.exact != 0) window_passes<HT, true, WTHREADS>(a, c, j, s_sten, s_wbox, s_list, &s_nlist, job, s, idx, nfin);
+    else window_passes<HT, false, WTHREADS>(a, c, j, s_sten, s_wbox, s_list, &s_nlist, job, s, idx, nfin);
     // ---- block reduction: lexicographic (score, index) minimum = first minimum in row-major order
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {

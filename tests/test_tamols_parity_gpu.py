@@ -144,6 +144,35 @@ def test_cuda_scores_have_the_oracles_bits(tc, kind):
     assert np.array_equal(res["best_score"].view(np.uint64), ores["best_score"].view(np.uint64))
 
 
+@pytest.mark.parametrize("kind", ["noise", "stepping_stones_tall"])
+def test_cuda_result_only_launch_and_reach_box(tc, kind, tile_rows):
+    """A launch without the per-candidate score output (what a batched caller runs) takes k_tamols_window's plain pass 1,
+    which skips rows and 32-cell segments outside the bounding box of the reach circles: the result records must still
+    carry the oracle's bits.  Hips are moved so that the box is clipped by every window border, misses the window
+    entirely (no finite candidate: best_index -1) or covers it whole; one robot stands still (no velocity circle)."""
+    from oracle import tamols_oracle as to
+    rng = np.random.default_rng(33)
+    sc = sy.sweep_scene("go2", rng, kind, window=64, map_rows=256, map_cols=256, res=0.02, seed=9, robots=6)
+    jobs = sc["jobs"].copy()
+    shifts = [(0.0, 0.0), (0.55, 0.0), (-0.55, 0.0), (0.0, 0.6), (0.0, -0.6), (0.5, -0.5), (3.0, 0.0), (0.0, -3.0)]
+    for k in range(len(jobs)):
+        dx, dy = shifts[k % len(shifts)]
+        jobs["hip"][k, 0] += dx
+        jobs["hip"][k, 1] += dy
+        jobs["seed"][k, 0] += dx
+        jobs["seed"][k, 1] += dy
+    jobs["vel"][20:] = [2.0, -1.0, 0.0]   # hip + vel * 0.3 s is 0.67 m away: the two circles barely meet or do not
+    jobs["flags"][:4] &= ~1                # TAMOLS_FLAG_HAS_VELOCITY off: one circle only
+    p = tc.make_params(sy.tamols_params_for("go2"), "go2")
+    res, _, launches = _device_run(tc, p, sc["heights"], jobs, want_scores=False)
+    assert launches == 1
+    ores, _ = to.score(p, sc["heights"], jobs, fast=False)
+    assert np.array_equal(res["best_index"], ores["best_index"]) and np.array_equal(res["num_finite"], ores["num_finite"])
+    assert np.array_equal(res["best_score"].view(np.uint64), ores["best_score"].view(np.uint64))
+    assert np.array_equal(res["best_xyz"], ores["best_xyz"])
+    assert (res["best_index"] == -1).any() and (res["num_finite"] > 300).any()  # both ends of the range are present
+
+
 def test_cuda_plain_staging_equals_tma_staging(tc):
     """Odd row pitch (no tensor map possible) takes the plain-load kernel: identical results."""
     from oracle import tamols_oracle as to
