@@ -129,9 +129,10 @@ class BatchedHostSolver:
         return sum(h.launch_count for h in self.handles)
 
     def close(self):
-        for stream in self.streams:
+        """Idempotent; also runs from __del__ (possibly after a constructor that failed half way)."""
+        for stream in getattr(self, "streams", []):
             stream.synchronize()
-        for h in self.handles:
+        for h in getattr(self, "handles", []):
             h.close()
         self.handles, self.streams = [], []
         self.p_in = self.p_out = self.d_in = self.d_out = None
