@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Small ncu target: a few launches of the hot kernels at bench shapes (C2 single solve, C5 batched, TAMOLS batched).
-Usage: python tools/profile_target.py [c2|c5|tamols] [reps]"""
+Usage: python tools/profile_target.py [c2|c3|c5|tamols] [reps]"""
 import os
 import sys
 
@@ -26,6 +26,15 @@ if what == "c2":
         r = h.solve(st, ref, seq, best, 42, it, timing=timing, nominal_freq=nominal, optimize_swing=1, want_costs=False)
         best = r["best"]
     print("c2 best cost", r["best_cost"])
+elif what == "c3":
+    st, ref, seq, timing, nominal = bench.config_problem("c3", 0)
+    h = _cabi.Handle(_cabi.make_config(sampling_method="cem_mppi", parametrization="cubic_spline", gait_adaptive=False,
+                                       num_parallel_computations=10000, **bench.HYQREAL1))
+    best, sig = np.zeros(h.P, np.float32), np.full(h.P, 3.0, np.float32)
+    for it in range(reps):
+        r = h.solve(st, ref, seq, best, 42, it, timing=timing, nominal_freq=nominal, optimize_swing=1, sigma_in=sig, want_costs=False)
+        best, sig = r["best"], r["sigma"]
+    print("c3 best cost", r["best_cost"])
 elif what == "c5":
     R, n = 8192, 1024
     h = _cabi.Handle(_cabi.make_config(sampling_method="mppi", parametrization="zero_order", num_parallel_computations=n,
